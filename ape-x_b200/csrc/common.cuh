@@ -1,0 +1,87 @@
+// common.cuh — shared host/device helpers for libper_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string>
+
+#include "../../include/per_b200.h"
+
+namespace perb {
+
+typedef unsigned long long u64;
+
+// ---- error plumbing -------------------------------------------------------------------
+inline std::string &err_slot() {
+    static thread_local std::string s;
+    return s;
+}
+inline int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    err_slot() = buf;
+    return code;
+}
+#define PER_CUDA(call)                                                                       \
+    do {                                                                                     \
+        cudaError_t e__ = (call);                                                            \
+        if (e__ != cudaSuccess)                                                              \
+            return perb::fail(PER_ERR_CUDA, "%s failed: %s (%s:%d)", #call,                  \
+                              cudaGetErrorString(e__), __FILE__, __LINE__);                  \
+    } while (0)
+
+// Makes the handle's device current for the duration of one ABI call and puts the
+// caller's device back afterwards (the caller is usually torch, which tracks its own).
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+        want = dev;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0 && prev != want) cudaSetDevice(prev);
+    }
+    int want = -1;
+};
+
+inline int ilog2_exact(int64_t x) {
+    int l = 0;
+    while ((int64_t(1) << l) < x) ++l;
+    return l;
+}
+inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// ---- device helpers -------------------------------------------------------------------
+// 64-bit L2-only loads: tree nodes are rewritten by other CTAs / earlier phases of the
+// same kernel, so the update path never reads them through L1.
+__device__ __forceinline__ double ldcg_f64(const double *p) { return __ldcg(p); }
+__device__ __forceinline__ double2 ldcg_f64x2(const double *p) {
+    return __ldcg(reinterpret_cast<const double2 *>(p));
+}
+
+__device__ __forceinline__ double shfl_f64(double x, int src) {
+    return __shfl_sync(0xffffffffu, x, src);
+}
+
+// max over non-negative doubles / floats through their integer bit patterns
+__device__ __forceinline__ void atomic_max_pos_f64(double *addr, double x) {
+    atomicMax(reinterpret_cast<u64 *>(addr), (u64)__double_as_longlong(x));
+}
+__device__ __forceinline__ void atomic_max_pos_f32(float *addr, float x) {
+    atomicMax(reinterpret_cast<unsigned int *>(addr), __float_as_uint(x));
+}
+
+// priority ** alpha (memory.py:317).  alpha == 1 and alpha == 0 are exact shortcuts.
+__device__ __forceinline__ double pow_alpha(double p, double alpha) {
+    if (alpha == 1.0) return p;
+    if (alpha == 0.0) return 1.0;
+    return pow(p, alpha);
+}
+
+}  // namespace perb

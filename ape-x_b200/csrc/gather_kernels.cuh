@@ -1,0 +1,228 @@
+// gather_kernels.cuh — K4: gather sampled transitions out of the HBM-resident ring into
+// dense batch arrays (memory.py:171-182 `_encode_sample`), and the ring insert (memory.py:162-169).
+//
+// A transition row is two observations (uint8[4,84,84] = 28 224 B each on Atari), an int64
+// action, float32 reward and done, and an optional extra row (AQL's a_mu).  Rows are padded
+// to a multiple of 16 B so that every row start is 16-B aligned; each big row is cut into
+// pieces of at most PIECE_BYTES and every piece travels  HBM -> shared memory -> HBM  as
+// two TMA bulk copies (cp.async.bulk, SASS UBLKCP) issued by ONE lane per warp: no
+// registers are staged, the SM's LSU is idle, and each warp keeps several pieces in flight
+// through an mbarrier ring.  Algorithmic traffic per sampled transition: read 2*28 224+16 B,
+// write the same.
+#pragma once
+#include "common.cuh"
+
+namespace perb {
+
+constexpr int GATHER_WARPS = 8;        // independent copy engines per CTA
+constexpr int GATHER_STAGES = 3;       // pieces in flight per warp
+constexpr int PIECE_BYTES = 7056;      // one 84x84 frame; a multiple of 16
+constexpr int GATHER_SMEM = GATHER_WARPS * GATHER_STAGES * PIECE_BYTES;  // 169 344 B
+
+struct RowClass {
+    const uint8_t *src;  // ring base
+    uint8_t *dst;        // batch base (null: skip)
+    int64_t src_stride;  // padded row bytes in the ring
+    int64_t dst_stride;  // row bytes in the batch array (unpadded)
+    int64_t row_bytes;   // bytes to move per row (multiple of 16 when moved by TMA)
+    int pieces;          // ceil(row_bytes / PIECE_BYTES)
+};
+
+struct GatherArgs {
+    RowClass rc[3];  // obs, next_obs, extra
+    const int64_t *idx;
+    int64_t batch;
+    int64_t n_rows;  // rows present (for clamping bad indices)
+    const int64_t *act; const float *rew; const float *done;
+    int64_t *out_act; float *out_rew; float *out_done;
+    u64 *status;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "W_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra D_%=;\n"
+        "bra W_%=;\n"
+        "D_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
+// Decodes work item w -> source / destination / size.  Items are ordered row-major over
+// (query, class, piece) so that consecutive warps touch consecutive pieces of one row.
+struct Piece {
+    const uint8_t *src;
+    uint8_t *dst;
+    uint32_t bytes;
+};
+__device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, int per_query) {
+    int64_t q = w / per_query;
+    int r = (int)(w - q * per_query);
+    int c = 0;
+    while (r >= a.rc[c].pieces) {
+        r -= a.rc[c].pieces;
+        ++c;
+    }
+    int64_t k = a.idx[q];
+    if (k < 0 || k >= a.n_rows) k = 0;  // flagged by the scalar pass below; keep the copy in bounds
+    const RowClass &rc = a.rc[c];
+    int64_t off = (int64_t)r * PIECE_BYTES;
+    int64_t left = rc.row_bytes - off;
+    Piece p;
+    p.src = rc.src + k * rc.src_stride + off;
+    p.dst = rc.dst + q * rc.dst_stride + off;
+    p.bytes = (uint32_t)(left < PIECE_BYTES ? left : PIECE_BYTES);
+    return p;
+}
+
+__global__ void __launch_bounds__(GATHER_WARPS * 32, 1) k_gather_tma(GatherArgs a, int per_query) {
+    extern __shared__ __align__(128) uint8_t g_smem[];
+    __shared__ __align__(8) uint64_t bars[GATHER_WARPS][GATHER_STAGES];
+
+    // scalar columns (action / reward / done): plain coalesced loads, all threads
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < a.batch; q += (int64_t)gridDim.x * blockDim.x) {
+        int64_t k = a.idx[q];
+        if (k < 0 || k >= a.n_rows) {
+            atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
+            k = 0;
+        }
+        if (a.out_act) a.out_act[q] = a.act[k];
+        if (a.out_rew) a.out_rew[q] = a.rew[k];
+        if (a.out_done) a.out_done[q] = a.done[k];
+    }
+    if (per_query == 0) return;
+
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) != 0) return;  // one issuing lane per warp; nothing below is a CTA barrier
+
+    uint32_t bar[GATHER_STAGES], buf[GATHER_STAGES];
+#pragma unroll
+    for (int s = 0; s < GATHER_STAGES; ++s) {
+        bar[s] = smem_u32(&bars[warp][s]);
+        buf[s] = smem_u32(g_smem + (size_t)(warp * GATHER_STAGES + s) * PIECE_BYTES);
+        mbar_init(bar[s], 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+
+    const int64_t total = a.batch * per_query;
+    const int64_t first = (int64_t)blockIdx.x * GATHER_WARPS + warp;
+    const int64_t stride = (int64_t)gridDim.x * GATHER_WARPS;
+    const int64_t mine = first < total ? (total - first + stride - 1) / stride : 0;
+
+    // prologue: fill the ring
+    for (int64_t i = 0; i < GATHER_STAGES && i < mine; ++i) {
+        Piece p = decode_piece(a, first + i * stride, per_query);
+        mbar_expect_tx(bar[i], p.bytes);
+        bulk_g2s(buf[i], p.src, p.bytes, bar[i]);
+    }
+    for (int64_t i = 0; i < mine; ++i) {
+        const int s = (int)(i % GATHER_STAGES);
+        const uint32_t parity = (uint32_t)((i / GATHER_STAGES) & 1);
+        Piece p = decode_piece(a, first + i * stride, per_query);
+        mbar_wait(bar[s], parity);
+        bulk_s2g(p.dst, buf[s], p.bytes);
+        bulk_commit();
+        // refill the stage whose store was committed one iteration ago
+        if (i >= 1 && i - 1 + GATHER_STAGES < mine) {
+            bulk_wait_read<1>();  // all but the newest store have finished reading shared memory
+            const int sp = (int)((i - 1) % GATHER_STAGES);
+            Piece n = decode_piece(a, first + (i - 1 + GATHER_STAGES) * stride, per_query);
+            mbar_expect_tx(bar[sp], n.bytes);
+            bulk_g2s(buf[sp], n.src, n.bytes, bar[sp]);
+        }
+    }
+    bulk_wait_read<0>();
+}
+
+// Fallback mover for row classes whose size is not a multiple of 16 B (small non-Atari
+// observations, e.g. CartPole's float32[4]): byte-granular, one warp per row.
+__global__ void k_gather_bytes(GatherArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t w = warp; w < a.batch * 3; w += nwarps) {
+        int64_t q = w / 3;
+        const RowClass &rc = a.rc[w - q * 3];
+        if (!rc.dst || rc.row_bytes == 0) continue;
+        int64_t k = a.idx[q];
+        if (k < 0 || k >= a.n_rows) k = 0;
+        const uint8_t *s = rc.src + k * rc.src_stride;
+        uint8_t *d = rc.dst + q * rc.dst_stride;
+        for (int64_t i = lane; i < rc.row_bytes; i += 32) d[i] = s[i];
+    }
+}
+
+// Ring insert: n rows land in slots (start + j) mod ring_size.  Contiguous in the ring
+// except for one wrap, so this is a streaming copy: 16-B vectors, grid-stride.
+struct AddArgs {
+    const uint8_t *src[3];  // obs, next, extra batches (unpadded rows), may be null
+    uint8_t *dst[3];        // ring bases
+    int64_t row_bytes[3];
+    int64_t dst_stride[3];
+    const int64_t *act; const float *rew; const float *done;
+    int64_t *ring_act; float *ring_rew; float *ring_done;
+    int64_t start, ring_size, n;
+};
+
+__global__ void k_ring_add(AddArgs a) {
+    const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t j = tid; j < a.n; j += nthreads) {
+        int64_t k = a.start + j;
+        if (k >= a.ring_size) k -= a.ring_size;
+        if (a.act) a.ring_act[k] = a.act[j];
+        if (a.rew) a.ring_rew[k] = a.rew[j];
+        if (a.done) a.ring_done[k] = a.done[j];
+    }
+    for (int c = 0; c < 3; ++c) {
+        if (!a.src[c] || a.row_bytes[c] == 0) continue;
+        const int64_t rb = a.row_bytes[c];
+        if ((rb & 15) == 0 && ((uintptr_t)a.src[c] & 15) == 0) {
+            const int64_t vec_per_row = rb >> 4;
+            const int64_t total = a.n * vec_per_row;
+            for (int64_t e = tid; e < total; e += nthreads) {
+                int64_t j = e / vec_per_row, o = e - j * vec_per_row;
+                int64_t k = a.start + j;
+                if (k >= a.ring_size) k -= a.ring_size;
+                int4 x = __ldcs(reinterpret_cast<const int4 *>(a.src[c] + j * rb) + o);
+                reinterpret_cast<int4 *>(a.dst[c] + k * a.dst_stride[c])[o] = x;
+            }
+        } else {
+            const int64_t total = a.n * rb;
+            for (int64_t e = tid; e < total; e += nthreads) {
+                int64_t j = e / rb, o = e - j * rb;
+                int64_t k = a.start + j;
+                if (k >= a.ring_size) k -= a.ring_size;
+                a.dst[c][k * a.dst_stride[c] + o] = a.src[c][j * rb + o];
+            }
+        }
+    }
+}
+
+}  // namespace perb

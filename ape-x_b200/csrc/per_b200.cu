@@ -1,0 +1,552 @@
+// per_b200.cu — C ABI (include/per_b200.h) over the sm_100a kernels.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include <math.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "gather_kernels.cuh"
+#include "td_kernels.cuh"
+#include "tree_kernels.cuh"
+
+using namespace perb;
+
+// ------------------------------------------------------------------------------------------
+// handles
+// ------------------------------------------------------------------------------------------
+struct seg_tree_s {
+    int device;
+    int kind;
+    TreeRef t;        // exactly one of sum / mnn is set
+    double *v;
+    u64 *stamps;
+    u64 epoch;
+    u64 *status;      // device word
+    int sm_count;
+};
+
+struct per_buffer_s {
+    int device;
+    int64_t ring_size;
+    double alpha;
+    int64_t obs_bytes, obs_stride, extra_bytes, extra_stride;
+    TreeRef t;
+    u64 *stamps;
+    u64 epoch;
+    // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5
+    u64 *scal;
+    uint8_t *obs, *next, *extra;
+    int64_t *act;
+    float *rew, *done;
+    float *td_scratch;       // out_td | out_prio when the caller passes none
+    int64_t td_scratch_cap;  // rows
+    int64_t len, cursor;
+    int sm_count;
+    u64 *status() const { return scal; }
+    double *max_prio() const { return reinterpret_cast<double *>(scal + 1); }
+    float *td_red() const { return reinterpret_cast<float *>(scal + 2); }
+};
+
+namespace {
+
+__global__ void k_fill_f64(double *p, int64_t n, double x) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = x;
+}
+
+bool is_pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
+
+int ceil_log2(int64_t x) {
+    int l = 0;
+    while ((int64_t(1) << l) < x) ++l;
+    return l;
+}
+
+int alloc_tree(double **out, int64_t cap, double neutral, cudaStream_t s) {
+    PER_CUDA(cudaMalloc(out, sizeof(double) * 2 * cap));
+    if (neutral == 0.0) {
+        PER_CUDA(cudaMemsetAsync(*out, 0, sizeof(double) * 2 * cap, s));
+    } else {
+        k_fill_f64<<<(int)((2 * cap + 255) / 256 > 4096 ? 4096 : (2 * cap + 255) / 256), 256, 0, s>>>(*out, 2 * cap, neutral);
+        PER_CUDA(cudaGetLastError());
+    }
+    return PER_OK;
+}
+
+int grid_for(int64_t n, int threads, int sm_count) {
+    int64_t g = (n + threads - 1) / threads;
+    int64_t cap = (int64_t)sm_count * 8;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+// Batched leaf update + re-reduction (K1).  `td` non-null fuses K5 in front (one-CTA form only).
+int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s) {
+    TdArgs none;
+    memset(&none, 0, sizeof none);
+    if (a.n <= UPD_BLOCK_MAX_ITEMS) {
+        int T = (int)round_up(a.n > 0 ? a.n : 1, 32);
+        if (T < 128) T = 128;
+        if (T > UPD_BLOCK_THREADS) T = UPD_BLOCK_THREADS;
+        k_update_block<<<1, T, 0, s>>>(a, td ? *td : none, td ? 1 : 0, skip_update);
+        PER_CUDA(cudaGetLastError());
+        return PER_OK;
+    }
+    if (td) return fail(PER_ERR_ARG, "internal: fused TD needs the one-CTA update form");
+    const int g = grid_for(a.n, 256, sm_count);
+    if (a.stamps) k_upd_stamp<<<g, 256, 0, s>>>(a);
+    k_upd_leaf<<<g, 256, 0, s>>>(a);
+    const int L = a.t.L;
+    const int top = L < TOP_LEVELS ? L : TOP_LEVELS;
+    int d_dense = ceil_log2(a.n) + 2;  // below this depth a dense rebuild touches fewer nodes than n sparse lifts
+    if (d_dense > L) d_dense = L;
+    if (d_dense < top) d_dense = top;
+    int done = 0;
+    while (L - done > d_dense) {
+        int sl = L - done - d_dense;
+        if (sl > 3) sl = 3;
+        k_upd_sparse<<<g, 256, 0, s>>>(a, done, sl);
+        done += sl;
+    }
+    int d = d_dense;
+    while (d > top) {
+        int k = d - top < TOP_LEVELS ? d - top : TOP_LEVELS;
+        k_dense_mid<<<(unsigned)(int64_t(1) << (d - k)), 256, 0, s>>>(a.t, d, k);
+        d -= k;
+    }
+    k_dense_top<<<1, 1024, 0, s>>>(a.t);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+u64 next_epoch(u64 &epoch, u64 *stamps, int64_t cap, cudaStream_t s) {
+    if (++epoch >= (u64(1) << 32)) {  // 2^32 calls: start the stamps over
+        cudaMemsetAsync(stamps, 0, sizeof(u64) * cap, s);
+        epoch = 1;
+    }
+    return epoch << 32;
+}
+
+int read_status(u64 *d_status, int64_t *h_out, cudaStream_t s) {
+    u64 w = 0;
+    PER_CUDA(cudaMemcpyAsync(&w, d_status, sizeof w, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemsetAsync(d_status, 0, sizeof w, s));
+    PER_CUDA(cudaStreamSynchronize(s));
+    if (h_out) *h_out = (int64_t)w;
+    return PER_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *per_last_error(void) { return err_slot().c_str(); }
+int per_version(void) { return 100; }
+
+// ---------------------------------------------------------------------------------- trees
+int seg_create(seg_tree **out, int device, int64_t capacity, int kind) {
+    if (!out) return fail(PER_ERR_ARG, "seg_create: null out");
+    if (!is_pow2(capacity)) return fail(PER_ERR_ASSERT, "capacity must be positive and a power of 2.");
+    if (kind != PER_TREE_SUM && kind != PER_TREE_MIN) return fail(PER_ERR_ARG, "seg_create: bad kind %d", kind);
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "seg_create: cannot select device %d", device);
+    seg_tree *t = new seg_tree();
+    memset(t, 0, sizeof *t);
+    t->device = device;
+    t->kind = kind;
+    cudaDeviceGetAttribute(&t->sm_count, cudaDevAttrMultiProcessorCount, device);
+    int rc = alloc_tree(&t->v, capacity, kind == PER_TREE_SUM ? 0.0 : (double)INFINITY, 0);
+    if (rc) { delete t; return rc; }
+    t->t.cap = capacity;
+    t->t.L = ilog2_exact(capacity);
+    (kind == PER_TREE_SUM ? t->t.sum : t->t.mnn) = t->v;
+    PER_CUDA(cudaMalloc(&t->stamps, sizeof(u64) * capacity));
+    PER_CUDA(cudaMemsetAsync(t->stamps, 0, sizeof(u64) * capacity, 0));
+    PER_CUDA(cudaMalloc(&t->status, sizeof(u64)));
+    PER_CUDA(cudaMemsetAsync(t->status, 0, sizeof(u64), 0));
+    PER_CUDA(cudaStreamSynchronize(0));
+    *out = t;
+    return PER_OK;
+}
+
+int seg_destroy(seg_tree *t) {
+    if (!t) return PER_OK;
+    DeviceGuard g(t->device);
+    cudaFree(t->v);
+    cudaFree(t->stamps);
+    cudaFree(t->status);
+    delete t;
+    return PER_OK;
+}
+
+int64_t seg_capacity(const seg_tree *t) { return t ? t->t.cap : -1; }
+
+int seg_set(seg_tree *t, const int64_t *d_idx, const double *d_val, int64_t n, void *stream) {
+    if (!t || n < 0 || (n && (!d_idx || !d_val))) return fail(PER_ERR_ARG, "seg_set: bad argument");
+    if (n == 0) return PER_OK;
+    DeviceGuard g(t->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    UpdArgs a;
+    memset(&a, 0, sizeof a);
+    a.t = t->t;
+    a.idx = d_idx;
+    a.src = d_val;
+    a.src_kind = LEAF_GIVEN;
+    a.alpha = 1.0;
+    a.n = n;
+    a.len_limit = t->t.cap;
+    a.stamps = t->stamps;
+    a.epoch_hi = next_epoch(t->epoch, t->stamps, t->t.cap, s);
+    a.status = t->status;
+    return run_update(a, nullptr, 0, t->sm_count, s);
+}
+
+int seg_reduce(seg_tree *t, int64_t start, int64_t end, double *d_out, void *stream) {
+    if (!t || !d_out) return fail(PER_ERR_ARG, "seg_reduce: bad argument");
+    if (end < 0) end += t->t.cap;  // memory.py:71-72
+    if (start < 0 || end > t->t.cap || end - 1 < start)
+        return fail(PER_ERR_ASSERT, "seg_reduce: empty or out-of-range [%lld, %lld)", (long long)start, (long long)end);
+    DeviceGuard g(t->device);
+    k_range_reduce<<<1, 32, 0, (cudaStream_t)stream>>>(t->v, t->t.cap, start, end - 1, t->kind == PER_TREE_SUM, d_out);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int seg_find_prefixsum(seg_tree *t, const double *d_mass, int64_t n, int64_t *d_out_idx, void *stream) {
+    if (!t || n < 0 || (n && (!d_mass || !d_out_idx))) return fail(PER_ERR_ARG, "seg_find_prefixsum: bad argument");
+    if (t->kind != PER_TREE_SUM) return fail(PER_ERR_ARG, "seg_find_prefixsum: not a sum tree");
+    if (n == 0) return PER_OK;
+    DeviceGuard g(t->device);
+    SampleArgs a;
+    memset(&a, 0, sizeof a);
+    a.sum = t->v;
+    a.cap = t->t.cap;
+    a.L = t->t.L;
+    a.u = d_mass;
+    a.direct_mass = 1;
+    a.batch = n;
+    a.out_idx = d_out_idx;
+    a.status = t->status;
+    k_sample<<<(unsigned)((n * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int seg_read(seg_tree *t, double *d_out, void *stream) {
+    if (!t || !d_out) return fail(PER_ERR_ARG, "seg_read: bad argument");
+    DeviceGuard g(t->device);
+    PER_CUDA(cudaMemcpyAsync(d_out, t->v, sizeof(double) * 2 * t->t.cap, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PER_OK;
+}
+
+int seg_status(seg_tree *t, int64_t *h_out, void *stream) {
+    if (!t) return fail(PER_ERR_ARG, "seg_status: null handle");
+    DeviceGuard g(t->device);
+    return read_status(t->status, h_out, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------ replay buffer
+int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, int64_t obs_bytes, int64_t extra_bytes) {
+    if (!out) return fail(PER_ERR_ARG, "per_create: null out");
+    if (!(alpha >= 0)) return fail(PER_ERR_ASSERT, "alpha >= 0");
+    if (ring_size <= 0 || obs_bytes < 0 || extra_bytes < 0) return fail(PER_ERR_ARG, "per_create: bad size");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "per_create: cannot select device %d", device);
+    per_buffer *b = new per_buffer();
+    memset(b, 0, sizeof *b);
+    b->device = device;
+    b->ring_size = ring_size;
+    b->alpha = alpha;
+    b->obs_bytes = obs_bytes;
+    b->obs_stride = round_up(obs_bytes, 16);
+    b->extra_bytes = extra_bytes;
+    b->extra_stride = round_up(extra_bytes, 16);
+    cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
+    int64_t cap = 1;
+    while (cap < ring_size) cap *= 2;  // memory.py:227-229
+    b->t.cap = cap;
+    b->t.L = ilog2_exact(cap);
+    int rc = alloc_tree(&b->t.sum, cap, 0.0, 0);
+    if (!rc) rc = alloc_tree(&b->t.mnn, cap, (double)INFINITY, 0);
+    if (rc) { per_destroy(b); return rc; }
+#define TRY_ALLOC(ptr, bytes)                                                                      \
+    do {                                                                                           \
+        if ((bytes) > 0 && cudaMalloc(&(ptr), (bytes)) != cudaSuccess) {                           \
+            cudaGetLastError();                                                                    \
+            per_destroy(b);                                                                        \
+            return fail(PER_ERR_NOMEM, "per_create: cudaMalloc of %lld bytes failed", (long long)(bytes)); \
+        }                                                                                          \
+    } while (0)
+    TRY_ALLOC(b->stamps, sizeof(u64) * cap);
+    TRY_ALLOC(b->scal, sizeof(u64) * 4);
+    TRY_ALLOC(b->obs, b->obs_stride * ring_size);
+    TRY_ALLOC(b->next, b->obs_stride * ring_size);
+    TRY_ALLOC(b->extra, b->extra_stride * ring_size);
+    TRY_ALLOC(b->act, sizeof(int64_t) * ring_size);
+    TRY_ALLOC(b->rew, sizeof(float) * ring_size);
+    TRY_ALLOC(b->done, sizeof(float) * ring_size);
+    b->td_scratch_cap = UPD_BLOCK_MAX_ITEMS;
+    TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
+#undef TRY_ALLOC
+    PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 4, 0));
+    const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
+    PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
+    PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM));
+    PER_CUDA(cudaStreamSynchronize(0));
+    *out = b;
+    return PER_OK;
+}
+
+int per_destroy(per_buffer *b) {
+    if (!b) return PER_OK;
+    DeviceGuard g(b->device);
+    cudaFree(b->t.sum);
+    cudaFree(b->t.mnn);
+    cudaFree(b->stamps);
+    cudaFree(b->scal);
+    cudaFree(b->obs);
+    cudaFree(b->next);
+    cudaFree(b->extra);
+    cudaFree(b->act);
+    cudaFree(b->rew);
+    cudaFree(b->done);
+    cudaFree(b->td_scratch);
+    delete b;
+    return PER_OK;
+}
+
+int64_t per_capacity(const per_buffer *b) { return b ? b->t.cap : -1; }
+int64_t per_len(const per_buffer *b) { return b ? b->len : -1; }
+int64_t per_cursor(const per_buffer *b) { return b ? b->cursor : -1; }
+
+int per_max_priority(per_buffer *b, double *h_out, void *stream) {
+    if (!b || !h_out) return fail(PER_ERR_ARG, "per_max_priority: bad argument");
+    DeviceGuard g(b->device);
+    PER_CUDA(cudaMemcpyAsync(h_out, b->max_prio(), sizeof(double), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return PER_OK;
+}
+
+int per_status(per_buffer *b, int64_t *h_out, void *stream) {
+    if (!b) return fail(PER_ERR_ARG, "per_status: null handle");
+    DeviceGuard g(b->device);
+    return read_status(b->status(), h_out, (cudaStream_t)stream);
+}
+
+int per_add_batch(per_buffer *b, const void *d_obs, const void *d_next, const int64_t *d_act, const float *d_rew,
+                  const float *d_done, const void *d_extra, const double *d_prio, const double *d_leaf,
+                  double batch_max_priority, int64_t n, void *stream) {
+    if (!b || n < 0) return fail(PER_ERR_ARG, "per_add_batch: bad argument");
+    if (n > b->ring_size) return fail(PER_ERR_ARG, "per_add_batch: n=%lld exceeds the ring size %lld", (long long)n, (long long)b->ring_size);
+    if (n == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    AddArgs r;
+    memset(&r, 0, sizeof r);
+    r.src[0] = (const uint8_t *)d_obs;   r.dst[0] = b->obs;   r.row_bytes[0] = b->obs_bytes;   r.dst_stride[0] = b->obs_stride;
+    r.src[1] = (const uint8_t *)d_next;  r.dst[1] = b->next;  r.row_bytes[1] = b->obs_bytes;   r.dst_stride[1] = b->obs_stride;
+    r.src[2] = (const uint8_t *)d_extra; r.dst[2] = b->extra; r.row_bytes[2] = b->extra_bytes; r.dst_stride[2] = b->extra_stride;
+    r.act = d_act; r.rew = d_rew; r.done = d_done;
+    r.ring_act = b->act; r.ring_rew = b->rew; r.ring_done = b->done;
+    r.start = b->cursor; r.ring_size = b->ring_size; r.n = n;
+    int64_t work = n * ((b->obs_bytes * 2 + b->extra_bytes) / 16 + 1);
+    k_ring_add<<<grid_for(work, 256, b->sm_count * 2), 256, 0, s>>>(r);
+    PER_CUDA(cudaGetLastError());
+
+    UpdArgs a;
+    memset(&a, 0, sizeof a);
+    a.t = b->t;
+    a.idx = nullptr;
+    a.ring_start = b->cursor;
+    a.ring_size = b->ring_size;
+    a.src = d_leaf ? d_leaf : d_prio;
+    a.src_kind = d_leaf ? LEAF_GIVEN : (d_prio ? LEAF_PRIO_F64 : LEAF_MAXPRIO);
+    a.batch_max = batch_max_priority;
+    a.alpha = b->alpha;
+    a.n = n;
+    a.len_limit = b->ring_size;
+    a.stamps = nullptr;  // ring slots of one batch are distinct
+    a.status = b->status();
+    a.max_prio = b->max_prio();
+    int rc = run_update(a, nullptr, 0, b->sm_count, s);
+    if (rc) return rc;
+    b->cursor = (b->cursor + n) % b->ring_size;                        // memory.py:169
+    b->len = b->len + n > b->ring_size ? b->ring_size : b->len + n;    // memory.py:165-168
+    return PER_OK;
+}
+
+int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double beta, int64_t *d_out_idx,
+                       double *d_out_w64, float *d_out_w32, void *stream) {
+    if (!b || batch <= 0 || !d_u || !d_out_idx) return fail(PER_ERR_ARG, "per_sample_indices: bad argument");
+    if (!(beta > 0)) return fail(PER_ERR_ASSERT, "beta > 0");
+    if (b->len < 2) return fail(PER_ERR_ASSERT, "sample needs at least 2 stored transitions (the reference's range sum over [0, len-2] does not terminate for len == 1)");
+    DeviceGuard g(b->device);
+    SampleArgs a;
+    memset(&a, 0, sizeof a);
+    a.sum = b->t.sum;
+    a.mnn = b->t.mnn;
+    a.cap = b->t.cap;
+    a.L = b->t.L;
+    a.u = d_u;
+    a.batch = batch;
+    a.n_rows = b->len;
+    a.beta = beta;
+    a.out_idx = d_out_idx;
+    a.out_w64 = d_out_w64;
+    a.out_w32 = d_out_w32;
+    a.status = b->status();
+    k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_obs, void *d_out_next, int64_t *d_out_act,
+               float *d_out_rew, float *d_out_done, void *d_out_extra, void *stream) {
+    if (!b || batch < 0 || (batch && !d_idx)) return fail(PER_ERR_ARG, "per_gather: bad argument");
+    if (batch == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    GatherArgs a;
+    memset(&a, 0, sizeof a);
+    const uint8_t *srcs[3] = {b->obs, b->next, b->extra};
+    void *dsts[3] = {d_out_obs, d_out_next, d_out_extra};
+    int64_t rb[3] = {b->obs_bytes, b->obs_bytes, b->extra_bytes};
+    int64_t ss[3] = {b->obs_stride, b->obs_stride, b->extra_stride};
+    GatherArgs slow = a;
+    int per_query = 0;
+    bool any_slow = false;
+    for (int c = 0; c < 3; ++c) {
+        RowClass rc;
+        rc.src = srcs[c];
+        rc.dst = (uint8_t *)dsts[c];
+        rc.src_stride = ss[c];
+        rc.dst_stride = rb[c];
+        rc.row_bytes = rb[c];
+        rc.pieces = 0;
+        RowClass off = rc;
+        off.dst = nullptr;
+        const bool wanted = rc.dst && rb[c] > 0;
+        const bool tma_ok = wanted && (rb[c] % 16 == 0) && (((uintptr_t)rc.dst) % 16 == 0);
+        if (tma_ok) {
+            rc.pieces = (int)((rb[c] + PIECE_BYTES - 1) / PIECE_BYTES);
+            per_query += rc.pieces;
+            a.rc[c] = rc;
+            slow.rc[c] = off;
+        } else {
+            a.rc[c] = off;
+            slow.rc[c] = wanted ? rc : off;
+            any_slow |= wanted;
+        }
+    }
+    a.idx = slow.idx = d_idx;
+    a.batch = slow.batch = batch;
+    a.n_rows = slow.n_rows = b->len;
+    a.act = b->act; a.rew = b->rew; a.done = b->done;
+    a.out_act = d_out_act; a.out_rew = d_out_rew; a.out_done = d_out_done;
+    a.status = slow.status = b->status();
+    int64_t items = batch * per_query;
+    int64_t grid = (items + GATHER_WARPS - 1) / GATHER_WARPS;
+    if (grid > b->sm_count) grid = b->sm_count;  // persistent: one CTA per SM
+    if (grid < 1) grid = 1;
+    k_gather_tma<<<(unsigned)grid, GATHER_WARPS * 32, per_query ? GATHER_SMEM : 0, s>>>(a, per_query);
+    if (any_slow) k_gather_bytes<<<grid_for(batch * 3 * 32, 256, b->sm_count), 256, 0, s>>>(slow);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, int kind, double batch_max, int64_t n,
+                         const TdArgs *td, cudaStream_t s) {
+    UpdArgs a;
+    memset(&a, 0, sizeof a);
+    a.t = b->t;
+    a.idx = d_idx;
+    a.src = src;
+    a.src_kind = kind;
+    a.alpha = b->alpha;
+    a.n = n;
+    a.len_limit = b->len;
+    a.stamps = b->stamps;
+    a.epoch_hi = next_epoch(b->epoch, b->stamps, b->t.cap, s);
+    a.status = b->status();
+    a.max_prio = b->max_prio();
+    a.batch_max = batch_max;
+    return run_update(a, td, 0, b->sm_count, s);
+}
+
+int per_update_priorities(per_buffer *b, const int64_t *d_idx, const void *d_prio, int prio_dtype, int64_t n, void *stream) {
+    if (!b || n < 0 || (n && (!d_idx || !d_prio))) return fail(PER_ERR_ARG, "per_update_priorities: bad argument");
+    if (prio_dtype != PER_PRIO_F64 && prio_dtype != PER_PRIO_F32) return fail(PER_ERR_ARG, "per_update_priorities: bad dtype");
+    if (n == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    return update_common(b, d_idx, d_prio, prio_dtype == PER_PRIO_F64 ? LEAF_PRIO_F64 : LEAF_PRIO_F32, 0.0, n, nullptr,
+                         (cudaStream_t)stream);
+}
+
+int per_update_leaves(per_buffer *b, const int64_t *d_idx, const double *d_leaf, double batch_max_priority, int64_t n,
+                      void *stream) {
+    if (!b || n < 0 || (n && (!d_idx || !d_leaf))) return fail(PER_ERR_ARG, "per_update_leaves: bad argument");
+    if (n == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    return update_common(b, d_idx, d_leaf, LEAF_GIVEN, batch_max_priority, n, nullptr, (cudaStream_t)stream);
+}
+
+int per_pow_alpha_host(const double *h_prio, double alpha, double *h_out, int64_t n) {
+    if (n < 0 || (n && (!h_prio || !h_out))) return fail(PER_ERR_ARG, "per_pow_alpha_host: bad argument");
+    for (int64_t i = 0; i < n; ++i) h_out[i] = pow(h_prio[i], alpha);
+    return PER_OK;
+}
+
+int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_next, const float *d_q_tgt, int64_t n_actions,
+                           const int64_t *d_act, const float *d_rew, const float *d_done, const float *d_w, float gamma_n,
+                           const int64_t *d_idx, int64_t batch, float *d_out_prio, float *d_out_td, float *d_out_loss,
+                           void *stream) {
+    if (!b || batch <= 0 || n_actions <= 0 || !d_q || !d_q_next || !d_q_tgt || !d_act || !d_rew || !d_done)
+        return fail(PER_ERR_ARG, "per_td_priority_update: bad argument");
+    if (d_out_loss && !d_w) return fail(PER_ERR_ARG, "per_td_priority_update: loss needs weights");
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (batch > b->td_scratch_cap && (!d_out_prio || !d_out_td)) {
+        PER_CUDA(cudaStreamSynchronize(s));
+        cudaFree(b->td_scratch);
+        b->td_scratch = nullptr;
+        PER_CUDA(cudaMalloc(&b->td_scratch, sizeof(float) * 2 * batch));
+        b->td_scratch_cap = batch;
+    }
+    TdArgs t;
+    memset(&t, 0, sizeof t);
+    t.q = d_q; t.q_next = d_q_next; t.q_tgt = d_q_tgt;
+    t.nA = n_actions;
+    t.act = d_act; t.rew = d_rew; t.done = d_done; t.w = d_w;
+    t.gamma_n = gamma_n;
+    t.batch = batch;
+    t.out_td = d_out_td ? d_out_td : b->td_scratch;
+    t.out_prio = d_out_prio ? d_out_prio : b->td_scratch + b->td_scratch_cap;
+    t.out_loss = d_out_loss;
+    t.red = b->td_red();
+    if (batch <= UPD_BLOCK_MAX_ITEMS) {
+        if (d_idx) return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, &t, s);
+        UpdArgs a;
+        memset(&a, 0, sizeof a);
+        a.t = b->t;
+        a.n = batch;
+        return run_update(a, &t, 1, b->sm_count, s);
+    }
+    const int grid = grid_for(batch, 256, b->sm_count);
+    k_td_reset<<<1, 1, 0, s>>>(t.red);
+    k_td_pass1<<<grid, 256, 0, s>>>(t);
+    k_td_pass2<<<grid, 256, 0, s>>>(t);
+    k_td_finish<<<1, 1, 0, s>>>(t);
+    PER_CUDA(cudaGetLastError());
+    if (!d_idx) return PER_OK;
+    return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, nullptr, s);
+}
+
+int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
+    if (!b || !d_out || (which != PER_TREE_SUM && which != PER_TREE_MIN)) return fail(PER_ERR_ARG, "per_tree_read: bad argument");
+    DeviceGuard g(b->device);
+    PER_CUDA(cudaMemcpyAsync(d_out, which == PER_TREE_SUM ? b->t.sum : b->t.mnn, sizeof(double) * 2 * b->t.cap,
+                             cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PER_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,394 @@
+#!/usr/bin/env python
+"""bench.py — prioritized-replay hot path on B200: sample (prefix-sum descent + importance
+weights + frame gather) -> TD-error -> priority -> tree update, per batch.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Prints ONE JSON line (rank 0).  `value` = transitions sampled+updated per second over all
+ranks with every input resident in HBM; `e2e` = the same loop through the reference-facing
+Python API (memory.py: sample() -> host numpy, update_priorities(host arrays)), host<->device
+copies inside the timed region; `roofline` = the frame-gather kernel (the HBM-bound one)
+timed with CUDA events around each of its launches inside the timed region;
+`cpu_baseline` = the oracle port of the reference's Python path on this box's host cores.
+
+Workload (BASELINE.json configs[1], SURVEY.md §8d "C2"): ring of 2^20 Atari transitions
+(uint8[4,84,84] obs + next_obs, int64 action, f32 reward/done = 59.2 GB in HBM), batch 512,
+alpha 0.6, beta 0.4, n-step 3, 18 actions, synthetic data (torch.Generator seed 0).
+The ring (59 GB) is far larger than L2 (126 MB), so sampled rows come from HBM; the two
+trees (32 MiB) are L2-resident by nature.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "ape-x_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+RING = 1 << 20
+BATCH = 512
+OBS_SHAPE = (4, 84, 84)
+OBS_BYTES = 4 * 84 * 84
+N_ACTIONS = 18
+ALPHA, BETA, N_STEP, GAMMA = 0.6, 0.4, 3, 0.99
+METRIC = "PER sample+update transitions/s"
+UNIT = "transitions/s"
+# per sampled transition the gather reads 2*28224 B of frames + 16 B of
+# scalars and writes the same.
+GATHER_BYTES_PER_ROW = 2 * (2 * OBS_BYTES + 16)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop_evt = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_evt.wait(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------ CPU baseline
+def build_cpu_port(ring, seed=0):
+    """The oracle's list-backed port of the reference buffer, pre-filled to `ring` rows.  The
+    trees are filled through the vectorised builder (same node values as `ring` sequential
+    adds, minutes faster); rows reference a pool of 256 distinct frame pairs, as the
+    reference stores rows by reference (memory.py:163-168)."""
+    from oracle import per_oracle as po
+    rng = np.random.default_rng(seed)
+    buf = po.ReplayOracle(ring, ALPHA, "apex")
+    pool = rng.integers(0, 256, size=(256,) + OBS_SHAPE, dtype=np.uint8)
+    prio = np.abs(rng.standard_normal(ring)) + 1e-6
+    leaves = prio ** ALPHA
+    cap = po.next_pow2(ring)
+    ls, lm = np.zeros(cap), np.full(cap, np.inf)
+    ls[:ring] = lm[:ring] = leaves
+    buf.sum_tree.v = po.build_tree(ls, "sum").tolist()
+    buf.min_tree.v = po.build_tree(lm, "min").tolist()
+    buf.rows = [(pool[i & 255], i % N_ACTIONS, float(i % 3 - 1), pool[(i + 1) & 255], 0.0) for i in range(ring)]
+    buf.cursor = 0
+    buf.max_priority = float(max(1.0, prio.max()))
+    return buf
+
+
+def cpu_step(buf, rng):
+    """One reference learner-side replay step: sample(B, beta) then update_priorities."""
+    u = rng.random(BATCH)
+    out = buf.sample(BATCH, BETA, u)
+    pr = np.abs(rng.standard_normal(BATCH)) + 1e-6
+    buf.update_priorities(out[-1], [float(p) for p in pr])
+
+
+def run_cpu_baseline(steps, warmup, budget_s=None):
+    buf = build_cpu_port(RING)
+    rng = np.random.default_rng(1)
+    for _ in range(warmup):
+        cpu_step(buf, rng)
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        cpu_step(buf, rng)
+        done += 1
+        if budget_s is not None and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return done * BATCH / dt, done, dt
+
+
+def reference_arm(args, rank):
+    """--impl reference: the reference's own CPU algorithm (oracle port: pure Python over
+    Python lists, like memory.py — it is serial, so 1 core) on the same config and metric."""
+    if rank != 0:
+        return
+    steps = min(args.steps, 400)  # ~25 ms per step; keeps the run within minutes
+    value, done, dt = run_cpu_baseline(steps, min(args.warmup, 5))
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+        "steps": done, "warmup": min(args.warmup, 5), "ms_per_step": 1e3 * dt / max(done, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": "%d steps of sample(512)+update_priorities(512) on a 2^20-leaf tree, "
+                                   "oracle/per_oracle.py ReplayOracle (pure Python like memory.py), "
+                                   "host has %d cores" % (done, os.cpu_count())},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus):
+    return {"workload": "Ape-X learner replay step, configs[1]: ring 2^20 Atari transitions per GPU (59.2 GB HBM), "
+                        "batch 512 per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions",
+            "ring_per_gpu": RING, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
+            "l2": "inputs (59 GB ring) larger than L2; no flush", "parallelism": "shard%d" % n_gpus}
+
+
+# ------------------------------------------------------------------------------- GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return 0
+
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as entry
+    entry.build()
+    import memory
+    import per_native as pn
+
+    assert torch.cuda.is_available(), "bench.py needs a B200; the product has no CPU path"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    ring = args.ring
+    W = max(args.warmup, 3)
+    K = args.steps
+
+    # ---- build + fill the shard --------------------------------------------------------
+    buf = memory.CustomPrioritizedReplayBuffer(ring, ALPHA)
+    gen = torch.Generator(device=dev).manual_seed(rank)
+    chunk = 8192
+    for lo in range(0, ring, chunk):
+        m = min(chunk, ring - lo)
+        obs = torch.randint(0, 256, (m,) + OBS_SHAPE, dtype=torch.uint8, device=dev, generator=gen)
+        nxt = torch.randint(0, 256, (m,) + OBS_SHAPE, dtype=torch.uint8, device=dev, generator=gen)
+        act = torch.randint(0, N_ACTIONS, (m,), dtype=torch.int64, device=dev, generator=gen)
+        rew = torch.randint(-1, 2, (m,), device=dev, generator=gen).float()
+        done = (torch.rand(m, device=dev, generator=gen) < 1e-3).float()
+        pr = torch.randn(m, dtype=torch.float64, device=dev, generator=gen).abs() + 1e-6
+        buf.add_batch_device(obs, nxt, act, rew, done, priorities=pr)
+    del obs, nxt
+    torch.cuda.synchronize()
+
+    # ---- resident inputs / outputs -------------------------------------------------------
+    total_steps = W + K
+    n_u = min(total_steps, 4096)  # distinct uniform vectors, cycled
+    u_all = torch.rand(n_u, BATCH, dtype=torch.float64, device=dev, generator=gen)
+    q = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
+    qn = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
+    qt = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
+    idx = torch.empty(BATCH, dtype=torch.int64, device=dev)
+    w32 = torch.empty(BATCH, dtype=torch.float32, device=dev)
+    o_obs = torch.empty((BATCH,) + OBS_SHAPE, dtype=torch.uint8, device=dev)
+    o_nxt = torch.empty_like(o_obs)
+    o_act = torch.empty(BATCH, dtype=torch.int64, device=dev)
+    o_rew = torch.empty(BATCH, dtype=torch.float32, device=dev)
+    o_done = torch.empty(BATCH, dtype=torch.float32, device=dev)
+    o_prio = torch.empty(BATCH, dtype=torch.float32, device=dev)
+    o_loss = torch.empty(1, dtype=torch.float32, device=dev)
+    shard_rec = torch.zeros(4, dtype=torch.float64, device=dev)
+    all_rec = torch.zeros(world * 4, dtype=torch.float64, device=dev) if world > 1 else None
+
+    lib, h = pn.lib, buf._h
+    stream = torch.cuda.current_stream()
+    sp = pn.stream_ptr(stream)
+    P = pn.ptr
+    gamma_n = float(np.float32(GAMMA ** N_STEP))
+    a_idx, a_w32 = P(idx), P(w32)
+    a_gather = (h, a_idx, BATCH, P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp)
+    a_td = (h, P(q), P(qn), P(qt), N_ACTIONS, P(o_act), P(o_rew), P(o_done), a_w32, gamma_n, a_idx, BATCH, P(o_prio),
+            None, P(o_loss), sp)
+    u_ptrs = [pn.C.c_void_p(u_all[i].data_ptr()) for i in range(n_u)]
+    launches_per_step = 3  # k_sample, k_gather_tma, k_update_block (TD fused in front)
+
+    def step(i, ev=None):
+        if world > 1:  # shard totals exchange: root sum/min + fill count, 32 B per rank
+            dist.all_gather_into_tensor(all_rec, shard_rec)
+        rc = lib.per_sample_indices(h, u_ptrs[i % n_u], BATCH, BETA, a_idx, None, a_w32, sp)
+        if ev is not None:
+            ev[0].record(stream)
+        rc |= lib.per_gather(*a_gather)
+        if ev is not None:
+            ev[1].record(stream)
+        rc |= lib.per_td_priority_update(*a_td)
+        if rc:
+            pn.check(rc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(W):
+        step(i)
+    barrier()
+
+    # ---- timed region: K eager steps, CUDA events on the launching stream ------------------
+    gather_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    e0.record(stream)
+    for i in range(K):
+        step(W + i, gather_ev[i])
+    e1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * BATCH * K / (ms * 1e-3)
+    gather_ms = float(np.mean([a.elapsed_time(b) for a, b in gather_ev]))
+    status = pn.C.c_int64(0)
+    pn.check(lib.per_status(h, pn.C.byref(status), sp))
+    assert status.value == 0, "device status word set during the bench: %d" % status.value
+
+    # ---- same loop as one CUDA graph (launch overhead removed) -----------------------------
+    graph_value = None
+    if world == 1:
+        try:
+            g_steps = min(K, 64)
+            side = torch.cuda.Stream()
+            side.wait_stream(stream)
+            with torch.cuda.stream(side):
+                sp_side = pn.stream_ptr(side)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=side):
+                    for i in range(g_steps):
+                        lib.per_sample_indices(h, u_ptrs[i % n_u], BATCH, BETA, a_idx, None, a_w32, sp_side)
+                        lib.per_gather(*(a_gather[:-1] + (sp_side,)))
+                        lib.per_td_priority_update(*(a_td[:-1] + (sp_side,)))
+            stream.wait_stream(side)
+            reps = max(3, K // g_steps)
+            graph.replay()
+            torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record(stream)
+            for _ in range(reps):
+                graph.replay()
+            g1.record(stream)
+            torch.cuda.synchronize()
+            graph_value = BATCH * g_steps * reps / (g0.elapsed_time(g1) * 1e-3)
+        except Exception as exc:  # capture is an extra, never the headline
+            graph_value = "capture failed: %s" % str(exc)[:120]
+
+    # ---- e2e: reference-facing API, host buffers in and out ---------------------------------
+    e2e_steps = max(3, min(K, 100))
+    prios_host = [np.abs(np.random.default_rng(i).standard_normal(BATCH)).astype(np.float32) + 1e-6 for i in range(8)]
+    import random as _random
+    _random.seed(0)
+    for i in range(3):
+        out = buf.sample(BATCH, BETA)
+        buf.update_priorities(out[-1], prios_host[i % 8])
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        out = buf.sample(BATCH, BETA)                      # uniforms H2D; frames, scalars, weights, idx D2H
+        buf.update_priorities(out[-1], prios_host[i % 8])  # idx + leaves H2D
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    d2h = sum(int(np.asarray(x).nbytes) for x in out[:-1]) + 8 * BATCH
+    h2d = 8 * BATCH + 8 * BATCH + 8 * BATCH
+    e2e = {"value": world * BATCH * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+           "api": "memory.CustomPrioritizedReplayBuffer.sample()/update_priorities() with host numpy in/out"}
+
+    # ---- CPU baseline on this box (rank 0, N=1 only) -----------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, done_steps, dt = run_cpu_baseline(10 ** 6, 3, budget_s=15.0)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": "%d steps (%.1f s) of sample(512)+update_priorities(512) on a 2^20-leaf tree with the "
+                         "oracle's pure-Python port of memory.py; host has %d cores, the reference path is serial"
+                         % (done_steps, dt, os.cpu_count())}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = GATHER_BYTES_PER_ROW * BATCH / (gather_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
+            "roofline": {"bound": "hbm", "kernel": "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "bytes_per_launch": GATHER_BYTES_PER_ROW * BATCH, "avg_launch_us": gather_ms * 1e3},
+            "cpu_baseline": cpu, "value_cuda_graph": graph_value,
+            "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

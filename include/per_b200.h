@@ -1,0 +1,172 @@
+/* per_b200.h — C ABI of the B200-native prioritized-replay library (libper_b200.so).
+ *
+ * This is the boundary a maintainer of Bing-Jing/Ape-X binds instead of the
+ * pure-Python classes of the reference's memory.py (the reference has no FFI
+ * of its own: it is Python only; the ctypes binding that replaces it is
+ * ape-x_b200/per_native.py, and INTEGRATION.md shows the stub).  Every entry point
+ * cites the reference function it replaces as  file:line  relative to the
+ * reference repository root.
+ *
+ * Conventions
+ *  - All pointers named d_* are DEVICE pointers on the handle's device; h_* are
+ *    host pointers.  The caller owns every buffer it passes; the handle owns
+ *    only the two trees, the transition ring and a small scratch area.
+ *  - `stream` is a cudaStream_t passed as void*.  All work is enqueued on it and
+ *    is stream-ordered; nothing synchronises unless the comment says so.
+ *  - One host thread per handle at a time (the reference object is not
+ *    thread-safe either; origin_repo/replay.py:92,121,142 serialises it).
+ *  - Return value: 0 = PER_OK, negative = error; per_last_error() gives the text
+ *    of the most recent failure on the calling thread.  Host-checkable
+ *    preconditions the reference asserts (memory.py:34,224,284,313) return
+ *    PER_ERR_ASSERT; data-dependent ones (priority <= 0, index out of range,
+ *    memory.py:315-316,121) set bits in a device status word read by
+ *    per_status() / seg_status().
+ *  - Tree node arrays use the reference's heap layout (memory.py:36): 2*capacity
+ *    float64, node 1 = root, children of i are 2i and 2i+1, leaf k at capacity+k,
+ *    so a copy to the host compares element by element with `_value`.
+ */
+#ifndef PER_B200_H
+#define PER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PER_OK            0
+#define PER_ERR_ASSERT   -1   /* a precondition the reference asserts */
+#define PER_ERR_CUDA     -2   /* a CUDA runtime call failed */
+#define PER_ERR_ARG      -3   /* malformed argument (null handle, negative size, ...) */
+#define PER_ERR_NOMEM    -4
+
+/* bits of the device status word */
+#define PER_STATUS_BAD_PRIORITY   1   /* priority <= 0 or NaN      (memory.py:315) */
+#define PER_STATUS_BAD_INDEX      2   /* idx outside [0, len)      (memory.py:316, :90) */
+#define PER_STATUS_BAD_PREFIXSUM  4   /* mass outside [0, sum+1e-5] (memory.py:121) */
+
+#define PER_TREE_SUM 0
+#define PER_TREE_MIN 1
+
+#define PER_PRIO_F64 0
+#define PER_PRIO_F32 1
+
+typedef struct seg_tree_s seg_tree;      /* one SumSegmentTree / MinSegmentTree          */
+typedef struct per_buffer_s per_buffer;  /* one (Custom)PrioritizedReplayBuffer(_AQL)    */
+
+const char *per_last_error(void);
+int per_version(void);
+
+/* ---------------------------------------------------------------- segment trees */
+
+/* SegmentTree.__init__ (memory.py:11-37): `capacity` must be a power of two
+ * (else PER_ERR_ASSERT); kind PER_TREE_SUM (neutral 0.0) or PER_TREE_MIN (+inf). */
+int seg_create(seg_tree **out, int device, int64_t capacity, int kind);
+int seg_destroy(seg_tree *t);
+
+/* Batched SegmentTree.__setitem__ (memory.py:76-87): equivalent to executing
+ * t[d_idx[j]] = d_val[j] for j = 0..n-1 in order (a later duplicate wins). */
+int seg_set(seg_tree *t, const int64_t *d_idx, const double *d_val, int64_t n, void *stream);
+
+/* SegmentTree.reduce(start, end) (memory.py:39-74), half-open, same association as
+ * the reference's recursion; result written to d_out[0].  end <= start is
+ * PER_ERR_ASSERT (the reference recurses without bound there). */
+int seg_reduce(seg_tree *t, int64_t start, int64_t end, double *d_out, void *stream);
+
+/* Batched SumSegmentTree.find_prefixsum_idx (memory.py:106-129). */
+int seg_find_prefixsum(seg_tree *t, const double *d_mass, int64_t n, int64_t *d_out_idx, void *stream);
+
+/* Copies the 2*capacity node array (`_value`, memory.py:36) to d_out. */
+int seg_read(seg_tree *t, double *d_out, void *stream);
+int64_t seg_capacity(const seg_tree *t);
+/* Reads and clears the status word.  Synchronises `stream`. */
+int seg_status(seg_tree *t, int64_t *h_out, void *stream);
+
+/* ---------------------------------------------------------------- prioritized replay */
+
+/* PrioritizedReplayBuffer.__init__ (memory.py:209-233) + ReplayBuffer.__init__
+ * (memory.py:147-157).  ring_size = the reference's `size` (the ring wraps there,
+ * memory.py:169); tree capacity = next power of two (memory.py:227-229).
+ * obs_bytes = bytes of one observation (28224 for uint8[4,84,84]); extra_bytes =
+ * bytes of the per-row extra field (AQL's a_mu, memory.py:370), 0 if none.
+ * alpha < 0 is PER_ERR_ASSERT (memory.py:224). */
+int per_create(per_buffer **out, int device, int64_t ring_size, double alpha,
+               int64_t obs_bytes, int64_t extra_bytes);
+int per_destroy(per_buffer *b);
+
+int64_t per_capacity(const per_buffer *b);   /* tree capacity (power of two)          */
+int64_t per_len(const per_buffer *b);        /* len(_storage)      (memory.py:159-160) */
+int64_t per_cursor(const per_buffer *b);     /* _next_idx          (memory.py:157,169) */
+/* _max_priority (memory.py:233,320).  Synchronises `stream`. */
+int per_max_priority(per_buffer *b, double *h_out, void *stream);
+int per_status(per_buffer *b, int64_t *h_out, void *stream);
+
+/* n consecutive ReplayBuffer.add calls (memory.py:162-169) fused with their tree
+ * writes.  Rows go to slots cursor, cursor+1, ... (mod ring_size); n <= ring_size.
+ * Leaf values, first match wins:
+ *   d_leaf != NULL : leaves = d_leaf[j] (float64, e.g. from per_pow_alpha_host: bit-exact
+ *                    with the reference) and _max_priority is raised to batch_max_priority
+ *   d_prio != NULL : leaves = d_prio[j] ** alpha on the device, running max raised
+ *                    (CustomPrioritizedReplayBuffer.add, memory.py:334-346; the ingest
+ *                    loop batchrecorder.py:133-137)
+ *   both NULL      : leaves = _max_priority ** alpha   (memory.py:235-240, :368-378)
+ * d_obs / d_next: n rows of obs_bytes; d_act int64[n]; d_rew, d_done float32[n];
+ * d_extra: n rows of extra_bytes or NULL.  Row pointers may be NULL (tree-only use). */
+int per_add_batch(per_buffer *b, const void *d_obs, const void *d_next, const int64_t *d_act,
+                  const float *d_rew, const float *d_done, const void *d_extra,
+                  const double *d_prio, const double *d_leaf, double batch_max_priority,
+                  int64_t n, void *stream);
+
+/* PrioritizedReplayBuffer._sample_proportional + the weight loop of sample()
+ * (memory.py:242-250, 288-296).  d_u: batch uniforms in [0,1) standing for the
+ * reference's random.random() draws, in order.  Outputs: d_out_idx int64[batch];
+ * d_out_w64 float64[batch] and/or d_out_w32 float32[batch] (either may be NULL).
+ * beta <= 0 is PER_ERR_ASSERT (memory.py:284); len < 2 is PER_ERR_ASSERT (the
+ * reference's range sum over [0, len-2] does not terminate for len == 1). */
+int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double beta,
+                       int64_t *d_out_idx, double *d_out_w64, float *d_out_w32, void *stream);
+
+/* ReplayBuffer._encode_sample (memory.py:171-182, :348-362, :380-391): gathers the
+ * rows d_idx[0..batch) into dense batch arrays.  Any output may be NULL. */
+int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch,
+               void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew,
+               float *d_out_done, void *d_out_extra, void *stream);
+
+/* PrioritizedReplayBuffer.update_priorities (memory.py:300-320), sequential
+ * semantics (a later duplicate wins), running max raised.  Priorities are float64
+ * (prio_dtype PER_PRIO_F64) or float32 (PER_PRIO_F32, what utils.py:77 hands back);
+ * leaves are priority ** alpha evaluated on the device (CUDA pow, <= 2 ulp from
+ * the C library's — for bit-identical leaves use per_update_leaves). */
+int per_update_priorities(per_buffer *b, const int64_t *d_idx, const void *d_prio, int prio_dtype,
+                          int64_t n, void *stream);
+
+/* Same, but the caller supplies the leaves (priority ** alpha, float64) and the
+ * raw priorities' maximum (for _max_priority, memory.py:320).  With leaves from
+ * per_pow_alpha_host this reproduces the reference tree bit for bit. */
+int per_update_leaves(per_buffer *b, const int64_t *d_idx, const double *d_leaf, double batch_max_priority,
+                      int64_t n, void *stream);
+
+/* Host helper: h_out[j] = pow(h_prio[j], alpha) with the C library's double pow —
+ * the function CPython's `priority ** alpha` calls (memory.py:317).  No GPU work. */
+int per_pow_alpha_host(const double *h_prio, double alpha, double *h_out, int64_t n);
+
+/* The arithmetic of utils.compute_loss after the three forwards (utils.py:71-80,
+ * identical in compute_loss_AQL utils.py:51-60) fused with update_priorities
+ * (ApeX.py:58,63): double-DQN target, |td|, prios = 0.9*max_b(td)+0.1*td+1e-6,
+ * Huber*weight loss, then leaves = prios**alpha written to both trees.
+ * d_q, d_q_next (online net on s, s'), d_q_tgt (target net on s'): float32
+ * [batch, n_actions] row-major.  gamma_n = gamma ** n_steps (float).  Outputs
+ * (any may be NULL): d_out_prio float32[batch], d_out_td float32[batch],
+ * d_out_loss float32[1].  If d_idx is NULL the trees are left alone. */
+int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_next, const float *d_q_tgt,
+                           int64_t n_actions, const int64_t *d_act, const float *d_rew, const float *d_done,
+                           const float *d_w, float gamma_n, const int64_t *d_idx, int64_t batch,
+                           float *d_out_prio, float *d_out_td, float *d_out_loss, void *stream);
+
+/* Copies one tree's node array (`_it_sum._value` / `_it_min._value`) to d_out[2*capacity]. */
+int per_tree_read(per_buffer *b, int which, double *d_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PER_B200_H */
