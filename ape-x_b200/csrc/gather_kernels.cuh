@@ -14,10 +14,17 @@
 
 namespace perb {
 
-constexpr int GATHER_WARPS = 8;        // independent copy engines per CTA
-constexpr int GATHER_STAGES = 3;       // pieces in flight per warp
-constexpr int PIECE_BYTES = 7056;      // one 84x84 frame; a multiple of 16
-constexpr int GATHER_SMEM = GATHER_WARPS * GATHER_STAGES * PIECE_BYTES;  // 169 344 B
+constexpr int GATHER_MAX_WARPS = 16;    // independent copy engines per CTA (upper bound)
+constexpr int GATHER_SMEM_MAX = 200 * 1024;
+
+// Launch shape of the TMA gather; defaults chosen by the sweep in profiles/ (see DESIGN.md).
+struct GatherTune {
+    int mode = 0;        // 0: TMA bulk copies through shared memory, 1: LDG.128/STG.128 through registers
+    int warps = 4;       // issuing warps per CTA
+    int stages = 2;      // pieces in flight per warp
+    int piece = 7056;    // bytes per piece (multiple of 16); 7056 = one 84x84 frame
+    int ctas_per_sm = 4; // 4 x (4 x 2 x 7056 B) = 226 KB of shared memory per SM
+};
 
 struct RowClass {
     const uint8_t *src;  // ring base
@@ -25,7 +32,7 @@ struct RowClass {
     int64_t src_stride;  // padded row bytes in the ring
     int64_t dst_stride;  // row bytes in the batch array (unpadded)
     int64_t row_bytes;   // bytes to move per row (multiple of 16 when moved by TMA)
-    int pieces;          // ceil(row_bytes / PIECE_BYTES)
+    int pieces;          // ceil(row_bytes / piece)
 };
 
 struct GatherArgs {
@@ -36,6 +43,8 @@ struct GatherArgs {
     const int64_t *act; const float *rew; const float *done;
     int64_t *out_act; float *out_rew; float *out_done;
     u64 *status;
+    int piece;   // bytes per piece
+    int stages;  // TMA ring depth per warp
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -69,6 +78,7 @@ __device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src, uint32_t bytes
                  : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ int round_up_dev(int x, int m) { return (x + m - 1) / m * m; }
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
@@ -92,19 +102,16 @@ __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, in
     int64_t k = a.idx[q];
     if (k < 0 || k >= a.n_rows) k = 0;  // flagged by the scalar pass below; keep the copy in bounds
     const RowClass &rc = a.rc[c];
-    int64_t off = (int64_t)r * PIECE_BYTES;
+    int64_t off = (int64_t)r * a.piece;
     int64_t left = rc.row_bytes - off;
     Piece p;
     p.src = rc.src + k * rc.src_stride + off;
     p.dst = rc.dst + q * rc.dst_stride + off;
-    p.bytes = (uint32_t)(left < PIECE_BYTES ? left : PIECE_BYTES);
+    p.bytes = (uint32_t)(left < a.piece ? left : a.piece);
     return p;
 }
 
-__global__ void __launch_bounds__(GATHER_WARPS * 32, 1) k_gather_tma(GatherArgs a, int per_query) {
-    extern __shared__ __align__(128) uint8_t g_smem[];
-    __shared__ __align__(8) uint64_t bars[GATHER_WARPS][GATHER_STAGES];
-
+__device__ __forceinline__ void gather_scalars(const GatherArgs &a) {
     // scalar columns (action / reward / done): plain coalesced loads, all threads
     for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < a.batch; q += (int64_t)gridDim.x * blockDim.x) {
         int64_t k = a.idx[q];
@@ -116,48 +123,90 @@ __global__ void __launch_bounds__(GATHER_WARPS * 32, 1) k_gather_tma(GatherArgs 
         if (a.out_rew) a.out_rew[q] = a.rew[k];
         if (a.out_done) a.out_done[q] = a.done[k];
     }
+}
+
+// Dynamic shared memory: [warps*stages mbarriers, padded to 128 B][warps*stages pieces].
+__global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs a, int per_query) {
+    extern __shared__ __align__(128) uint8_t g_smem[];
+    gather_scalars(a);
     if (per_query == 0) return;
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
     if ((threadIdx.x & 31) != 0) return;  // one issuing lane per warp; nothing below is a CTA barrier
 
-    uint32_t bar[GATHER_STAGES], buf[GATHER_STAGES];
-#pragma unroll
-    for (int s = 0; s < GATHER_STAGES; ++s) {
-        bar[s] = smem_u32(&bars[warp][s]);
-        buf[s] = smem_u32(g_smem + (size_t)(warp * GATHER_STAGES + s) * PIECE_BYTES);
-        mbar_init(bar[s], 1);
-    }
+    const int NS = a.stages;
+    const uint32_t bar0 = smem_u32(g_smem) + (uint32_t)(warp * NS) * 8u;
+    const uint32_t buf0 = smem_u32(g_smem) + (uint32_t)round_up_dev(warps * NS * 8, 128) + (uint32_t)(warp * NS) * (uint32_t)a.piece;
+    for (int s = 0; s < NS; ++s) mbar_init(bar0 + 8u * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 
     const int64_t total = a.batch * per_query;
-    const int64_t first = (int64_t)blockIdx.x * GATHER_WARPS + warp;
-    const int64_t stride = (int64_t)gridDim.x * GATHER_WARPS;
+    const int64_t first = (int64_t)blockIdx.x * warps + warp;
+    const int64_t stride = (int64_t)gridDim.x * warps;
     const int64_t mine = first < total ? (total - first + stride - 1) / stride : 0;
 
     // prologue: fill the ring
-    for (int64_t i = 0; i < GATHER_STAGES && i < mine; ++i) {
+    for (int64_t i = 0; i < NS && i < mine; ++i) {
         Piece p = decode_piece(a, first + i * stride, per_query);
-        mbar_expect_tx(bar[i], p.bytes);
-        bulk_g2s(buf[i], p.src, p.bytes, bar[i]);
+        mbar_expect_tx(bar0 + 8u * (uint32_t)i, p.bytes);
+        bulk_g2s(buf0 + (uint32_t)i * (uint32_t)a.piece, p.src, p.bytes, bar0 + 8u * (uint32_t)i);
     }
+    int s = 0;
+    uint32_t parity = 0;
     for (int64_t i = 0; i < mine; ++i) {
-        const int s = (int)(i % GATHER_STAGES);
-        const uint32_t parity = (uint32_t)((i / GATHER_STAGES) & 1);
         Piece p = decode_piece(a, first + i * stride, per_query);
-        mbar_wait(bar[s], parity);
-        bulk_s2g(p.dst, buf[s], p.bytes);
+        mbar_wait(bar0 + 8u * s, parity);
+        bulk_s2g(p.dst, buf0 + (uint32_t)s * (uint32_t)a.piece, p.bytes);
         bulk_commit();
         // refill the stage whose store was committed one iteration ago
-        if (i >= 1 && i - 1 + GATHER_STAGES < mine) {
+        if (i >= 1 && i - 1 + NS < mine) {
             bulk_wait_read<1>();  // all but the newest store have finished reading shared memory
-            const int sp = (int)((i - 1) % GATHER_STAGES);
-            Piece n = decode_piece(a, first + (i - 1 + GATHER_STAGES) * stride, per_query);
-            mbar_expect_tx(bar[sp], n.bytes);
-            bulk_g2s(buf[sp], n.src, n.bytes, bar[sp]);
+            const int sp = s == 0 ? NS - 1 : s - 1;
+            Piece n = decode_piece(a, first + (i - 1 + NS) * stride, per_query);
+            mbar_expect_tx(bar0 + 8u * sp, n.bytes);
+            bulk_g2s(buf0 + (uint32_t)sp * (uint32_t)a.piece, n.src, n.bytes, bar0 + 8u * sp);
         }
+        if (++s == NS) { s = 0; parity ^= 1u; }
     }
     bulk_wait_read<0>();
+}
+
+// Register-staged variant: one warp per piece, up to 16 x 16-B loads in flight per lane,
+// streaming cache hints (rows are touched once).
+__device__ __forceinline__ int4 ld_stream(const int4 *p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream(int4 *p, const int4 &v) {
+    asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__global__ void __launch_bounds__(256) k_gather_ldg(GatherArgs a, int per_query) {
+    gather_scalars(a);
+    if (per_query == 0) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t total = a.batch * per_query;
+    for (int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; w < total; w += warps) {
+        Piece p = decode_piece(a, w, per_query);
+        const int4 *src = reinterpret_cast<const int4 *>(p.src);
+        int4 *dst = reinterpret_cast<int4 *>(p.dst);
+        const int nv = (int)(p.bytes >> 4);
+        for (int base = 0; base < nv; base += 32 * 16) {
+            int4 v[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                int e = base + j * 32 + lane;
+                if (e < nv) v[j] = ld_stream(src + e);
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                int e = base + j * 32 + lane;
+                if (e < nv) st_stream(dst + e, v[j]);
+            }
+        }
+    }
 }
 
 // Fallback mover for row classes whose size is not a multiple of 16 B (small non-Atari

@@ -7,6 +7,7 @@
 #include "gather_kernels.cuh"
 #include "td_kernels.cuh"
 #include "tree_kernels.cuh"
+#include "update_kernels.cuh"
 
 using namespace perb;
 
@@ -41,6 +42,7 @@ struct per_buffer_s {
     int64_t td_scratch_cap;  // rows
     int64_t len, cursor;
     int sm_count;
+    GatherTune tune;
     u64 *status() const { return scal; }
     double *max_prio() const { return reinterpret_cast<double *>(scal + 1); }
     float *td_red() const { return reinterpret_cast<float *>(scal + 2); }
@@ -83,37 +85,45 @@ int grid_for(int64_t n, int threads, int sm_count) {
 int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s) {
     TdArgs none;
     memset(&none, 0, sizeof none);
-    if (a.n <= UPD_BLOCK_MAX_ITEMS) {
-        int T = (int)round_up(a.n > 0 ? a.n : 1, 32);
-        if (T < 128) T = 128;
-        if (T > UPD_BLOCK_THREADS) T = UPD_BLOCK_THREADS;
-        k_update_block<<<1, T, 0, s>>>(a, td ? *td : none, td ? 1 : 0, skip_update);
-        PER_CUDA(cudaGetLastError());
+    if (a.n <= UPD_CLUSTER_MAX_ITEMS) {
+        // one launch: a cluster of CTAs, 64 items (8 lanes each) per CTA and round
+        int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));
+        if (ncta < 1) ncta = 1;
+        if (ncta > UPD_MAX_CTAS) ncta = UPD_MAX_CTAS;
+        if (skip_update) ncta = 1;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3(ncta);
+        cfg.blockDim = dim3(UPD_THREADS);
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = ncta;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        PER_CUDA(cudaLaunchKernelEx(&cfg, k_update_cluster, a, td ? *td : none, td ? 1 : 0, skip_update));
         return PER_OK;
     }
-    if (td) return fail(PER_ERR_ARG, "internal: fused TD needs the one-CTA update form");
+    if (td) return fail(PER_ERR_ARG, "internal: fused TD needs the one-launch update form");
     const int g = grid_for(a.n, 256, sm_count);
     if (a.stamps) k_upd_stamp<<<g, 256, 0, s>>>(a);
     k_upd_leaf<<<g, 256, 0, s>>>(a);
     const int L = a.t.L;
     const int top = L < TOP_LEVELS ? L : TOP_LEVELS;
-    int d_dense = ceil_log2(a.n) + 2;  // below this depth a dense rebuild touches fewer nodes than n sparse lifts
-    if (d_dense > L) d_dense = L;
-    if (d_dense < top) d_dense = top;
-    int done = 0;
-    while (L - done > d_dense) {
-        int sl = L - done - d_dense;
-        if (sl > 3) sl = 3;
-        k_upd_sparse<<<g, 256, 0, s>>>(a, done, sl);
-        done += sl;
-    }
+    int want = ceil_log2(a.n) + 2;  // below this depth a dense rebuild touches fewer nodes than n sparse lifts
+    if (want > L) want = L;
+    if (want < top) want = top;
+    const int d_dense = L - LIFT * ((L - want) / LIFT);  // sparse rounds lift LIFT generations each
+    for (int done = 0; L - done > d_dense; done += LIFT) k_upd_sparse<<<g, 256, 0, s>>>(a, done);
     int d = d_dense;
     while (d > top) {
         int k = d - top < TOP_LEVELS ? d - top : TOP_LEVELS;
         k_dense_mid<<<(unsigned)(int64_t(1) << (d - k)), 256, 0, s>>>(a.t, d, k);
         d -= k;
     }
-    k_dense_top<<<1, 1024, 0, s>>>(a.t);
+    k_dense_top<<<1, 1024, 0, s>>>(a.t, top);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
@@ -284,14 +294,15 @@ int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, in
     TRY_ALLOC(b->act, sizeof(int64_t) * ring_size);
     TRY_ALLOC(b->rew, sizeof(float) * ring_size);
     TRY_ALLOC(b->done, sizeof(float) * ring_size);
-    b->td_scratch_cap = UPD_BLOCK_MAX_ITEMS;
+    b->td_scratch_cap = UPD_CLUSTER_MAX_ITEMS;
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
     PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 4, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
-    PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM));
+    PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
+    b->tune = GatherTune();
     PER_CUDA(cudaStreamSynchronize(0));
     *out = b;
     return PER_OK;
@@ -413,6 +424,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     int64_t rb[3] = {b->obs_bytes, b->obs_bytes, b->extra_bytes};
     int64_t ss[3] = {b->obs_stride, b->obs_stride, b->extra_stride};
     GatherArgs slow = a;
+    const GatherTune &tn = b->tune;
     int per_query = 0;
     bool any_slow = false;
     for (int c = 0; c < 3; ++c) {
@@ -428,7 +440,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
         const bool wanted = rc.dst && rb[c] > 0;
         const bool tma_ok = wanted && (rb[c] % 16 == 0) && (((uintptr_t)rc.dst) % 16 == 0);
         if (tma_ok) {
-            rc.pieces = (int)((rb[c] + PIECE_BYTES - 1) / PIECE_BYTES);
+            rc.pieces = (int)((rb[c] + tn.piece - 1) / tn.piece);
             per_query += rc.pieces;
             a.rc[c] = rc;
             slow.rc[c] = off;
@@ -444,13 +456,42 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.act = b->act; a.rew = b->rew; a.done = b->done;
     a.out_act = d_out_act; a.out_rew = d_out_rew; a.out_done = d_out_done;
     a.status = slow.status = b->status();
-    int64_t items = batch * per_query;
-    int64_t grid = (items + GATHER_WARPS - 1) / GATHER_WARPS;
-    if (grid > b->sm_count) grid = b->sm_count;  // persistent: one CTA per SM
-    if (grid < 1) grid = 1;
-    k_gather_tma<<<(unsigned)grid, GATHER_WARPS * 32, per_query ? GATHER_SMEM : 0, s>>>(a, per_query);
+    a.piece = slow.piece = tn.piece;
+    a.stages = slow.stages = tn.stages;
+    const int64_t items = batch * per_query;
+    if (tn.mode == 0) {
+        int64_t grid = (items + tn.warps - 1) / tn.warps;
+        if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;  // persistent CTAs
+        if (grid < 1) grid = 1;
+        const size_t smem = per_query ? (size_t)round_up(tn.warps * tn.stages * 8, 128) + (size_t)tn.warps * tn.stages * tn.piece : 0;
+        k_gather_tma<<<(unsigned)grid, tn.warps * 32, smem, s>>>(a, per_query);
+    } else {
+        int64_t grid = (items + 7) / 8;
+        if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;
+        if (grid < 1) grid = 1;
+        k_gather_ldg<<<(unsigned)grid, 256, 0, s>>>(a, per_query);
+    }
     if (any_slow) k_gather_bytes<<<grid_for(batch * 3 * 32, 256, b->sm_count), 256, 0, s>>>(slow);
     PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int per_tune(per_buffer *b, const char *key, int64_t value) {
+    if (!b || !key) return fail(PER_ERR_ARG, "per_tune: bad argument");
+    GatherTune t = b->tune;
+    if (!strcmp(key, "gather_mode")) t.mode = (int)value;
+    else if (!strcmp(key, "gather_warps")) t.warps = (int)value;
+    else if (!strcmp(key, "gather_stages")) t.stages = (int)value;
+    else if (!strcmp(key, "gather_piece")) t.piece = (int)value;
+    else if (!strcmp(key, "gather_ctas_per_sm")) t.ctas_per_sm = (int)value;
+    else return fail(PER_ERR_ARG, "per_tune: unknown key %s", key);
+    const int64_t smem = round_up(t.warps * t.stages * 8, 128) + (int64_t)t.warps * t.stages * t.piece;
+    if (t.mode < 0 || t.mode > 1 || t.warps < 1 || t.warps > GATHER_MAX_WARPS || t.stages < 2 || t.stages > 64 ||
+        t.piece < 16 || t.piece % 16 || t.ctas_per_sm < 1 || t.ctas_per_sm > 8 || smem > GATHER_SMEM_MAX ||
+        (smem + 1024) * t.ctas_per_sm > 228 * 1024)
+        return fail(PER_ERR_ARG, "per_tune: %s=%lld gives an invalid launch shape (smem %lld B x %d CTAs/SM)", key,
+                    (long long)value, (long long)smem, t.ctas_per_sm);
+    b->tune = t;
     return PER_OK;
 }
 
@@ -523,7 +564,7 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
     t.out_prio = d_out_prio ? d_out_prio : b->td_scratch + b->td_scratch_cap;
     t.out_loss = d_out_loss;
     t.red = b->td_red();
-    if (batch <= UPD_BLOCK_MAX_ITEMS) {
+    if (batch <= UPD_CLUSTER_MAX_ITEMS) {
         if (d_idx) return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, &t, s);
         UpdArgs a;
         memset(&a, 0, sizeof a);

@@ -1,0 +1,356 @@
+// update_kernels.cuh — K1 (+K5 prologue): batched leaf update with the reference's
+// sequential semantics and re-reduction of every touched ancestor (memory.py:76-87, 300-320).
+//
+// What bounds it (profiles/r01_notes.md): a batch of 512 leaves dirties ~500 distinct 128-B
+// lines per generation in each tree.  One SM retires about one 32-B sector per cycle for
+// scattered accesses, so the first, single-CTA version (every thread re-reading its own 16
+// nodes with 8 LDG.128 and writing 15 STG.64 per tree and round) needed ~95 k sector
+// operations on one SM = 55 us.  This version
+//   * spreads the batch over a thread-block CLUSTER of up to 8 CTAs (8 SMs) that meet at
+//     hardware cluster barriers between phases, and
+//   * lets 8 adjacent lanes share one item: each lane loads 16 B of the item's 128-B line
+//     (one wavefront per 4 items instead of 8 per item) and the 4 generations are reduced
+//     with shuffles, left operand always the lower-numbered child.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "td_kernels.cuh"
+
+namespace perb {
+namespace cg = cooperative_groups;
+
+constexpr int TOP_LEVELS = 10;            // the dense top rebuild covers at most this many generations
+constexpr int TOP_NODES = 1 << TOP_LEVELS;
+constexpr int LIFT = 4;                    // generations recomputed per sparse round (16 nodes = one 128-B line)
+constexpr int LIFT_LANES = 8;              // lanes that share one item in a sparse round
+constexpr int UPD_CLUSTER_MAX_ITEMS = 2048;  // largest batch the one-launch (cluster) form takes
+constexpr int UPD_THREADS = 512;
+constexpr int UPD_MAX_CTAS = 8;            // portable cluster size
+
+enum LeafSrc : int {
+    LEAF_GIVEN = 0,     // float64 leaves supplied by the caller
+    LEAF_PRIO_F64 = 1,  // float64 priorities, leaf = p ** alpha
+    LEAF_PRIO_F32 = 2,  // float32 priorities, leaf = double(p) ** alpha
+    LEAF_MAXPRIO = 3,   // leaf = max_priority ** alpha  (memory.py:239-240)
+};
+
+struct TreeRef {
+    double *sum;  // may be null (stand-alone MinSegmentTree)
+    double *mnn;  // may be null (stand-alone SumSegmentTree)
+    int64_t cap;
+    int L;  // log2(cap)
+};
+
+struct UpdArgs {
+    TreeRef t;
+    const int64_t *idx;       // null: ring mode, idx_j = (ring_start + j) % ring_size
+    int64_t ring_start, ring_size;
+    const void *src;          // leaves / priorities, see src_kind
+    int src_kind;
+    double alpha;
+    int64_t n;
+    int64_t len_limit;        // valid indices are [0, len_limit)
+    u64 *stamps;              // cap entries; null when indices are known distinct
+    u64 epoch_hi;             // call counter << 32
+    u64 *status;
+    double *max_prio;         // device scalar `_max_priority`; may be null (stand-alone trees)
+    double batch_max;         // LEAF_GIVEN: raw-priority maximum of the batch (<=0: none)
+};
+
+// Depth at which the dense top rebuild starts: the largest value <= TOP_LEVELS that leaves
+// a multiple of LIFT generations below it.
+__host__ __device__ __forceinline__ int top_depth(int L) {
+    if (L <= TOP_LEVELS) return L;
+    const int r = (L - TOP_LEVELS) % LIFT;
+    return r == 0 ? TOP_LEVELS : TOP_LEVELS - (LIFT - r);
+}
+
+__device__ __forceinline__ int64_t upd_index(const UpdArgs &a, int64_t j) {
+    if (a.idx) return a.idx[j];
+    int64_t k = a.ring_start + j;
+    return k >= a.ring_size ? k - a.ring_size : k;
+}
+
+// Raw priority (for the running max) and leaf value of item j.  Returns false for an
+// item the reference would have rejected (memory.py:315-316).  One pow() call site.
+__device__ __forceinline__ bool upd_item(const UpdArgs &a, int64_t j, int64_t &k, double &leaf, double &raw) {
+    k = upd_index(a, j);
+    raw = 0.0;
+    unsigned bad = (k < 0 || k >= a.len_limit) ? PER_STATUS_BAD_INDEX : 0u;
+    double base = 1.0;
+    bool powered = true, checked = false;
+    if (a.src_kind == LEAF_GIVEN) {
+        base = static_cast<const double *>(a.src)[j];
+        powered = false;
+    } else if (a.src_kind == LEAF_PRIO_F64) {
+        base = raw = static_cast<const double *>(a.src)[j];
+        checked = true;
+    } else if (a.src_kind == LEAF_PRIO_F32) {
+        base = raw = (double)static_cast<const float *>(a.src)[j];
+        checked = true;
+    } else {
+        base = ldcg_f64(a.max_prio);
+    }
+    if (checked && !(raw > 0.0)) bad |= PER_STATUS_BAD_PRIORITY;
+    if (bad) {
+        atomicOr(a.status, (u64)bad);
+        return false;
+    }
+    leaf = powered ? pow_alpha(base, a.alpha) : base;
+    return true;
+}
+
+// One sparse round for one item, executed by LIFT_LANES = 8 adjacent lanes (sub = lane & 7):
+// recompute the 4 generations of ancestors above the 16 contiguous nodes (g<<4)..(g<<4)+15.
+// Every lane of the warp must call this (shuffles); `valid` guards the memory traffic.
+template <bool IS_SUM>
+__device__ __forceinline__ void lift8(double *v, int64_t g, int sub, bool valid) {
+    double x = 0.0, y = 0.0;
+    if (valid) {
+        double2 c = ldcg_f64x2(v + (g << 4) + 2 * sub);
+        x = c.x;
+        y = c.y;
+    }
+    double r = IS_SUM ? __dadd_rn(x, y) : fmin(x, y);  // generation 1: node (g<<3)+sub
+    if (valid) v[(g << 3) + sub] = r;
+#pragma unroll
+    for (int s = 1; s <= 3; ++s) {  // generations 2..4: lanes with the low s bits clear own a node
+        const double other = __shfl_xor_sync(0xffffffffu, r, 1 << (s - 1));
+        r = IS_SUM ? __dadd_rn(r, other) : fmin(r, other);  // on owning lanes r is the LEFT child
+        if (valid && (sub & ((1 << s) - 1)) == 0) v[(g << (3 - s)) + (sub >> s)] = r;
+    }
+}
+
+__device__ __forceinline__ void lift8_both(const TreeRef &t, int64_t g, int sub, bool valid) {
+    if (t.sum) lift8<true>(t.sum, g, sub, valid);
+    if (t.mnn) lift8<false>(t.mnn, g, sub, valid);
+}
+
+// Dense rebuild, by one CTA, of the k generations above the 2^k contiguous nodes that
+// descend from node `a` (k <= TOP_LEVELS).  smem: 2 * 2^k doubles per tree, addressed as a
+// relative heap (generation j, position t at s[(1<<j) + t]).
+__device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+    const int n = 1 << k;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        if (t.sum) s_sum[n + i] = ldcg_f64(t.sum + (a << k) + i);
+        if (t.mnn) s_min[n + i] = ldcg_f64(t.mnn + (a << k) + i);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int j = k - 1; j >= 0; --j) {
+        const int m = 1 << j;
+        for (int i = threadIdx.x; i < m; i += blockDim.x) {
+            if (t.sum) {
+                double2 c = *reinterpret_cast<double2 *>(s_sum + 2 * (m + i));
+                double x = __dadd_rn(c.x, c.y);
+                s_sum[m + i] = x;
+                t.sum[(a << j) + i] = x;
+            }
+            if (t.mnn) {
+                double2 c = *reinterpret_cast<double2 *>(s_min + 2 * (m + i));
+                double x = fmin(c.x, c.y);
+                s_min[m + i] = x;
+                t.mnn[(a << j) + i] = x;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// One-launch form (n <= UPD_CLUSTER_MAX_ITEMS): a cluster of 1..8 CTAs.
+//   phase 0  (optional, fused_td) K5: TD error -> priority for the batch (utils.py:71-80);
+//            every CTA evaluates the whole batch (the max is batch-wide) and publishes
+//            the priorities of its own slice
+//   phase 1  last-write-wins arbitration: atomicMax(stamp[idx], epoch|j)    (memory.py:314-318)
+//   phase 2  winners write the leaves of both trees; max -> _max_priority   (memory.py:320)
+//   phase 3  sparse rounds (lift8) down to depth top_depth(L), cluster barrier between rounds
+//   phase 4  CTA 0: dense rebuild of depths top_depth(L)..0 in shared memory
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, TdArgs td, int fused_td, int skip_update) {
+    __shared__ __align__(16) double s_sum[2 * TOP_NODES];  // phases 1-2: leaf values of this CTA's slice
+    __shared__ __align__(16) double s_min[2 * TOP_NODES];  // phase 0: |td| of the whole batch (float)
+    __shared__ int s_k[UPD_CLUSTER_MAX_ITEMS];             // leaf index of each surviving item of the slice, else -1
+    __shared__ double s_red[34];
+
+    cg::cluster_group cl = cg::this_cluster();
+    const int ncta = (int)cl.num_blocks();
+    const int rank = (int)cl.block_rank();
+    const int T = blockDim.x, tid = threadIdx.x;
+    const int nwarp = (T + 31) >> 5;
+    const int n = (int)a.n;
+    const int per = (n + ncta - 1) / ncta;  // slice of this CTA: items [lo, hi)
+    const int lo = rank * per < n ? rank * per : n;
+    const int hi = lo + per < n ? lo + per : n;
+    const int cnt = hi - lo;
+
+    if (fused_td) {
+        float *f_red = reinterpret_cast<float *>(s_red);  // [0..31] warp partials, [32] result
+        float *s_td = reinterpret_cast<float *>(s_min);
+        const int nb = (int)td.batch;
+        float mx = 0.0f;
+#pragma unroll 1
+        for (int j = tid; j < nb; j += T) {
+            float x = td_row(td, j);
+            s_td[j] = x;
+            mx = fmaxf(mx, x);
+        }
+        mx = warp_max_f32(mx);
+        if ((tid & 31) == 0) f_red[tid >> 5] = mx;
+        __syncthreads();
+        if (tid < 32) {
+            float m = tid < nwarp ? f_red[tid] : 0.0f;
+            m = warp_max_f32(m);
+            if (tid == 0) f_red[32] = m;
+        }
+        __syncthreads();
+        mx = f_red[32];
+        const int plo = skip_update ? (rank == 0 ? 0 : nb) : lo, phi = skip_update ? nb : hi;
+#pragma unroll 1
+        for (int j = plo + tid; j < phi; j += T) {
+            const float x = s_td[j];
+            td.out_prio[j] = td_prio(x, mx);
+            if (td.out_td) td.out_td[j] = x;
+        }
+        if (td.out_loss && rank == 0) {
+            float acc = 0.0f;
+#pragma unroll 1
+            for (int j = tid; j < nb; j += T) acc += __fmul_rn(td_huber(s_td[j]), td.w[j]);
+            acc = warp_sum_f32(acc);
+            __syncthreads();
+            if ((tid & 31) == 0) f_red[tid >> 5] = acc;
+            __syncthreads();
+            if (tid < 32) {
+                float m = tid < nwarp ? f_red[tid] : 0.0f;
+                m = warp_sum_f32(m);
+                if (tid == 0) td.out_loss[0] = m / (float)nb;  // .mean(), utils.py:80
+            }
+        }
+        if (skip_update) return;
+        __syncthreads();  // this CTA's out_prio slice is read back below; s_red is reused
+    }
+
+    // phase 1
+    double *s_leaf = s_sum;
+    double my_max = 0.0;
+#pragma unroll 1
+    for (int i = tid; i < cnt; i += T) {
+        int64_t k;
+        double leaf, raw;
+        int kk = -1;
+        if (upd_item(a, lo + i, k, leaf, raw)) {
+            kk = (int)k;
+            s_leaf[i] = leaf;
+            my_max = fmax(my_max, raw);
+            if (a.stamps) atomicMax(a.stamps + k, a.epoch_hi | (u64)(lo + i));
+        }
+        s_k[i] = kk;
+    }
+    if (a.stamps) {
+        cl.sync();
+#pragma unroll 1
+        for (int i = tid; i < cnt; i += T) {
+            const int kk = s_k[i];
+            if (kk >= 0 && __ldcg(a.stamps + kk) != (a.epoch_hi | (u64)(lo + i))) s_k[i] = -1;  // a later item wins
+        }
+    }
+    // phase 2 (each thread revisits the items it handled itself)
+#pragma unroll 1
+    for (int i = tid; i < cnt; i += T) {
+        const int kk = s_k[i];
+        if (kk >= 0) {
+            const double leaf = s_leaf[i];
+            if (a.t.sum) a.t.sum[a.t.cap + kk] = leaf;
+            if (a.t.mnn) a.t.mnn[a.t.cap + kk] = leaf;
+        }
+    }
+    if (a.max_prio) {
+        if (a.src_kind == LEAF_GIVEN) my_max = (tid == 0 && rank == 0) ? a.batch_max : 0.0;
+        for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, (tid & 31) ^ o));
+        if ((tid & 31) == 0) s_red[tid >> 5] = my_max;
+        __syncthreads();
+        if (tid < 32) {
+            double m = tid < nwarp ? s_red[tid] : 0.0;
+            for (int o = 16; o; o >>= 1) m = fmax(m, shfl_f64(m, tid ^ o));
+            if (tid == 0 && m > 0.0) atomic_max_pos_f64(a.max_prio, m);
+        }
+    }
+    cl.sync();
+    // phase 3
+    const int top = top_depth(a.t.L);
+    const int sub = tid & (LIFT_LANES - 1);
+#pragma unroll 1
+    for (int done = 0; a.t.L - done > top; done += LIFT) {
+#pragma unroll 1
+        for (int base = 0; base < cnt; base += T / LIFT_LANES) {
+            const int i = base + tid / LIFT_LANES;
+            const int kk = i < cnt ? s_k[i] : -1;
+            lift8_both(a.t, (a.t.cap + (int64_t)(kk < 0 ? 0 : kk)) >> (done + LIFT), sub, kk >= 0);
+        }
+        cl.sync();
+    }
+    // phase 4
+    if (rank == 0) dense_lift_block(a.t, 1, top, s_sum, s_min);
+}
+
+// ---------------------------------------------------------------------------------------
+// Multi-launch form (any n): the same phases as separate grid-wide launches.
+// ---------------------------------------------------------------------------------------
+__global__ void k_upd_stamp(UpdArgs a) {
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < a.n; j += (int64_t)gridDim.x * blockDim.x) {
+        int64_t k = upd_index(a, j);
+        if (k >= 0 && k < a.len_limit) atomicMax(a.stamps + k, a.epoch_hi | (u64)j);
+    }
+}
+
+__device__ __forceinline__ bool upd_is_winner(const UpdArgs &a, int64_t j, int64_t k) {
+    return !a.stamps || __ldcg(a.stamps + k) == (a.epoch_hi | (u64)j);
+}
+
+__global__ void k_upd_leaf(UpdArgs a) {
+    double my_max = 0.0;
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < a.n; j += (int64_t)gridDim.x * blockDim.x) {
+        int64_t k;
+        double leaf, raw;
+        if (!upd_item(a, j, k, leaf, raw)) continue;
+        my_max = fmax(my_max, raw);
+        if (!upd_is_winner(a, j, k)) continue;
+        if (a.t.sum) a.t.sum[a.t.cap + k] = leaf;
+        if (a.t.mnn) a.t.mnn[a.t.cap + k] = leaf;
+    }
+    if (a.max_prio) {
+        if (a.src_kind == LEAF_GIVEN) my_max = (blockIdx.x == 0 && threadIdx.x == 0) ? a.batch_max : 0.0;
+        for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, (threadIdx.x & 31) ^ o));
+        if ((threadIdx.x & 31) == 0 && my_max > 0.0) atomic_max_pos_f64(a.max_prio, my_max);
+    }
+}
+
+// One sparse round above depth (L - done) for every valid item, 8 lanes per item.
+__global__ void __launch_bounds__(256) k_upd_sparse(UpdArgs a, int done) {
+    const int sub = threadIdx.x & (LIFT_LANES - 1);
+    const int64_t group = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / LIFT_LANES;
+    const int64_t groups = ((int64_t)gridDim.x * blockDim.x) / LIFT_LANES;
+    const int64_t rounds = (a.n + groups - 1) / groups;  // same trip count for every lane of a warp
+    for (int64_t r = 0; r < rounds; ++r) {
+        const int64_t j = r * groups + group;
+        int64_t k = j < a.n ? upd_index(a, j) : -1;
+        const bool valid = k >= 0 && k < a.len_limit;
+        lift8_both(a.t, (a.t.cap + (valid ? k : 0)) >> (done + LIFT), sub, valid);
+    }
+}
+
+// CTA b rebuilds the k generations above the 2^k nodes below node (2^(d-k) + b).
+__global__ void __launch_bounds__(256) k_dense_mid(TreeRef t, int d, int k) {
+    __shared__ __align__(16) double s_sum[2 * TOP_NODES];
+    __shared__ __align__(16) double s_min[2 * TOP_NODES];
+    dense_lift_block(t, (int64_t(1) << (d - k)) + blockIdx.x, k, s_sum, s_min);
+}
+
+__global__ void __launch_bounds__(1024) k_dense_top(TreeRef t, int top) {
+    __shared__ __align__(16) double s_sum[2 * TOP_NODES];
+    __shared__ __align__(16) double s_min[2 * TOP_NODES];
+    dense_lift_block(t, 1, top, s_sum, s_min);
+}
+
+}  // namespace perb

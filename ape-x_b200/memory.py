@@ -267,6 +267,7 @@ class ReplayBuffer(object):
         self._extra_dtype = None
         self._storage = _StorageView(self)
         self._host = _HostStage(self._device)
+        self._max_priority_stale = False
         if not hasattr(self, "_alpha"):
             self._alpha = self._alpha_default
         self._max_priority = 1.0
@@ -366,13 +367,16 @@ class ReplayBuffer(object):
             self._h = h
         if _count:
             self._flush()
-        _n.check(_n.lib.per_add_batch(self._h, _n.ptr(obs), _n.ptr(next_obs), _n.ptr(actions), _n.ptr(rewards),
-                                      _n.ptr(dones), _n.ptr(extra), _n.ptr(priorities), _n.ptr(leaves),
-                                      float(batch_max), n, _n.stream_ptr()))
+        cut = lambda t, lo, hi: None if t is None else t[lo:hi].contiguous()
+        for lo in range(0, n, self._ring):  # one native call never laps the ring
+            hi = min(n, lo + self._ring)
+            parts = [cut(t, lo, hi) for t in (obs, next_obs, actions, rewards, dones, extra, priorities, leaves)]
+            _n.check(_n.lib.per_add_batch(self._h, *[_n.ptr(t) for t in parts], float(batch_max), hi - lo,
+                                          _n.stream_ptr()))
         if _count:
             self._cursor = (self._cursor + n) % self._ring
             self._len = min(self._ring, self._len + n)
-            self._max_priority_stale = priorities is not None
+            self._max_priority_stale = self._max_priority_stale or priorities is not None
         assert _n.lib.per_len(self._h) == self._len and _n.lib.per_cursor(self._h) == self._cursor
 
     # -- gather -------------------------------------------------------------------------------
@@ -520,8 +524,9 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         assert bool(((idx >= 0) & (idx < len(self))).all())
         leaves = _pow_alpha_exact(pr, self._alpha)
         bmax = float(pr.max())
-        _n.check(_n.lib.per_update_leaves(self._h, _n.ptr(self._host.up("upd_idx", idx)),
-                                          _n.ptr(self._host.up("upd_leaf", leaves)), bmax, idx.size, _n.stream_ptr()))
+        d_idx = self._host.up("upd_idx", idx)  # keep both alive until the launch is enqueued
+        d_leaf = self._host.up("upd_leaf", leaves)
+        _n.check(_n.lib.per_update_leaves(self._h, _n.ptr(d_idx), _n.ptr(d_leaf), bmax, idx.size, _n.stream_ptr()))
         self._max_priority = max(self._max_priority, bmax)
 
     def update_priorities_device(self, idx, priorities):

@@ -55,6 +55,7 @@ SIGNATURES = {
     "per_pow_alpha_host": (C.c_int, [_p, _f64, _p, _i64]),
     "per_td_priority_update": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, C.c_float, _p, _i64, _p, _p, _p, _p]),
     "per_tree_read": (C.c_int, [_p, C.c_int, _p, _p]),
+    "per_tune": (C.c_int, [_p, C.c_char_p, _i64]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

