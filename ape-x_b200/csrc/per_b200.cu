@@ -590,4 +590,66 @@ int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
     return PER_OK;
 }
 
+// ------------------------------------------------------------------------------ no-allocation entry
+// seg_set_noalloc: the batched tree write of seg_set for callers that may not allocate device
+// memory.  seg_set keeps its last-write-wins arbitration stamps (8 bytes per leaf) in memory
+// that seg_create obtained with cudaMalloc; here the stamps live in the file-scope array
+// below, which every GPU that loads this library carries from module load until the process
+// exits (8 MiB + 256 B).  Host code must not pass `g_noalloc_scratch` itself to a kernel (in
+// host code that name is only a stand-in for the symbol): the device address is looked up
+// once per device with cudaGetSymbolAddress, with that device current, and cached.
+#define SEG_NOALLOC_HEADER_WORDS 32  /* 256 B: word 0 is the fallback status word */
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[SEG_NOALLOC_HEADER_WORDS + SEG_NOALLOC_MAX_CAPACITY];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct NoallocDevice {
+    u64 *base = nullptr;  // device address of g_noalloc_scratch on this device
+    u64 epoch = 0;        // call counter; a stamp of an earlier call can never win a later one
+    int sm_count = 0;
+};
+NoallocDevice g_noalloc_dev[NOALLOC_MAX_DEVICES];
+}  // namespace
+
+int seg_set_noalloc(int device, double *d_sum_nodes, double *d_min_nodes, int64_t capacity, const int64_t *d_idx,
+                    const double *d_val, int64_t n, uint64_t *d_status, void *stream) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(PER_ERR_ARG, "seg_set_noalloc: bad device %d", device);
+    if ((!d_sum_nodes && !d_min_nodes) || n < 0 || (n && (!d_idx || !d_val)))
+        return fail(PER_ERR_ARG, "seg_set_noalloc: bad argument");
+    if (!is_pow2(capacity)) return fail(PER_ERR_ASSERT, "capacity must be positive and a power of 2.");
+    if (capacity > SEG_NOALLOC_MAX_CAPACITY)
+        return fail(PER_ERR_ARG,
+                    "seg_set_noalloc: capacity %lld exceeds the built-in scratch (SEG_NOALLOC_MAX_CAPACITY = %lld leaves); "
+                    "use seg_create/seg_set for larger trees",
+                    (long long)capacity, (long long)SEG_NOALLOC_MAX_CAPACITY);
+    if (n >= (int64_t(1) << 32)) return fail(PER_ERR_ARG, "seg_set_noalloc: n too large");
+    if (n == 0) return PER_OK;
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "seg_set_noalloc: cannot select device %d", device);
+    cudaStream_t s = (cudaStream_t)stream;
+    NoallocDevice &nd = g_noalloc_dev[device];
+    if (!nd.base) {  // first call on this device: resolve the symbol while the device is current
+        void *p = nullptr;
+        PER_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        PER_CUDA(cudaDeviceGetAttribute(&nd.sm_count, cudaDevAttrMultiProcessorCount, device));
+        nd.base = static_cast<u64 *>(p);
+    }
+    UpdArgs a;
+    memset(&a, 0, sizeof a);
+    a.t.sum = d_sum_nodes;
+    a.t.mnn = d_min_nodes;
+    a.t.cap = capacity;
+    a.t.L = ilog2_exact(capacity);
+    a.idx = d_idx;
+    a.src = d_val;
+    a.src_kind = LEAF_GIVEN;
+    a.alpha = 1.0;
+    a.n = n;
+    a.len_limit = capacity;
+    a.stamps = nd.base + SEG_NOALLOC_HEADER_WORDS;
+    a.epoch_hi = next_epoch(nd.epoch, a.stamps, SEG_NOALLOC_MAX_CAPACITY, s);  // clears the stamps only on 2^32 wrap
+    a.status = d_status ? reinterpret_cast<u64 *>(d_status) : nd.base;
+    return run_update(a, nullptr, 0, nd.sm_count, s);
+}
+
 }  // extern "C"

@@ -82,6 +82,38 @@ int64_t seg_capacity(const seg_tree *t);
 /* Reads and clears the status word.  Synchronises `stream`. */
 int seg_status(seg_tree *t, int64_t *h_out, void *stream);
 
+/* Batched tree write for callers that cannot allocate device memory.  (No counterpart in
+ * the reference, which has no device memory at all.)
+ *
+ * seg_set needs a handle from seg_create, and seg_create calls cudaMalloc for the node array
+ * and for 8 bytes of arbitration stamps per leaf.  Some callers must not do that: a process
+ * whose framework has already claimed the whole GPU for its own memory pool (a 2^21-row Atari
+ * ring leaves little of the 180 GB), or a latency-critical loop that cannot afford the
+ * device-wide synchronisation cudaMalloc/cudaFree imply.  This entry point allocates
+ * nothing — no cudaMalloc, cudaFree or allocating library call on any path.  The caller
+ * passes its own node arrays (heap layout of memory.py:36, 2*capacity float64 each, one of
+ * the two may be NULL; initialise them to 0.0 / +inf) and the stamps live in a static
+ * device array inside the library, SEG_NOALLOC_MAX_CAPACITY entries (8 MiB + 256 B on every
+ * GPU that loads the library, held until the process exits).
+ *
+ *  - Semantics are seg_set's: for j in 0..n-1 in order, node[capacity + d_idx[j]] = d_val[j]
+ *    in both trees, then every touched ancestor = op(left, right) (memory.py:76-87); a later
+ *    duplicate wins.  Out-of-range indices are skipped and PER_STATUS_BAD_INDEX is OR-ed into
+ *    *d_status (a caller-owned device word; may be NULL).
+ *  - capacity > SEG_NOALLOC_MAX_CAPACITY is rejected with PER_ERR_ARG and a message naming
+ *    the limit; use seg_create/seg_set there.
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress, with that device current) and caches it; make that first call
+ *    before any stream capture begins.
+ *  - All calls on a device share the one array, which keeps what the previous call wrote
+ *    (stamps carry a call counter, so stale entries never win; they are cleared only when
+ *    the counter wraps after 2^32 calls).  Two calls whose kernels overlap on the GPU
+ *    (different streams without ordering, or two host threads) race on it: order them. */
+#define SEG_NOALLOC_MAX_CAPACITY (1 << 20)
+int seg_set_noalloc(int device, double *d_sum_nodes, double *d_min_nodes, int64_t capacity,
+                    const int64_t *d_idx, const double *d_val, int64_t n, uint64_t *d_status,
+                    void *stream);
+
 /* ---------------------------------------------------------------- prioritized replay */
 
 /* PrioritizedReplayBuffer.__init__ (memory.py:209-233) + ReplayBuffer.__init__
