@@ -45,6 +45,8 @@ struct GatherArgs {
     u64 *status;
     int piece;   // bytes per piece
     int stages;  // TMA ring depth per warp
+    int64_t idx_base;  // sharded replay: global index of this shard's row 0
+    int skip_foreign;  // sharded replay: idx == -1 = another shard's row, skipped silently
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -100,11 +102,19 @@ __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, in
         ++c;
     }
     int64_t k = a.idx[q];
-    if (k < 0 || k >= a.n_rows) k = 0;  // flagged by the scalar pass below; keep the copy in bounds
+    const bool foreign = a.skip_foreign && k == -1;
+    k -= a.idx_base;
+    if (k < 0 || k >= a.n_rows) k = 0;  // flagged by the scalar pass; keep the copy in bounds
     const RowClass &rc = a.rc[c];
     int64_t off = (int64_t)r * a.piece;
     int64_t left = rc.row_bytes - off;
     Piece p;
+    if (foreign) {
+        p.src = nullptr;
+        p.dst = nullptr;
+        p.bytes = 0;
+        return p;
+    }
     p.src = rc.src + k * rc.src_stride + off;
     p.dst = rc.dst + q * rc.dst_stride + off;
     p.bytes = (uint32_t)(left < a.piece ? left : a.piece);
@@ -115,6 +125,8 @@ __device__ __forceinline__ void gather_scalars(const GatherArgs &a) {
     // scalar columns (action / reward / done): plain coalesced loads, all threads
     for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < a.batch; q += (int64_t)gridDim.x * blockDim.x) {
         int64_t k = a.idx[q];
+        if (a.skip_foreign && k == -1) continue;  // another shard's row
+        k -= a.idx_base;
         if (k < 0 || k >= a.n_rows) {
             atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
             k = 0;
@@ -148,15 +160,15 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
     // prologue: fill the ring
     for (int64_t i = 0; i < NS && i < mine; ++i) {
         Piece p = decode_piece(a, first + i * stride, per_query);
-        mbar_expect_tx(bar0 + 8u * (uint32_t)i, p.bytes);
-        bulk_g2s(buf0 + (uint32_t)i * (uint32_t)a.piece, p.src, p.bytes, bar0 + 8u * (uint32_t)i);
+        mbar_expect_tx(bar0 + 8u * (uint32_t)i, p.bytes);  // 0 bytes (skipped row): the phase completes at once
+        if (p.bytes) bulk_g2s(buf0 + (uint32_t)i * (uint32_t)a.piece, p.src, p.bytes, bar0 + 8u * (uint32_t)i);
     }
     int s = 0;
     uint32_t parity = 0;
     for (int64_t i = 0; i < mine; ++i) {
         Piece p = decode_piece(a, first + i * stride, per_query);
         mbar_wait(bar0 + 8u * s, parity);
-        bulk_s2g(p.dst, buf0 + (uint32_t)s * (uint32_t)a.piece, p.bytes);
+        if (p.bytes) bulk_s2g(p.dst, buf0 + (uint32_t)s * (uint32_t)a.piece, p.bytes);
         bulk_commit();
         // refill the stage whose store was committed one iteration ago
         if (i >= 1 && i - 1 + NS < mine) {
@@ -164,7 +176,7 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
             const int sp = s == 0 ? NS - 1 : s - 1;
             Piece n = decode_piece(a, first + (i - 1 + NS) * stride, per_query);
             mbar_expect_tx(bar0 + 8u * sp, n.bytes);
-            bulk_g2s(buf0 + (uint32_t)sp * (uint32_t)a.piece, n.src, n.bytes, bar0 + 8u * sp);
+            if (n.bytes) bulk_g2s(buf0 + (uint32_t)sp * (uint32_t)a.piece, n.src, n.bytes, bar0 + 8u * sp);
         }
         if (++s == NS) { s = 0; parity ^= 1u; }
     }
@@ -220,6 +232,8 @@ __global__ void k_gather_bytes(GatherArgs a) {
         const RowClass &rc = a.rc[w - q * 3];
         if (!rc.dst || rc.row_bytes == 0) continue;
         int64_t k = a.idx[q];
+        if (a.skip_foreign && k == -1) continue;
+        k -= a.idx_base;
         if (k < 0 || k >= a.n_rows) k = 0;
         const uint8_t *s = rc.src + k * rc.src_stride;
         uint8_t *d = rc.dst + q * rc.dst_stride;

@@ -43,6 +43,8 @@ struct per_buffer_s {
     int64_t len, cursor;
     int sm_count;
     GatherTune tune;
+    int shard_rank, n_shards;  // sharded replay: this buffer is slice shard_rank of n_shards (1: not sharded)
+    int64_t idx_base;          // shard_rank * tree capacity
     u64 *status() const { return scal; }
     double *max_prio() const { return reinterpret_cast<double *>(scal + 1); }
     float *td_red() const { return reinterpret_cast<float *>(scal + 2); }
@@ -90,7 +92,6 @@ int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cuda
         int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));
         if (ncta < 1) ncta = 1;
         if (ncta > UPD_MAX_CTAS) ncta = UPD_MAX_CTAS;
-        if (skip_update) ncta = 1;
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = dim3(ncta);
@@ -150,6 +151,7 @@ int read_status(u64 *d_status, int64_t *h_out, cudaStream_t s) {
 extern "C" {
 
 const char *per_last_error(void) { return err_slot().c_str(); }
+int per_destroy(per_buffer *b);
 int per_version(void) { return 100; }
 
 // ---------------------------------------------------------------------------------- trees
@@ -255,10 +257,11 @@ int seg_status(seg_tree *t, int64_t *h_out, void *stream) {
 }
 
 // ------------------------------------------------------------------------------ replay buffer
-int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, int64_t obs_bytes, int64_t extra_bytes) {
+static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t tree_capacity, double alpha, int64_t obs_bytes,
+                       int64_t extra_bytes, int rank, int n_shards) {
     if (!out) return fail(PER_ERR_ARG, "per_create: null out");
     if (!(alpha >= 0)) return fail(PER_ERR_ASSERT, "alpha >= 0");
-    if (ring_size <= 0 || obs_bytes < 0 || extra_bytes < 0) return fail(PER_ERR_ARG, "per_create: bad size");
+    if (ring_size < (n_shards > 1 ? 0 : 1) || obs_bytes < 0 || extra_bytes < 0) return fail(PER_ERR_ARG, "per_create: bad size");
     DeviceGuard g(device);
     if (!g.ok) return fail(PER_ERR_CUDA, "per_create: cannot select device %d", device);
     per_buffer *b = new per_buffer();
@@ -273,6 +276,10 @@ int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, in
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     int64_t cap = 1;
     while (cap < ring_size) cap *= 2;  // memory.py:227-229
+    if (tree_capacity > 0) cap = tree_capacity;
+    b->shard_rank = rank;
+    b->n_shards = n_shards;
+    b->idx_base = (int64_t)rank * cap;
     b->t.cap = cap;
     b->t.L = ilog2_exact(cap);
     int rc = alloc_tree(&b->t.sum, cap, 0.0, 0);
@@ -306,6 +313,25 @@ int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, in
     PER_CUDA(cudaStreamSynchronize(0));
     *out = b;
     return PER_OK;
+}
+
+int per_create(per_buffer **out, int device, int64_t ring_size, double alpha, int64_t obs_bytes, int64_t extra_bytes) {
+    return create_impl(out, device, ring_size, 0, alpha, obs_bytes, extra_bytes, 0, 1);
+}
+
+int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank, int n_shards, double alpha,
+                     int64_t obs_bytes, int64_t extra_bytes) {
+    if (n_shards < 1 || n_shards > 16 || (n_shards & (n_shards - 1)) || rank < 0 || rank >= n_shards)
+        return fail(PER_ERR_ARG, "per_create_shard: n_shards must be a power of two <= 16 and 0 <= rank < n_shards");
+    if (global_size < 2) return fail(PER_ERR_ARG, "per_create_shard: bad size");
+    int64_t cap_g = 1;
+    while (cap_g < global_size) cap_g *= 2;  // memory.py:227-229 on the whole replay
+    if (cap_g < n_shards) return fail(PER_ERR_ARG, "per_create_shard: fewer leaves than shards");
+    const int64_t cap_l = cap_g / n_shards;
+    int64_t ring_l = global_size - (int64_t)rank * cap_l;  // ring slots that fall into this slice
+    if (ring_l < 0) ring_l = 0;
+    if (ring_l > cap_l) ring_l = cap_l;
+    return create_impl(out, device, ring_l, cap_l, alpha, obs_bytes, extra_bytes, rank, n_shards);
 }
 
 int per_destroy(per_buffer *b) {
@@ -411,6 +437,45 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     return PER_OK;
 }
 
+int per_shard_record(per_buffer *b, int64_t global_len, double *d_out, void *stream) {
+    if (!b || !d_out || global_len < 0) return fail(PER_ERR_ARG, "per_shard_record: bad argument");
+    DeviceGuard g(b->device);
+    int64_t need_local = (global_len - 1) - b->idx_base;  // leaves of this slice inside the global prefix [0, len-1)
+    if (need_local < 0) need_local = 0;
+    if (need_local > b->t.cap) need_local = b->t.cap;
+    k_shard_record<<<1, 32, 0, (cudaStream_t)stream>>>(b->t.sum, b->t.mnn, b->t.cap, need_local, b->len, d_out);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch, double beta,
+                       int64_t global_len, int64_t *d_out_idx, double *d_out_w64, float *d_out_w32, void *stream) {
+    if (!b || batch <= 0 || !d_u || !d_out_idx || !d_records) return fail(PER_ERR_ARG, "per_sample_sharded: bad argument");
+    if (!(beta > 0)) return fail(PER_ERR_ASSERT, "beta > 0");
+    if (global_len < 2) return fail(PER_ERR_ASSERT, "sample needs at least 2 stored transitions");
+    DeviceGuard g(b->device);
+    SampleArgs a;
+    memset(&a, 0, sizeof a);
+    a.sum = b->t.sum;
+    a.mnn = b->t.mnn;
+    a.cap = b->t.cap;
+    a.L = b->t.L;
+    a.u = d_u;
+    a.batch = batch;
+    a.n_rows = global_len;
+    a.beta = beta;
+    a.out_idx = d_out_idx;
+    a.out_w64 = d_out_w64;
+    a.out_w32 = d_out_w32;
+    a.status = b->status();
+    a.recs = d_records;
+    a.n_shards = b->n_shards;
+    a.rank = b->shard_rank;
+    k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
 int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_obs, void *d_out_next, int64_t *d_out_act,
                float *d_out_rew, float *d_out_done, void *d_out_extra, void *stream) {
     if (!b || batch < 0 || (batch && !d_idx)) return fail(PER_ERR_ARG, "per_gather: bad argument");
@@ -456,6 +521,8 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.act = b->act; a.rew = b->rew; a.done = b->done;
     a.out_act = d_out_act; a.out_rew = d_out_rew; a.out_done = d_out_done;
     a.status = slow.status = b->status();
+    a.idx_base = slow.idx_base = b->idx_base;
+    a.skip_foreign = slow.skip_foreign = b->n_shards > 1;
     a.piece = slow.piece = tn.piece;
     a.stages = slow.stages = tn.stages;
     const int64_t items = batch * per_query;
@@ -511,6 +578,8 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.status = b->status();
     a.max_prio = b->max_prio();
     a.batch_max = batch_max;
+    a.idx_base = b->idx_base;
+    a.skip_foreign = b->n_shards > 1;
     return run_update(a, td, 0, b->sm_count, s);
 }
 

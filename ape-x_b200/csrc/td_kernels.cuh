@@ -37,6 +37,21 @@ __device__ __forceinline__ float td_row(const TdArgs &a, int64_t b) {
     return fabsf(__fsub_rn(y, q_a));
 }
 
+// Same, with the row of q_next already in shared memory (coalesced staging by the caller).
+__device__ __forceinline__ float td_row_from(const TdArgs &a, int64_t b, const float *qn) {
+    int best = 0;
+    float bv = qn[0];
+#pragma unroll 1
+    for (int i = 1; i < (int)a.nA; ++i) {
+        float x = qn[i];
+        if (x > bv) { bv = x; best = i; }
+    }
+    const float q_a = a.q[b * a.nA + a.act[b]];
+    const float boot = a.q_tgt[b * a.nA + best];
+    const float y = __fadd_rn(a.rew[b], __fmul_rn(__fmul_rn(a.gamma_n, boot), __fsub_rn(1.0f, a.done[b])));
+    return fabsf(__fsub_rn(y, q_a));
+}
+
 __device__ __forceinline__ float td_prio(float td, float mx) {  // utils.py:77
     return __fadd_rn(__fadd_rn(__fmul_rn(0.9f, mx), __fmul_rn(0.1f, td)), 1e-6f);
 }

@@ -22,45 +22,25 @@ namespace perb {
 // Range reductions with the reference's association (memory.py:39-52).
 // ---------------------------------------------------------------------------------------
 
-// Warp-cooperative  sum over leaves [0, need)  =  t1 + (t2 + (... + tk)) : the node walk
-// depends only on `need`, so lane s replays s integer steps, all loads go out together,
-// and the chain is folded innermost-first through shuffles.  Every lane returns the total.
+// Warp-cooperative  sum over leaves [0, need)  =  t1 + (t2 + (... + tk)).  Walking the
+// reference's recursion (memory.py:39-52) from the root with start = 0, a term is emitted for
+// every set bit b of `need`, most significant first: the aligned block of 2^b leaves that
+// starts where the higher bits of `need` end, i.e. node (cap >> b) + (need >> (b+1) << 1).
+// Lane b owns bit b, so all loads go out together; the chain is then folded innermost
+// (lowest bit) first.  Every lane returns the total.  Requires cap <= 2^31.
 __device__ __forceinline__ double warp_prefix_total(const double *v, int64_t cap, int64_t need) {
     const int lane = threadIdx.x & 31;
-    int64_t node = 1, width = cap, rem = need, tnode = 0;
-    bool emit = false, finished = false;
-#pragma unroll 1
-    for (int s = 0; s <= lane; ++s) {
-        emit = false;
-        if (finished) continue;
-        if (rem == width) {
-            emit = true;
-            tnode = node;
-            finished = true;
-        } else {
-            int64_t half = width >> 1;
-            if (rem <= half) {
-                node = 2 * node;
-            } else {
-                emit = true;
-                tnode = 2 * node;
-                node = 2 * node + 1;
-                rem -= half;
-            }
-            width = half;
-        }
-    }
-    double term = emit ? v[tnode] : 0.0;
-    unsigned mask = __ballot_sync(0xffffffffu, emit);
+    const bool emit = (need >> lane) & 1;
+    const double term = emit ? v[(cap >> lane) + ((need >> (lane + 1)) << 1)] : 0.0;
     double acc = 0.0;
     bool first = true;
-#pragma unroll 1
-    while (mask) {
-        int s = 31 - __clz(mask);
-        mask &= ~(1u << s);
-        double t = shfl_f64(term, s);
-        acc = first ? t : __dadd_rn(t, acc);
-        first = false;
+#pragma unroll
+    for (int b = 0; b < 32; ++b) {
+        const double t = shfl_f64(term, b);  // independent of acc: the shuffles pipeline
+        if ((need >> b) & 1) {
+            acc = first ? t : __dadd_rn(t, acc);
+            first = false;
+        }
     }
     return acc;
 }
@@ -135,13 +115,35 @@ struct SampleArgs {
     const double *u;       // uniforms (per_sample_indices) or masses (seg_find_prefixsum)
     int direct_mass;       // 1: `u` holds masses already
     int64_t batch;
-    int64_t n_rows;        // len(_storage)
+    int64_t n_rows;        // len(_storage)  (sharded: of the whole replay)
     double beta;
     int64_t *out_idx;
     double *out_w64;
     float *out_w32;
     u64 *status;
+    // Sharded replay: this tree is slice `rank` of a virtual tree of
+    // n_shards * cap leaves whose depth-log2(n_shards) nodes are the shard roots.
+    const double *recs;    // null: not sharded.  n_shards records {root_sum, root_min, boundary_partial, len}
+    int n_shards;          // power of two, <= 16
+    int rank;
 };
+
+constexpr int SHARD_REC = 4;  // doubles per shard record
+
+// One record per shard and sample call, all-gathered across ranks: the two roots, and the
+// shard-local part of the reference's  sum(0, len-1)  chain (memory.py:244): the prefix over
+// this shard's first `need_local` leaves when the global prefix ends inside this shard.
+__global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
+                               double *out) {
+    double partial = 0.0;
+    if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
+    if (threadIdx.x == 0) {
+        out[0] = sum[1];
+        out[1] = mnn[1];
+        out[2] = partial;
+        out[3] = (double)len_local;
+    }
+}
 
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     const int lane = threadIdx.x & 31;
@@ -149,14 +151,73 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     if (q >= a.batch) return;  // whole warp leaves together
 
     double mass;
-    const double root_sum = a.sum[1];
-    if (a.direct_mass) {
-        mass = a.u[q];
-        if (lane == 0 && !(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
+    double root_sum, root_min = 0.0;
+    int64_t idx_base = 0;
+    if (a.recs) {
+        // Top of the virtual tree, one node per lane: lanes N..2N-1 hold the shard roots,
+        // lanes 1..N-1 their pairwise sums built level by level like memory.py:82-87.
+        const int N = a.n_shards;
+        double top = (lane >= N && lane < 2 * N) ? a.recs[(lane - N) * SHARD_REC] : 0.0;
+        double mn = lane < N ? a.recs[lane * SHARD_REC + 1] : __longlong_as_double(0x7ff0000000000000LL);
+        for (int w = N >> 1; w >= 1; w >>= 1) {
+            const double l = shfl_f64(top, (2 * lane) & 31), r = shfl_f64(top, (2 * lane + 1) & 31);
+            if (lane >= w && lane < 2 * w) top = __dadd_rn(l, r);
+        }
+        for (int o = 16; o; o >>= 1) mn = fmin(mn, shfl_f64(mn, lane ^ o));
+        root_sum = shfl_f64(top, 1);
+        root_min = mn;
+        // p_total = sum over global leaves [0, need): shard-aligned blocks come from the top
+        // tree (one per set bit of need / cap), the rest from the owning shard's record.
+        const int64_t need = a.n_rows - 1;
+        const int64_t need_hi = need >> a.L;  // whole shards covered
+        const int64_t need_lo = need & (a.cap - 1);
+        double acc = 0.0;
+        bool first = true;
+        if (need_lo) {
+            acc = a.recs[need_hi * SHARD_REC + 2];
+            first = false;
+        }
+#pragma unroll 1
+        for (int b = 0; (int64_t(1) << b) <= need_hi; ++b) {
+            if ((need_hi >> b) & 1) {
+                const double t = shfl_f64(top, (int)((N >> b) + ((need_hi >> (b + 1)) << 1)));
+                acc = first ? t : __dadd_rn(t, acc);
+                first = false;
+            }
+        }
+        const double seg = __ddiv_rn(acc, (double)a.batch);
+        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));
+        // descent through the top tree
+        int node = 1;
+        while (node < N) {
+            const double lv = shfl_f64(top, 2 * node);
+            if (lv > mass) {
+                node = 2 * node;
+            } else {
+                mass = __dsub_rn(mass, lv);
+                node = 2 * node + 1;
+            }
+        }
+        if (node - N != a.rank) {  // another shard owns this stratum
+            if (lane == 0) {
+                a.out_idx[q] = -1;
+                if (a.out_w64) a.out_w64[q] = 0.0;
+                if (a.out_w32) a.out_w32[q] = 0.0f;
+            }
+            return;
+        }
+        idx_base = (int64_t)a.rank * a.cap;
     } else {
-        const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
-        const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
-        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
+        root_sum = a.sum[1];
+        if (a.direct_mass) {
+            mass = a.u[q];
+            if (lane == 0 && !(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
+        } else {
+            const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
+            const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
+            mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
+        }
+        if (a.mnn) root_min = a.mnn[1];
     }
 
     // lane -> (generation j in 1..5, pair qg): lane 0 -> 1, lanes 1-2 -> 2, 3-6 -> 3, 7-14 -> 4, 15-30 -> 5
@@ -186,12 +247,12 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         depth += s;
     }
     const int64_t k = node - a.cap;
-    if (lane == 0) a.out_idx[q] = k;
+    if (lane == 0) a.out_idx[q] = idx_base + k;
     if (a.mnn && (a.out_w64 || a.out_w32)) {
         // memory.py:289-295.  The two pow() evaluations run side by side: lane 0 raises the
         // sampled probability, lane 1 the minimum one (one call site, one pow latency).
         const double n = (double)a.n_rows;
-        const double num = lane == 1 ? a.mnn[1] : a.sum[a.cap + k];
+        const double num = lane == 1 ? root_min : a.sum[a.cap + k];
         const double r = pow(__dmul_rn(__ddiv_rn(num, root_sum), n), -a.beta);
         const double max_w = shfl_f64(r, 1);
         if (lane == 0) {

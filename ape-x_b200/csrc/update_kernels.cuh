@@ -56,7 +56,11 @@ struct UpdArgs {
     u64 *status;
     double *max_prio;         // device scalar `_max_priority`; may be null (stand-alone trees)
     double batch_max;         // LEAF_GIVEN: raw-priority maximum of the batch (<=0: none)
+    int64_t idx_base;         // sharded replay: global index of this shard's leaf 0
+    int skip_foreign;         // sharded replay: idx == -1 marks another shard's item, skipped silently
 };
+
+constexpr int64_t IDX_SKIP = INT64_MIN;
 
 // Depth at which the dense top rebuild starts: the largest value <= TOP_LEVELS that leaves
 // a multiple of LIFT generations below it.
@@ -67,7 +71,10 @@ __host__ __device__ __forceinline__ int top_depth(int L) {
 }
 
 __device__ __forceinline__ int64_t upd_index(const UpdArgs &a, int64_t j) {
-    if (a.idx) return a.idx[j];
+    if (a.idx) {
+        const int64_t g = a.idx[j];
+        return (a.skip_foreign && g == -1) ? IDX_SKIP : g - a.idx_base;
+    }
     int64_t k = a.ring_start + j;
     return k >= a.ring_size ? k - a.ring_size : k;
 }
@@ -77,6 +84,7 @@ __device__ __forceinline__ int64_t upd_index(const UpdArgs &a, int64_t j) {
 __device__ __forceinline__ bool upd_item(const UpdArgs &a, int64_t j, int64_t &k, double &leaf, double &raw) {
     k = upd_index(a, j);
     raw = 0.0;
+    if (k == IDX_SKIP) return false;
     unsigned bad = (k < 0 || k >= a.len_limit) ? PER_STATUS_BAD_INDEX : 0u;
     double base = 1.0;
     bool powered = true, checked = false;
@@ -161,18 +169,20 @@ __device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, in
 // ---------------------------------------------------------------------------------------
 // One-launch form (n <= UPD_CLUSTER_MAX_ITEMS): a cluster of 1..8 CTAs.
 //   phase 0  (optional, fused_td) K5: TD error -> priority for the batch (utils.py:71-80);
-//            every CTA evaluates the whole batch (the max is batch-wide) and publishes
-//            the priorities of its own slice
+//            each CTA evaluates its own slice of rows (Q rows staged through shared memory
+//            with coalesced loads), the batch-wide max and the loss terms meet in CTA 0's
+//            shared memory (DSMEM) at one cluster barrier
 //   phase 1  last-write-wins arbitration: atomicMax(stamp[idx], epoch|j)    (memory.py:314-318)
 //   phase 2  winners write the leaves of both trees; max -> _max_priority   (memory.py:320)
 //   phase 3  sparse rounds (lift8) down to depth top_depth(L), cluster barrier between rounds
 //   phase 4  CTA 0: dense rebuild of depths top_depth(L)..0 in shared memory
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, TdArgs td, int fused_td, int skip_update) {
-    __shared__ __align__(16) double s_sum[2 * TOP_NODES];  // phases 1-2: leaf values of this CTA's slice
-    __shared__ __align__(16) double s_min[2 * TOP_NODES];  // phase 0: |td| of the whole batch (float)
-    __shared__ int s_k[UPD_CLUSTER_MAX_ITEMS];             // leaf index of each surviving item of the slice, else -1
+    __shared__ __align__(16) double s_tree[4 * TOP_NODES];  // phase 4: both trees' top; earlier: staging
+    __shared__ int s_k[UPD_CLUSTER_MAX_ITEMS];              // leaf index of each surviving item of the slice, else -1
     __shared__ double s_red[34];
+    __shared__ float s_clu[2 * UPD_MAX_CTAS];               // CTA 0's copy collects per-CTA max / loss partials
+    double *s_sum = s_tree, *s_min = s_tree + 2 * TOP_NODES;
 
     cg::cluster_group cl = cg::this_cluster();
     const int ncta = (int)cl.num_blocks();
@@ -185,50 +195,66 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     const int hi = lo + per < n ? lo + per : n;
     const int cnt = hi - lo;
 
-    if (fused_td) {
-        float *f_red = reinterpret_cast<float *>(s_red);  // [0..31] warp partials, [32] result
-        float *s_td = reinterpret_cast<float *>(s_min);
-        const int nb = (int)td.batch;
-        float mx = 0.0f;
+    if (fused_td) {  // a.n == td.batch: rows are partitioned like the items
+        float *f_red = reinterpret_cast<float *>(s_red);
+        float *s_q = reinterpret_cast<float *>(s_tree);  // staged q_next rows of the slice (8192 floats)
+        float *s_td = reinterpret_cast<float *>(s_k);    // |td| of the slice
+        const int nA = (int)td.nA;
+        const bool staged = (int64_t)cnt * nA <= 8 * TOP_NODES;
+        if (staged) {
+            const float *src = td.q_next + (int64_t)lo * nA;
 #pragma unroll 1
-        for (int j = tid; j < nb; j += T) {
-            float x = td_row(td, j);
-            s_td[j] = x;
+            for (int e = tid; e < cnt * nA; e += T) s_q[e] = src[e];
+            __syncthreads();
+        }
+        float mx = 0.0f, acc = 0.0f;
+#pragma unroll 1
+        for (int i = tid; i < cnt; i += T) {
+            const float x = staged ? td_row_from(td, lo + i, s_q + i * nA) : td_row(td, lo + i);
+            s_td[i] = x;
             mx = fmaxf(mx, x);
+            if (td.out_loss) acc += __fmul_rn(td_huber(x), td.w[lo + i]);
         }
         mx = warp_max_f32(mx);
-        if ((tid & 31) == 0) f_red[tid >> 5] = mx;
+        acc = warp_sum_f32(acc);
+        if ((tid & 31) == 0) {
+            f_red[tid >> 5] = mx;
+            f_red[32 + (tid >> 5)] = acc;
+        }
         __syncthreads();
         if (tid < 32) {
             float m = tid < nwarp ? f_red[tid] : 0.0f;
+            float l = tid < nwarp ? f_red[32 + tid] : 0.0f;
             m = warp_max_f32(m);
-            if (tid == 0) f_red[32] = m;
-        }
-        __syncthreads();
-        mx = f_red[32];
-        const int plo = skip_update ? (rank == 0 ? 0 : nb) : lo, phi = skip_update ? nb : hi;
-#pragma unroll 1
-        for (int j = plo + tid; j < phi; j += T) {
-            const float x = s_td[j];
-            td.out_prio[j] = td_prio(x, mx);
-            if (td.out_td) td.out_td[j] = x;
-        }
-        if (td.out_loss && rank == 0) {
-            float acc = 0.0f;
-#pragma unroll 1
-            for (int j = tid; j < nb; j += T) acc += __fmul_rn(td_huber(s_td[j]), td.w[j]);
-            acc = warp_sum_f32(acc);
-            __syncthreads();
-            if ((tid & 31) == 0) f_red[tid >> 5] = acc;
-            __syncthreads();
-            if (tid < 32) {
-                float m = tid < nwarp ? f_red[tid] : 0.0f;
-                m = warp_sum_f32(m);
-                if (tid == 0) td.out_loss[0] = m / (float)nb;  // .mean(), utils.py:80
+            l = warp_sum_f32(l);
+            if (tid == 0) {
+                float *home = cl.map_shared_rank(s_clu, 0);
+                home[rank] = m;
+                home[UPD_MAX_CTAS + rank] = l;
             }
         }
-        if (skip_update) return;
-        __syncthreads();  // this CTA's out_prio slice is read back below; s_red is reused
+        cl.sync();
+        {
+            const float *home = cl.map_shared_rank(s_clu, 0);
+            mx = 0.0f;
+            for (int r = 0; r < ncta; ++r) mx = fmaxf(mx, home[r]);
+            if (td.out_loss && rank == 0 && tid == 0) {
+                float l = 0.0f;
+                for (int r = 0; r < ncta; ++r) l += home[UPD_MAX_CTAS + r];  // fixed order: deterministic
+                td.out_loss[0] = l / (float)td.batch;                         // .mean(), utils.py:80
+            }
+        }
+#pragma unroll 1
+        for (int i = tid; i < cnt; i += T) {
+            const float x = s_td[i];
+            td.out_prio[lo + i] = td_prio(x, mx);
+            if (td.out_td) td.out_td[lo + i] = x;
+        }
+        if (skip_update) {
+            cl.sync();  // CTA 0's shared memory stays alive until every CTA has read it
+            return;
+        }
+        __syncthreads();  // this CTA's out_prio slice is read back below; s_k / s_tree are reused
     }
 
     // phase 1

@@ -1,0 +1,196 @@
+"""Prioritized replay sharded over the GPUs of one box (BASELINE configs[3]).
+
+The reference keeps one tree in one process (memory.py:231-232).  Here the replay of `size`
+transitions is cut into `world` (a power of two) contiguous index ranges, one per GPU / rank:
+with C = next_pow2(size) leaves in the reference's tree, rank r owns leaves
+[r*C/world, (r+1)*C/world) — the subtree under the reference's node world + r — together with
+the ring slots that fall into that range.  The reference tree is then exactly the `world` local
+trees plus the world-1 nodes above them, and one sample() is
+
+  1. every rank writes a 32-byte record {root sum, root min, its part of the reference's
+     sum(0, len-1) chain, local len}                         (per_shard_record)
+  2. ONE collective: all-gather of the records, rank order   (NCCL over NVLink; gloo on CPU)
+  3. every rank runs all strata through the top log2(world) levels redundantly, keeps the
+     ones that land in its slice and finishes them on its own tree        (per_sample_sharded)
+  4. rank-local gather of the sampled rows; rows, indices and weights can be written straight
+     into a peer GPU's batch buffers by passing peer-mapped output pointers (the gather kernel
+     only sees addresses), and returned priorities are read the same way.
+
+Every rank passes the same full-batch arrays to gather / update: indices are global, and
+-1 marks a stratum owned by another rank (skipped inside the kernels).
+
+Host logic here: geometry, routing of a global add stream to shards, cursor / len bookkeeping,
+the collective.  Everything else is the C ABI (include/per_b200.h).
+"""
+import numpy as np
+import torch
+
+import per_native as _n
+
+REC = 4  # doubles per shard record
+
+
+class ShardGeometry(object):
+    """Where the reference's global slots live.  `size` = the reference's buffer size (ring
+    wraps there, memory.py:169); tree capacity = next power of two (memory.py:227-229)."""
+
+    def __init__(self, size, world):
+        size = int(size)
+        assert world >= 1 and world & (world - 1) == 0 and world <= 16, "world must be a power of two <= 16"
+        cap = 1
+        while cap < size:
+            cap *= 2
+        assert cap >= world
+        self.size, self.world, self.cap = size, world, cap
+        self.cap_local = cap // world
+
+    def ring_local(self, rank):
+        return max(0, min(self.cap_local, self.size - rank * self.cap_local))
+
+    def owner(self, slot):
+        return slot // self.cap_local
+
+    def route(self, cursor, n):
+        """Splits n consecutive adds starting at global slot `cursor` (wrapping at size) into
+        [(rank, src_lo, src_hi, local_slot)] segments in add order (memory.py:162-169)."""
+        out, done = [], 0
+        while done < n:
+            slot = (cursor + done) % self.size
+            r = slot // self.cap_local
+            end = min((r + 1) * self.cap_local, self.size)
+            m = min(n - done, end - slot)
+            out.append((r, done, done + m, slot - r * self.cap_local))
+            done += m
+        return out
+
+
+def exchange_records(rec, group=None):
+    """All-gather of one 4-double record per rank (the only collective of a sample)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    out = torch.empty(world * REC, dtype=rec.dtype, device=rec.device)
+    dist.all_gather_into_tensor(out, rec, group=group)
+    return out
+
+
+class ShardedReplay(object):
+    """One rank's slice of a sharded CustomPrioritizedReplayBuffer (memory.py:323-362).
+    `exchange`: callable(record tensor) -> all records in rank order; defaults to the
+    torch.distributed all-gather on `group`.  Tests emulate several ranks in one process by
+    passing their own exchange."""
+
+    def __init__(self, size, alpha, rank, world, obs_shape=(4, 84, 84), obs_dtype=torch.uint8, extra_shape=None,
+                 extra_dtype=torch.float32, device=None, group=None, exchange=None):
+        assert alpha >= 0
+        self.geo = ShardGeometry(size, world)
+        self.rank, self.world, self.alpha = rank, world, alpha
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.obs_shape, self.obs_dtype = tuple(obs_shape), obs_dtype
+        self.extra_shape, self.extra_dtype = extra_shape, extra_dtype
+        self._exchange = exchange if exchange is not None else (lambda rec: exchange_records(rec, group))
+        obs_bytes = int(np.prod(obs_shape)) * torch.empty(0, dtype=obs_dtype).element_size()
+        extra_bytes = 0 if extra_shape is None else int(np.prod(extra_shape)) * torch.empty(0, dtype=extra_dtype).element_size()
+        h = _n.C.c_void_p()
+        _n.check(_n.lib.per_create_shard(_n.C.byref(h), self.device.index, self.geo.size, rank, world, float(alpha),
+                                         obs_bytes, extra_bytes))
+        self._h = h
+        self._len = 0       # global len(_storage)
+        self._cursor = 0    # global _next_idx
+        self._rec = torch.zeros(REC, dtype=torch.float64, device=self.device)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and _n is not None:
+            _n.lib.per_destroy(h)
+            self._h = None
+
+    def __len__(self):
+        return self._len
+
+    @property
+    def tree_capacity_local(self):
+        return self.geo.cap_local
+
+    # -- insert ---------------------------------------------------------------------------------
+    def add_batch_device(self, obs, next_obs, actions, rewards, dones, priorities, extra=None):
+        """The same call on every rank with the same full batch (n global adds with actor
+        priorities, memory.py:334-346); each rank ingests the rows routed to its slice."""
+        n = int(actions.numel())
+        for r, lo, hi, _slot in self.geo.route(self._cursor, n):
+            if r != self.rank:
+                continue
+            cut = lambda t: None if t is None else t[lo:hi].contiguous()
+            parts = [cut(t) for t in (obs, next_obs, actions, rewards, dones, extra, priorities)]
+            _n.check(_n.lib.per_add_batch(self._h, *[_n.ptr(t) for t in parts], None, 0.0, hi - lo, _n.stream_ptr()))
+        self._cursor = (self._cursor + n) % self.geo.size
+        self._len = min(self.geo.size, self._len + n)
+
+    # -- sample ---------------------------------------------------------------------------------
+    def sample_device(self, batch, beta, uniforms, gather=True, out=None):
+        """Global stratified sample of `batch` transitions (memory.py:252-298).  Returns full-batch
+        CUDA tensors; entries of strata owned by other ranks hold idx -1 / weight 0 and their
+        rows are left untouched.  `out`: optional dict of preallocated (possibly peer-mapped)
+        tensors obs / next_obs / act / rew / done to gather into."""
+        assert beta > 0
+        u = uniforms if torch.is_tensor(uniforms) else torch.as_tensor(np.asarray(uniforms, dtype=np.float64))
+        u = u.to(self.device, dtype=torch.float64)
+        sp = _n.stream_ptr()
+        _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
+        recs = self._exchange(self._rec)
+        idx = torch.empty(batch, dtype=torch.int64, device=self.device)
+        w32 = torch.empty(batch, dtype=torch.float32, device=self.device)
+        w64 = torch.empty(batch, dtype=torch.float64, device=self.device)
+        _n.check(_n.lib.per_sample_sharded(self._h, _n.ptr(recs), _n.ptr(u), batch, float(beta), self._len, _n.ptr(idx),
+                                           _n.ptr(w64), _n.ptr(w32), sp))
+        res = {"idx": idx, "weights": w32, "weights64": w64, "records": recs}
+        if gather:
+            res.update(self.gather_device(idx, out))
+        return res
+
+    def gather_device(self, idx, out=None):
+        b = idx.numel()
+        if out is None:
+            out = {
+                "obs": torch.zeros((b,) + self.obs_shape, dtype=self.obs_dtype, device=self.device),
+                "next_obs": torch.zeros((b,) + self.obs_shape, dtype=self.obs_dtype, device=self.device),
+                "act": torch.zeros(b, dtype=torch.int64, device=self.device),
+                "rew": torch.zeros(b, dtype=torch.float32, device=self.device),
+                "done": torch.zeros(b, dtype=torch.float32, device=self.device),
+            }
+            if self.extra_shape is not None:
+                out["a_mu"] = torch.zeros((b,) + tuple(self.extra_shape), dtype=self.extra_dtype, device=self.device)
+        _n.check(_n.lib.per_gather(self._h, _n.ptr(idx), b, _n.ptr(out["obs"]), _n.ptr(out["next_obs"]), _n.ptr(out["act"]),
+                                   _n.ptr(out["rew"]), _n.ptr(out["done"]), _n.ptr(out.get("a_mu")), _n.stream_ptr()))
+        return out
+
+    # -- update ---------------------------------------------------------------------------------
+    def update_priorities_device(self, idx, priorities):
+        """Full-batch global indices (-1 = not mine) and priorities (float32 / float64 CUDA)."""
+        kind = _n.PRIO_F64 if priorities.dtype == torch.float64 else _n.PRIO_F32
+        _n.check(_n.lib.per_update_priorities(self._h, _n.ptr(idx), _n.ptr(priorities), kind, idx.numel(), _n.stream_ptr()))
+
+    def update_leaves_device(self, idx, leaves, batch_max):
+        _n.check(_n.lib.per_update_leaves(self._h, _n.ptr(idx), _n.ptr(leaves), float(batch_max), idx.numel(),
+                                          _n.stream_ptr()))
+
+    def td_priority_update(self, q, q_next, q_tgt, actions, rewards, dones, weights, n_steps, gamma, idx):
+        """utils.py:71-80 over the FULL batch (the 0.9*max term is batch-wide) + the tree update
+        of this rank's strata.  All ranks pass the same full-batch tensors."""
+        b = int(actions.numel())
+        prio = torch.empty(b, dtype=torch.float32, device=self.device)
+        loss = torch.empty(1, dtype=torch.float32, device=self.device)
+        gamma_n = float(np.float32(gamma ** n_steps))
+        _n.check(_n.lib.per_td_priority_update(self._h, _n.ptr(q), _n.ptr(q_next), _n.ptr(q_tgt), int(q.shape[1]),
+                                               _n.ptr(actions), _n.ptr(rewards), _n.ptr(dones), _n.ptr(weights), gamma_n,
+                                               _n.ptr(idx), b, _n.ptr(prio), None, _n.ptr(loss), _n.stream_ptr()))
+        return loss, prio
+
+    def tree_values(self, which):
+        out = torch.empty(2 * self.geo.cap_local, dtype=torch.float64, device=self.device)
+        _n.check(_n.lib.per_tree_read(self._h, which, _n.ptr(out), _n.stream_ptr()))
+        return out.cpu().numpy()
+
+    def status(self):
+        w = _n.C.c_int64(0)
+        _n.check(_n.lib.per_status(self._h, _n.C.byref(w), _n.stream_ptr()))
+        return w.value

@@ -43,6 +43,9 @@ UNIT = "transitions/s"
 # per sampled transition the gather reads 2*28224 B of frames + 16 B of
 # scalars and writes the same.
 GATHER_BYTES_PER_ROW = 2 * (2 * OBS_BYTES + 16)
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_gather_tma launch at this workload, from the
+# ncu --set full capture summarised in profiles/ (the 28.9 MB written stay in the 126 MB L2)
+NCU_GATHER_TRAFFIC = 29242368 + 434688
 
 
 def peaks():
@@ -176,6 +179,8 @@ def workload_config(n_gpus):
     return {"workload": "Ape-X learner replay step, configs[1]: ring 2^20 Atari transitions per GPU (59.2 GB HBM), "
                         "batch 512 per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions",
             "ring_per_gpu": RING, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
+            "sharding": "none" if n_gpus == 1 else "one replay of %d x 2^20 transitions cut into %d contiguous slices; "
+                        "per step one 32-byte-per-rank NCCL all-gather, global stratified batch %d" % (n_gpus, n_gpus, BATCH * n_gpus),
             "l2": "inputs (59 GB ring) larger than L2; no flush", "parallelism": "shard%d" % n_gpus}
 
 
@@ -214,9 +219,18 @@ def main():
     ring = args.ring
     W = max(args.warmup, 3)
     K = args.steps
+    GB = BATCH * world  # global batch: 512 strata per GPU
 
-    # ---- build + fill the shard --------------------------------------------------------
-    buf = memory.CustomPrioritizedReplayBuffer(ring, ALPHA)
+    # ---- build + fill this rank's slice ----------------------------------------------------
+    # world == 1: the drop-in buffer.  world > 1: slice `rank` of one replay of world*ring
+    # transitions (sharded.py); every rank fills the slots it owns.
+    if world == 1:
+        buf = memory.CustomPrioritizedReplayBuffer(ring, ALPHA)
+        shard = None
+    else:
+        import sharded
+        shard = sharded.ShardedReplay(world * ring, ALPHA, rank, world, obs_shape=OBS_SHAPE)
+        buf = None
     gen = torch.Generator(device=dev).manual_seed(rank)
     chunk = 8192
     for lo in range(0, ring, chunk):
@@ -227,45 +241,66 @@ def main():
         rew = torch.randint(-1, 2, (m,), device=dev, generator=gen).float()
         done = (torch.rand(m, device=dev, generator=gen) < 1e-3).float()
         pr = torch.randn(m, dtype=torch.float64, device=dev, generator=gen).abs() + 1e-6
-        buf.add_batch_device(obs, nxt, act, rew, done, priorities=pr)
+        if world == 1:
+            buf.add_batch_device(obs, nxt, act, rew, done, priorities=pr)
+        else:
+            pn.check(pn.lib.per_add_batch(shard._h, pn.ptr(obs), pn.ptr(nxt), pn.ptr(act), pn.ptr(rew), pn.ptr(done), None,
+                                          pn.ptr(pr), None, 0.0, m, pn.stream_ptr()))
     del obs, nxt
+    if shard is not None:
+        shard._len, shard._cursor = world * ring, 0
+    glen = world * ring
     torch.cuda.synchronize()
 
-    # ---- resident inputs / outputs -------------------------------------------------------
+    # ---- resident inputs / outputs (same on every rank: common seed) -------------------------
+    cgen = torch.Generator(device=dev).manual_seed(1234)
     total_steps = W + K
-    n_u = min(total_steps, 4096)  # distinct uniform vectors, cycled
-    u_all = torch.rand(n_u, BATCH, dtype=torch.float64, device=dev, generator=gen)
-    q = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
-    qn = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
-    qt = torch.randn(BATCH, N_ACTIONS, device=dev, generator=gen)
-    idx = torch.empty(BATCH, dtype=torch.int64, device=dev)
-    w32 = torch.empty(BATCH, dtype=torch.float32, device=dev)
-    o_obs = torch.empty((BATCH,) + OBS_SHAPE, dtype=torch.uint8, device=dev)
-    o_nxt = torch.empty_like(o_obs)
-    o_act = torch.empty(BATCH, dtype=torch.int64, device=dev)
-    o_rew = torch.empty(BATCH, dtype=torch.float32, device=dev)
-    o_done = torch.empty(BATCH, dtype=torch.float32, device=dev)
-    o_prio = torch.empty(BATCH, dtype=torch.float32, device=dev)
+    n_u = min(total_steps, 1024)  # distinct uniform vectors, cycled
+    u_all = torch.rand(n_u, GB, dtype=torch.float64, device=dev, generator=cgen)
+    q = torch.randn(GB, N_ACTIONS, device=dev, generator=cgen)
+    qn = torch.randn(GB, N_ACTIONS, device=dev, generator=cgen)
+    qt = torch.randn(GB, N_ACTIONS, device=dev, generator=cgen)
+    idx = torch.empty(GB, dtype=torch.int64, device=dev)
+    w32 = torch.empty(GB, dtype=torch.float32, device=dev)
+    o_obs = torch.zeros((GB,) + OBS_SHAPE, dtype=torch.uint8, device=dev)
+    o_nxt = torch.zeros_like(o_obs)
+    o_act = torch.zeros(GB, dtype=torch.int64, device=dev)
+    o_rew = torch.zeros(GB, dtype=torch.float32, device=dev)
+    o_done = torch.zeros(GB, dtype=torch.float32, device=dev)
+    o_prio = torch.empty(GB, dtype=torch.float32, device=dev)
     o_loss = torch.empty(1, dtype=torch.float32, device=dev)
+    # world > 1: the TD arithmetic runs over the full batch on every rank (its 0.9*max term is
+    # batch-wide); rows owned by other ranks are stood in for by replicated synthetic columns
+    t_act = o_act if world == 1 else torch.randint(0, N_ACTIONS, (GB,), dtype=torch.int64, device=dev, generator=cgen)
+    t_rew = o_rew if world == 1 else torch.randint(-1, 2, (GB,), device=dev, generator=cgen).float()
+    t_done = o_done if world == 1 else torch.zeros(GB, device=dev)
+    t_w = w32 if world == 1 else torch.rand(GB, device=dev, generator=cgen)
     shard_rec = torch.zeros(4, dtype=torch.float64, device=dev)
-    all_rec = torch.zeros(world * 4, dtype=torch.float64, device=dev) if world > 1 else None
+    all_rec = torch.zeros(world * 4, dtype=torch.float64, device=dev)
 
-    lib, h = pn.lib, buf._h
+    lib = pn.lib
+    h = buf._h if world == 1 else shard._h
     stream = torch.cuda.current_stream()
     sp = pn.stream_ptr(stream)
     P = pn.ptr
     gamma_n = float(np.float32(GAMMA ** N_STEP))
     a_idx, a_w32 = P(idx), P(w32)
-    a_gather = (h, a_idx, BATCH, P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp)
-    a_td = (h, P(q), P(qn), P(qt), N_ACTIONS, P(o_act), P(o_rew), P(o_done), a_w32, gamma_n, a_idx, BATCH, P(o_prio),
+    a_gather = (h, a_idx, GB, P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp)
+    a_td = (h, P(q), P(qn), P(qt), N_ACTIONS, P(t_act), P(t_rew), P(t_done), P(t_w), gamma_n, a_idx, GB, P(o_prio),
             None, P(o_loss), sp)
     u_ptrs = [pn.C.c_void_p(u_all[i].data_ptr()) for i in range(n_u)]
-    launches_per_step = 3  # k_sample, k_gather_tma, k_update_block (TD fused in front)
+    a_rec, a_all = P(shard_rec), P(all_rec)
+    # kernels per step: k_sample, k_gather_tma, k_update_cluster (TD fused in front); sharded adds
+    # k_shard_record (+ NCCL's all-gather kernel, not ours) and B > 2048 uses the multi-launch update
+    launches_per_step = 3 if world == 1 else 4 + (0 if GB <= 2048 else 9)
 
     def step(i, ev=None):
-        if world > 1:  # shard totals exchange: root sum/min + fill count, 32 B per rank
+        if world > 1:  # the one exchange of the path: 32-byte record per rank
+            rc = lib.per_shard_record(h, glen, a_rec, sp)
             dist.all_gather_into_tensor(all_rec, shard_rec)
-        rc = lib.per_sample_indices(h, u_ptrs[i % n_u], BATCH, BETA, a_idx, None, a_w32, sp)
+            rc |= lib.per_sample_sharded(h, a_all, u_ptrs[i % n_u], GB, BETA, glen, a_idx, None, a_w32, sp)
+        else:
+            rc = lib.per_sample_indices(h, u_ptrs[i % n_u], GB, BETA, a_idx, None, a_w32, sp)
         if ev is not None:
             ev[0].record(stream)
         rc |= lib.per_gather(*a_gather)
@@ -279,6 +314,13 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     for i in range(W):
         step(i)
@@ -296,18 +338,15 @@ def main():
     e1.record(stream)
     barrier()
     clocks = sampler.stop()
-    ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = world * BATCH * K / (ms * 1e-3)
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    value = GB * K / (ms * 1e-3)
     gather_ms = float(np.mean([a.elapsed_time(b) for a, b in gather_ev]))
+    rows_this_rank = int((idx >= 0).sum().item())
     status = pn.C.c_int64(0)
     pn.check(lib.per_status(h, pn.C.byref(status), sp))
     assert status.value == 0, "device status word set during the bench: %d" % status.value
 
-    # ---- same loop as one CUDA graph (launch overhead removed) -----------------------------
+    # ---- same loop as one CUDA graph (launch overhead removed; single GPU only) ------------
     graph_value = None
     if world == 1:
         try:
@@ -319,7 +358,7 @@ def main():
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph, stream=side):
                     for i in range(g_steps):
-                        lib.per_sample_indices(h, u_ptrs[i % n_u], BATCH, BETA, a_idx, None, a_w32, sp_side)
+                        lib.per_sample_indices(h, u_ptrs[i % n_u], GB, BETA, a_idx, None, a_w32, sp_side)
                         lib.per_gather(*(a_gather[:-1] + (sp_side,)))
                         lib.per_td_priority_update(*(a_td[:-1] + (sp_side,)))
             stream.wait_stream(side)
@@ -332,34 +371,58 @@ def main():
                 graph.replay()
             g1.record(stream)
             torch.cuda.synchronize()
-            graph_value = BATCH * g_steps * reps / (g0.elapsed_time(g1) * 1e-3)
+            graph_value = GB * g_steps * reps / (g0.elapsed_time(g1) * 1e-3)
         except Exception as exc:  # capture is an extra, never the headline
             graph_value = "capture failed: %s" % str(exc)[:120]
 
-    # ---- e2e: reference-facing API, host buffers in and out ---------------------------------
+    # ---- e2e: the public API with host buffers ---------------------------------------------
     e2e_steps = max(3, min(K, 100))
-    prios_host = [np.abs(np.random.default_rng(i).standard_normal(BATCH)).astype(np.float32) + 1e-6 for i in range(8)]
-    import random as _random
-    _random.seed(0)
-    for i in range(3):
-        out = buf.sample(BATCH, BETA)
-        buf.update_priorities(out[-1], prios_host[i % 8])
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        out = buf.sample(BATCH, BETA)                      # uniforms H2D; frames, scalars, weights, idx D2H
-        buf.update_priorities(out[-1], prios_host[i % 8])  # idx + leaves H2D
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    d2h = sum(int(np.asarray(x).nbytes) for x in out[:-1]) + 8 * BATCH
-    h2d = 8 * BATCH + 8 * BATCH + 8 * BATCH
-    e2e = {"value": world * BATCH * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-           "api": "memory.CustomPrioritizedReplayBuffer.sample()/update_priorities() with host numpy in/out"}
+    if world == 1:
+        # reference-facing API: sample() -> host numpy (frames cross PCIe), update_priorities(host arrays)
+        prios_host = [np.abs(np.random.default_rng(i).standard_normal(BATCH)).astype(np.float32) + 1e-6 for i in range(8)]
+        import random as _random
+        _random.seed(0)
+        for i in range(3):
+            out = buf.sample(BATCH, BETA)
+            buf.update_priorities(out[-1], prios_host[i % 8])
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            out = buf.sample(BATCH, BETA)                      # uniforms H2D; frames, scalars, weights, idx D2H
+            buf.update_priorities(out[-1], prios_host[i % 8])  # idx + leaves H2D
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        d2h = sum(int(np.asarray(x).nbytes) for x in out[:-1]) + 8 * BATCH
+        h2d = 8 * BATCH + 8 * BATCH + 8 * BATCH
+        api = "memory.CustomPrioritizedReplayBuffer.sample()/update_priorities() with host numpy in/out"
+    else:
+        # sharded API: uniforms arrive from pinned host memory, frames stay on the GPUs that train on
+        # them, the step's result (loss + the batch's new priorities) is read back to the host
+        u_host = [torch.rand(GB, dtype=torch.float64, generator=torch.Generator().manual_seed(i)).pin_memory() for i in range(8)]
+        res_host = torch.empty(GB + 1, dtype=torch.float32).pin_memory()
+        outbuf = {"obs": o_obs, "next_obs": o_nxt, "act": o_act, "rew": o_rew, "done": o_done}
+
+        def e2e_step(i):
+            u_dev = u_host[i % 8].to(dev, non_blocking=True)
+            d = shard.sample_device(GB, BETA, u_dev, gather=True, out=outbuf)
+            loss, prio = shard.td_priority_update(q, qn, qt, t_act, t_rew, t_done, t_w, N_STEP, GAMMA, d["idx"])
+            res_host[:GB].copy_(prio, non_blocking=True)
+            res_host[GB:].copy_(loss, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for i in range(3):
+            e2e_step(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        h2d, d2h = 8 * GB, 4 * (GB + 1)
+        api = "sharded.ShardedReplay.sample_device()/td_priority_update(): uniforms from pinned host memory, loss+priorities to host"
+    e2e_s = max_over_ranks(e2e_s)
+    e2e = {"value": GB * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "steps": e2e_steps, "api": api}
 
     # ---- CPU baseline on this box (rank 0, N=1 only) -----------------------------------------
     cpu = None
@@ -372,15 +435,16 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
-        achieved = GATHER_BYTES_PER_ROW * BATCH / (gather_ms * 1e-3) / 1e9
+        launch_bytes = GATHER_BYTES_PER_ROW * rows_this_rank  # rows this rank's gather actually moved (last step)
+        achieved = launch_bytes / (gather_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "roofline": {"bound": "hbm", "kernel": "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "bytes_per_launch": GATHER_BYTES_PER_ROW * BATCH, "avg_launch_us": gather_ms * 1e3},
+                         "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC if world == 1 else None,
+                         "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3},
             "cpu_baseline": cpu, "value_cuda_graph": graph_value,
             "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
         }

@@ -195,6 +195,35 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
                            const float *d_w, float gamma_n, const int64_t *d_idx, int64_t batch,
                            float *d_out_prio, float *d_out_td, float *d_out_loss, void *stream);
 
+/* ---- sharded replay (the reference has one tree in one process) ------------
+ * The replay of `global_size` transitions is cut into n_shards (power of two <= 16)
+ * contiguous index ranges, one per GPU: with C = next_pow2(global_size) leaves in the
+ * reference's single tree (memory.py:227-229), shard r owns leaves [r*C/n, (r+1)*C/n), i.e.
+ * the subtree under the reference's node n + r, so the reference tree is reproduced exactly
+ * by the n local trees plus the n-1 nodes above them.  A sharded handle interprets every
+ * index it is given as GLOBAL (it subtracts r*C/n itself) and silently skips the value -1,
+ * which per_sample_sharded writes for strata owned by other shards; per_gather,
+ * per_update_*, per_td_priority_update can therefore be called on every rank with the same
+ * full-batch arrays.  per_add_batch on a sharded handle takes the rows that fall into this
+ * shard, in slot order (the caller routes them; ape-x_b200/sharded.py has the router). */
+int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank, int n_shards,
+                     double alpha, int64_t obs_bytes, int64_t extra_bytes);
+
+/* Writes this shard's 4-double record {root sum, root min, the shard-local part of the
+ * reference's sum(0, len-1) chain (memory.py:244), local len} to d_out.  The caller
+ * all-gathers the records of all shards in rank order (32 bytes per rank) and passes the
+ * n_shards*4 doubles to per_sample_sharded.  global_len = len(_storage) of the whole replay. */
+int per_shard_record(per_buffer *b, int64_t global_len, double *d_out, void *stream);
+
+/* memory.py:242-250 + 288-296 on the virtual global tree: every rank runs all `batch`
+ * strata through the top log2(n_shards) levels (built from the gathered roots with the
+ * reference's pairwise order), keeps the strata that land in its slice and finishes them on
+ * its local tree.  d_out_idx[i] = global index, or -1 if stratum i belongs to another shard
+ * (weights 0 there).  The union over ranks equals the single-tree result bit for bit. */
+int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch,
+                       double beta, int64_t global_len, int64_t *d_out_idx, double *d_out_w64,
+                       float *d_out_w32, void *stream);
+
 /* Launch-shape knobs of the gather kernel, for the sweeps under profiles/ (not needed in
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies
  * through shared memory, 1 register-staged LDG/STG), "gather_warps", "gather_stages",

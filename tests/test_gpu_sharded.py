@@ -1,0 +1,137 @@
+"""Sharded replay on the GPU.  `world` ranks are emulated in ONE process on ONE device: each
+rank is a ShardedReplay (its own native handle, trees and ring), the all-gather is a
+concatenation, and the ranks run one after the other (they never wait on one another inside a
+kernel, so sequential execution is equivalent).  Checked against a single unsharded buffer
+holding the same data (which test_gpu_parity.py ties to the reference) and against the
+oracle: indices bit-exact, every shard tree equal to the matching subtree of the single tree."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import per_oracle as po
+from oracle import shard_oracle as so
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import __graft_entry__ as entry
+    entry.build()
+    import memory
+    import per_native
+    import sharded
+    return memory, sharded, per_native
+
+
+def bits(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64)).view(np.uint64)
+
+
+def make_data(n, obs_shape, seed):
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    obs = torch.randint(0, 256, (n,) + obs_shape, dtype=torch.uint8, device="cuda", generator=gen)
+    nxt = torch.randint(0, 256, (n,) + obs_shape, dtype=torch.uint8, device="cuda", generator=gen)
+    act = torch.randint(0, 18, (n,), dtype=torch.int64, device="cuda", generator=gen)
+    rew = torch.randn(n, device="cuda", generator=gen)
+    done = (torch.rand(n, device="cuda", generator=gen) < 0.05).float()
+    prio = torch.rand(n, dtype=torch.float64, device="cuda", generator=gen) + 1e-3
+    return obs, nxt, act, rew, done, prio
+
+
+@pytest.mark.parametrize("size,world,n_add,batch", [
+    (4096, 2, 4096, 256), (5000, 4, 5000, 512), (5000, 8, 3001, 512), (100000, 8, 100000, 4096),
+    (5000, 8, 7300, 512),      # wraps the global ring: early slots overwritten
+    (1 << 16, 16, 60000, 512),
+])
+def test_sharded_equals_single_tree(mods, size, world, n_add, batch):
+    memory, sharded, pn = mods
+    obs_shape = (2, 8)
+    data = make_data(n_add, obs_shape, size + world)
+    single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    store = {}
+    shards = [sharded.ShardedReplay(size, 0.6, r, world, obs_shape=obs_shape,
+                                    exchange=lambda rec, r=r: store["all"]) for r in range(world)]
+    for lo in range(0, n_add, 1777):  # uneven chunks crossing slice borders
+        hi = min(n_add, lo + 1777)
+        part = [t[lo:hi].contiguous() for t in data]
+        single.add_batch_device(part[0], part[1], part[2], part[3], part[4], priorities=part[5])
+        for s in shards:
+            s.add_batch_device(*part)
+    assert all(len(s) == len(single) for s in shards)
+    cap_l = shards[0].tree_capacity_local
+    rng = np.random.default_rng(7)
+
+    def exchange_all():
+        recs = []
+        for s in shards:
+            pn.check(pn.lib.per_shard_record(s._h, len(s), pn.ptr(s._rec), pn.stream_ptr()))
+            recs.append(s._rec.clone())
+        store["all"] = torch.cat(recs)
+
+    for step in range(3):
+        sv, mv = single._it_sum._value, single._it_min._value
+        for r, s in enumerate(shards):  # every shard tree is the matching subtree of the single tree
+            assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
+            assert np.array_equal(bits(s.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, r, world))[1:])
+        u = rng.random(batch)
+        want = single.sample_device(batch, 0.4, uniforms=u)
+        exchange_all()
+        assert np.array_equal(bits(store["all"].cpu().numpy().reshape(world, 4)[:, :3]),
+                              bits(np.stack([so.shard_record(so.slice_of(sv, r, world), so.slice_of(mv, r, world), r,
+                                                             len(single)) for r in range(world)])[:, :3]))
+        merged = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        w_merged = torch.zeros(batch, dtype=torch.float64, device="cuda")
+        out = None
+        for s in shards:
+            d = s.sample_device(batch, 0.4, u, gather=False)
+            mine = d["idx"] >= 0
+            assert not bool((merged[mine] >= 0).any())  # one owner per stratum
+            merged[mine] = d["idx"][mine]
+            w_merged[mine] = d["weights64"][mine]
+            # all ranks gather into the SAME full-batch buffers, as they would into a learner's peer memory
+            out = s.gather_device(d["idx"], out)
+            assert s.status() == 0
+        assert torch.equal(merged, want["idx"])
+        assert np.array_equal(merged.cpu().numpy(), po.descend_many(sv, po.stratified_masses(
+            po.prefix_total(sv, len(single) - 1), batch, u)))
+        np.testing.assert_allclose(w_merged.cpu().numpy(), want["weights64"].cpu().numpy(), rtol=1e-12)
+        for k in ("obs", "next_obs", "act", "rew", "done"):
+            assert torch.equal(out[k], want[k]), k
+        # priorities come back for the full batch; each rank applies its own strata
+        newp = torch.rand(batch, device="cuda") + 1e-3
+        single.update_priorities_device(want["idx"], newp)
+        for s in shards:
+            d_idx = torch.where((merged // cap_l) == s.rank, merged, torch.full_like(merged, -1))
+            s.update_priorities_device(d_idx, newp)
+            assert s.status() == 0
+
+
+def test_sharded_fused_td_update(mods):
+    memory, sharded, pn = mods
+    size, world, batch = 1 << 14, 4, 512
+    data = make_data(size, (2, 8), 5)
+    single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    store = {}
+    shards = [sharded.ShardedReplay(size, 0.6, r, world, obs_shape=(2, 8), exchange=lambda rec: store["all"])
+              for r in range(world)]
+    single.add_batch_device(*data[:5], priorities=data[5])
+    for s in shards:
+        s.add_batch_device(*data)
+    u = np.random.default_rng(3).random(batch)
+    want = single.sample_device(batch, 0.4, uniforms=u)
+    recs = []
+    for s in shards:
+        pn.check(pn.lib.per_shard_record(s._h, len(s), pn.ptr(s._rec), pn.stream_ptr()))
+        recs.append(s._rec.clone())
+    store["all"] = torch.cat(recs)
+    q, qn, qt = (torch.randn(batch, 18, device="cuda") for _ in range(3))
+    loss0, prio0, _ = single.td_priority_update(q, qn, qt, want["act"], want["rew"], want["done"], want["weights"], 3, 0.99,
+                                                idx=want["idx"])
+    for s in shards:
+        d = s.sample_device(batch, 0.4, u, gather=False)
+        loss, prio = s.td_priority_update(q, qn, qt, want["act"], want["rew"], want["done"], want["weights"], 3, 0.99, d["idx"])
+        assert torch.equal(prio, prio0) and float(loss) == float(loss0)
+    sv = single._it_sum._value
+    for r, s in enumerate(shards):
+        assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
