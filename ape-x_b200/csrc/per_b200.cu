@@ -43,6 +43,8 @@ struct per_buffer_s {
     int64_t len, cursor;
     int sm_count;
     GatherTune tune;
+    double *rec_out;           // sharded replay: record refreshed by every tree-modifying call (may be null)
+    int64_t global_len;        //   len(_storage) of the whole replay, as last told by the caller
     int shard_rank, n_shards;  // sharded replay: this buffer is slice shard_rank of n_shards (1: not sharded)
     int64_t idx_base;          // shard_rank * tree capacity
     u64 *status() const { return scal; }
@@ -124,9 +126,16 @@ int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cuda
         k_dense_mid<<<(unsigned)(int64_t(1) << (d - k)), 256, 0, s>>>(a.t, d, k);
         d -= k;
     }
-    k_dense_top<<<1, 1024, 0, s>>>(a.t, top);
+    k_dense_top<<<1, 1024, 0, s>>>(a.t, top, a.rec_out, a.rec_need, a.rec_len);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
+}
+
+int64_t shard_need(int64_t global_len, int64_t idx_base, int64_t cap) {
+    int64_t need = (global_len - 1) - idx_base;  // leaves of this slice inside the global prefix [0, len-1)
+    if (need < 0) need = 0;
+    if (need > cap) need = cap;
+    return need;
 }
 
 u64 next_epoch(u64 &epoch, u64 *stamps, int64_t cap, cudaStream_t s) {
@@ -440,11 +449,16 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
 int per_shard_record(per_buffer *b, int64_t global_len, double *d_out, void *stream) {
     if (!b || !d_out || global_len < 0) return fail(PER_ERR_ARG, "per_shard_record: bad argument");
     DeviceGuard g(b->device);
-    int64_t need_local = (global_len - 1) - b->idx_base;  // leaves of this slice inside the global prefix [0, len-1)
-    if (need_local < 0) need_local = 0;
-    if (need_local > b->t.cap) need_local = b->t.cap;
+    const int64_t need_local = shard_need(global_len, b->idx_base, b->t.cap);
     k_shard_record<<<1, 32, 0, (cudaStream_t)stream>>>(b->t.sum, b->t.mnn, b->t.cap, need_local, b->len, d_out);
     PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len) {
+    if (!b || global_len < 0) return fail(PER_ERR_ARG, "per_shard_attach_record: bad argument");
+    b->rec_out = d_record;
+    b->global_len = global_len;
     return PER_OK;
 }
 
@@ -580,6 +594,9 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.batch_max = batch_max;
     a.idx_base = b->idx_base;
     a.skip_foreign = b->n_shards > 1;
+    a.rec_out = b->rec_out;
+    a.rec_need = shard_need(b->global_len, b->idx_base, b->t.cap);
+    a.rec_len = b->len;
     return run_update(a, td, 0, b->sm_count, s);
 }
 

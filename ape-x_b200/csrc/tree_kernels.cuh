@@ -31,7 +31,7 @@ namespace perb {
 __device__ __forceinline__ double warp_prefix_total(const double *v, int64_t cap, int64_t need) {
     const int lane = threadIdx.x & 31;
     const bool emit = (need >> lane) & 1;
-    const double term = emit ? v[(cap >> lane) + ((need >> (lane + 1)) << 1)] : 0.0;
+    const double term = emit ? __ldcg(v + (cap >> lane) + ((need >> (lane + 1)) << 1)) : 0.0;
     double acc = 0.0;
     bool first = true;
 #pragma unroll
@@ -133,16 +133,22 @@ constexpr int SHARD_REC = 4;  // doubles per shard record
 // One record per shard and sample call, all-gathered across ranks: the two roots, and the
 // shard-local part of the reference's  sum(0, len-1)  chain (memory.py:244): the prefix over
 // this shard's first `need_local` leaves when the global prefix ends inside this shard.
-__global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
-                               double *out) {
+// Called by one full warp.  Nodes are read through L2 (the caller may have just written them).
+__device__ __forceinline__ void write_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
+                                                   int64_t len_local, double *out) {
     double partial = 0.0;
     if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
-    if (threadIdx.x == 0) {
-        out[0] = sum[1];
-        out[1] = mnn[1];
+    if ((threadIdx.x & 31) == 0) {
+        out[0] = __ldcg(sum + 1);
+        out[1] = __ldcg(mnn + 1);
         out[2] = partial;
         out[3] = (double)len_local;
     }
+}
+
+__global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
+                               double *out) {
+    write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {

@@ -24,7 +24,9 @@ constexpr int TOP_LEVELS = 10;            // the dense top rebuild covers at mos
 constexpr int TOP_NODES = 1 << TOP_LEVELS;
 constexpr int LIFT = 4;                    // generations recomputed per sparse round (16 nodes = one 128-B line)
 constexpr int LIFT_LANES = 8;              // lanes that share one item in a sparse round
-constexpr int UPD_CLUSTER_MAX_ITEMS = 2048;  // largest batch the one-launch (cluster) form takes
+constexpr int UPD_CLUSTER_MAX_ITEMS = 4096;  // largest batch the one-launch (cluster) form takes
+constexpr int UPD_SLICE_MAX = UPD_CLUSTER_MAX_ITEMS / 8;  // items per CTA at most (8 CTAs above 448 items)
+constexpr int UPD_STAGE_FLOATS = 10240;      // shared staging for Q rows (40 KB; its first 32 KB double as the top-of-tree buffers)
 constexpr int UPD_THREADS = 512;
 constexpr int UPD_MAX_CTAS = 8;            // portable cluster size
 
@@ -58,6 +60,9 @@ struct UpdArgs {
     double batch_max;         // LEAF_GIVEN: raw-priority maximum of the batch (<=0: none)
     int64_t idx_base;         // sharded replay: global index of this shard's leaf 0
     int skip_foreign;         // sharded replay: idx == -1 marks another shard's item, skipped silently
+    double *rec_out;          // sharded replay: refresh this shard's 4-double record after the update (may be null)
+    int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
+    int64_t rec_len;          //   local len
 };
 
 constexpr int64_t IDX_SKIP = INT64_MIN;
@@ -178,8 +183,10 @@ __device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, in
 //   phase 4  CTA 0: dense rebuild of depths top_depth(L)..0 in shared memory
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, TdArgs td, int fused_td, int skip_update) {
-    __shared__ __align__(16) double s_tree[4 * TOP_NODES];  // phase 4: both trees' top; earlier: staging
-    __shared__ int s_k[UPD_CLUSTER_MAX_ITEMS];              // leaf index of each surviving item of the slice, else -1
+    __shared__ __align__(16) float s_raw[UPD_STAGE_FLOATS];  // phase 0: staged Q rows; phases 1-2: leaf values; phase 4: tree tops
+    __shared__ int s_k[UPD_SLICE_MAX];                       // leaf index of each surviving item of the slice, else -1
+    __shared__ float s_tdv[UPD_SLICE_MAX];                   // |td| of the slice
+    double *s_tree = reinterpret_cast<double *>(s_raw);
     __shared__ double s_red[34];
     __shared__ float s_clu[2 * UPD_MAX_CTAS];               // CTA 0's copy collects per-CTA max / loss partials
     double *s_sum = s_tree, *s_min = s_tree + 2 * TOP_NODES;
@@ -197,10 +204,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
 
     if (fused_td) {  // a.n == td.batch: rows are partitioned like the items
         float *f_red = reinterpret_cast<float *>(s_red);
-        float *s_q = reinterpret_cast<float *>(s_tree);  // staged q_next rows of the slice (8192 floats)
-        float *s_td = reinterpret_cast<float *>(s_k);    // |td| of the slice
+        float *s_q = s_raw;  // staged q_next rows of the slice
+        float *s_td = s_tdv;
         const int nA = (int)td.nA;
-        const bool staged = (int64_t)cnt * nA <= 8 * TOP_NODES;
+        const bool staged = (int64_t)cnt * nA <= UPD_STAGE_FLOATS;
         if (staged) {
             const float *src = td.q_next + (int64_t)lo * nA;
 #pragma unroll 1
@@ -317,7 +324,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         cl.sync();
     }
     // phase 4
-    if (rank == 0) dense_lift_block(a.t, 1, top, s_sum, s_min);
+    if (rank == 0) {
+        dense_lift_block(a.t, 1, top, s_sum, s_min);
+        if (a.rec_out && tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -373,10 +383,11 @@ __global__ void __launch_bounds__(256) k_dense_mid(TreeRef t, int d, int k) {
     dense_lift_block(t, (int64_t(1) << (d - k)) + blockIdx.x, k, s_sum, s_min);
 }
 
-__global__ void __launch_bounds__(1024) k_dense_top(TreeRef t, int top) {
+__global__ void __launch_bounds__(1024) k_dense_top(TreeRef t, int top, double *rec_out, int64_t rec_need, int64_t rec_len) {
     __shared__ __align__(16) double s_sum[2 * TOP_NODES];
     __shared__ __align__(16) double s_min[2 * TOP_NODES];
     dense_lift_block(t, 1, top, s_sum, s_min);
+    if (rec_out && threadIdx.x < 32) write_shard_record(t.sum, t.mnn, t.cap, rec_need, rec_len, rec_out);
 }
 
 }  // namespace perb

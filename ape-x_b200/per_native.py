@@ -46,6 +46,7 @@ SIGNATURES = {
     "per_destroy": (C.c_int, [_p]),
     "per_create_shard": (C.c_int, [C.POINTER(_p), C.c_int, _i64, C.c_int, C.c_int, _f64, _i64, _i64]),
     "per_shard_record": (C.c_int, [_p, _i64, _p, _p]),
+    "per_shard_attach_record": (C.c_int, [_p, _p, _i64]),
     "per_sample_sharded": (C.c_int, [_p, _p, _p, _i64, _f64, _i64, _p, _p, _p, _p]),
     "per_capacity": (_i64, [_p]),
     "per_len": (_i64, [_p]),

@@ -97,6 +97,8 @@ class ShardedReplay(object):
         self._len = 0       # global len(_storage)
         self._cursor = 0    # global _next_idx
         self._rec = torch.zeros(REC, dtype=torch.float64, device=self.device)
+        self._rec_fresh = False  # True while the record at _rec reflects the current trees and len
+        self._attach()
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -106,6 +108,18 @@ class ShardedReplay(object):
 
     def __len__(self):
         return self._len
+
+    def _attach(self):
+        """Every tree-changing call rewrites the record for the current whole-replay len."""
+        _n.check(_n.lib.per_shard_attach_record(self._h, _n.ptr(self._rec), self._len))
+
+    def set_global_len(self, n, cursor=None):
+        """For callers that fill the slices themselves (bench): the whole replay now holds n rows."""
+        self._len = int(n)
+        if cursor is not None:
+            self._cursor = int(cursor)
+        self._rec_fresh = False
+        self._attach()
 
     @property
     def tree_capacity_local(self):
@@ -124,6 +138,8 @@ class ShardedReplay(object):
             _n.check(_n.lib.per_add_batch(self._h, *[_n.ptr(t) for t in parts], None, 0.0, hi - lo, _n.stream_ptr()))
         self._cursor = (self._cursor + n) % self.geo.size
         self._len = min(self.geo.size, self._len + n)
+        self._rec_fresh = False
+        self._attach()
 
     # -- sample ---------------------------------------------------------------------------------
     def sample_device(self, batch, beta, uniforms, gather=True, out=None):
@@ -135,7 +151,8 @@ class ShardedReplay(object):
         u = uniforms if torch.is_tensor(uniforms) else torch.as_tensor(np.asarray(uniforms, dtype=np.float64))
         u = u.to(self.device, dtype=torch.float64)
         sp = _n.stream_ptr()
-        _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
+        if not self._rec_fresh:  # inserts since the last update: recompute; otherwise the update left it current
+            _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
         recs = self._exchange(self._rec)
         idx = torch.empty(batch, dtype=torch.int64, device=self.device)
         w32 = torch.empty(batch, dtype=torch.float32, device=self.device)
@@ -168,10 +185,12 @@ class ShardedReplay(object):
         """Full-batch global indices (-1 = not mine) and priorities (float32 / float64 CUDA)."""
         kind = _n.PRIO_F64 if priorities.dtype == torch.float64 else _n.PRIO_F32
         _n.check(_n.lib.per_update_priorities(self._h, _n.ptr(idx), _n.ptr(priorities), kind, idx.numel(), _n.stream_ptr()))
+        self._rec_fresh = True
 
     def update_leaves_device(self, idx, leaves, batch_max):
         _n.check(_n.lib.per_update_leaves(self._h, _n.ptr(idx), _n.ptr(leaves), float(batch_max), idx.numel(),
                                           _n.stream_ptr()))
+        self._rec_fresh = True
 
     def td_priority_update(self, q, q_next, q_tgt, actions, rewards, dones, weights, n_steps, gamma, idx):
         """utils.py:71-80 over the FULL batch (the 0.9*max term is batch-wide) + the tree update
@@ -183,6 +202,7 @@ class ShardedReplay(object):
         _n.check(_n.lib.per_td_priority_update(self._h, _n.ptr(q), _n.ptr(q_next), _n.ptr(q_tgt), int(q.shape[1]),
                                                _n.ptr(actions), _n.ptr(rewards), _n.ptr(dones), _n.ptr(weights), gamma_n,
                                                _n.ptr(idx), b, _n.ptr(prio), None, _n.ptr(loss), _n.stream_ptr()))
+        self._rec_fresh = True
         return loss, prio
 
     def tree_values(self, which):

@@ -193,6 +193,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="time plain launches instead of CUDA graphs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -248,7 +249,7 @@ def main():
                                           pn.ptr(pr), None, 0.0, m, pn.stream_ptr()))
     del obs, nxt
     if shard is not None:
-        shard._len, shard._cursor = world * ring, 0
+        shard.set_global_len(world * ring, 0)
     glen = world * ring
     torch.cuda.synchronize()
 
@@ -326,54 +327,106 @@ def main():
         step(i)
     barrier()
 
-    # ---- timed region: K eager steps, CUDA events on the launching stream ------------------
-    gather_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    barrier()
-    e0.record(stream)
-    for i in range(K):
-        step(W + i, gather_ev[i])
-    e1.record(stream)
-    barrier()
-    clocks = sampler.stop()
-    ms = max_over_ranks(e0.elapsed_time(e1))
-    value = GB * K / (ms * 1e-3)
-    gather_ms = float(np.mean([a.elapsed_time(b) for a, b in gather_ev]))
-    rows_this_rank = int((idx >= 0).sum().item())
-    status = pn.C.c_int64(0)
-    pn.check(lib.per_status(h, pn.C.byref(status), sp))
-    assert status.value == 0, "device status word set during the bench: %d" % status.value
+    # ---- CUDA graphs for the launch-bound loop ----------------------------------------------
+    # The step is four small launches, so plain Python launches are CPU-bound.  Timed region =
+    # blocks of GRAPH_STEPS whole steps replayed as ONE CUDA graph, each block followed by one
+    # instrumented step whose gather is launched by hand between two timing events (the
+    # roofline's per-launch duration comes from those).  Falls back to eager launches if capture fails.
+    GRAPH_STEPS, N_GRAPHS = 15, 4
+    graphs, head_graphs, launch_mode = None, None, "eager launches"
 
-    # ---- same loop as one CUDA graph (launch overhead removed; single GPU only) ------------
-    graph_value = None
-    if world == 1:
+    def capture(body):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            body()
+        return g
+
+    def enqueue_head(j, sps):  # TD + tree update of the previous batch, record exchange, sample
+        rc = lib.per_td_priority_update(*(a_td[:-1] + (sps,)))
+        if world > 1:
+            dist.all_gather_into_tensor(all_rec, shard_rec)
+            rc |= lib.per_sample_sharded(h, a_all, u_ptrs[j % n_u], GB, BETA, glen, a_idx, None, a_w32, sps)
+        else:
+            rc |= lib.per_sample_indices(h, u_ptrs[j % n_u], GB, BETA, a_idx, None, a_w32, sps)
+        if rc:
+            pn.check(rc)
+
+    if not args.eager:
         try:
-            g_steps = min(K, 64)
+            if shard is not None:
+                pn.check(lib.per_shard_attach_record(h, a_rec, glen))  # update kernels refresh the record themselves
             side = torch.cuda.Stream()
             side.wait_stream(stream)
             with torch.cuda.stream(side):
                 sp_side = pn.stream_ptr(side)
-                graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=side):
-                    for i in range(g_steps):
-                        lib.per_sample_indices(h, u_ptrs[i % n_u], GB, BETA, a_idx, None, a_w32, sp_side)
-                        lib.per_gather(*(a_gather[:-1] + (sp_side,)))
-                        lib.per_td_priority_update(*(a_td[:-1] + (sp_side,)))
+
+                def full_block(base):
+                    for t in range(GRAPH_STEPS):
+                        enqueue_head(base + t, sp_side)
+                        rc = lib.per_gather(*(a_gather[:-1] + (sp_side,)))
+                        if rc:
+                            pn.check(rc)
+
+                built = [capture(lambda j=j: full_block(j * GRAPH_STEPS)) for j in range(N_GRAPHS)]
+                heads = [capture(lambda j=j: enqueue_head(N_GRAPHS * GRAPH_STEPS + j, sp_side)) for j in range(N_GRAPHS)]
             stream.wait_stream(side)
-            reps = max(3, K // g_steps)
-            graph.replay()
             torch.cuda.synchronize()
-            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            g0.record(stream)
-            for _ in range(reps):
-                graph.replay()
-            g1.record(stream)
-            torch.cuda.synchronize()
-            graph_value = GB * g_steps * reps / (g0.elapsed_time(g1) * 1e-3)
-        except Exception as exc:  # capture is an extra, never the headline
-            graph_value = "capture failed: %s" % str(exc)[:120]
+            graphs, head_graphs = built, heads
+            launch_mode = ("cuda graphs: blocks of %d whole steps per graph + 1 instrumented step "
+                           "(gather launched between timing events)" % GRAPH_STEPS)
+        except Exception as exc:
+            sys.stderr.write("graph capture failed, timing eager launches: %s\n" % str(exc)[:300])
+            graphs = None
+
+    def timed(n_steps, use_graphs):
+        """Runs exactly n_steps steps; returns (ms over all ranks, mean ms of the instrumented gather launches)."""
+        evs = []
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        t0.record(stream)
+        if use_graphs:
+            done, blk = 0, 0
+            while done < n_steps:
+                if n_steps - done > GRAPH_STEPS:
+                    graphs[blk % N_GRAPHS].replay()
+                    done += GRAPH_STEPS
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                head_graphs[blk % N_GRAPHS].replay()
+                ev[0].record(stream)
+                rc = lib.per_gather(*a_gather)
+                ev[1].record(stream)
+                if rc:
+                    pn.check(rc)
+                evs.append(ev)
+                done += 1
+                blk += 1
+        else:
+            for i in range(n_steps):
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                step(W + i, ev)
+                evs.append(ev)
+        t1.record(stream)
+        barrier()
+        return max_over_ranks(t0.elapsed_time(t1)), float(np.mean([x.elapsed_time(y) for x, y in evs]))
+
+    if graphs is not None:
+        timed(min(K, 64), True)  # warm the graphs
+    # ---- timed region: K steps, CUDA events on the launching stream --------------------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms, gather_ms = timed(K, graphs is not None)
+    clocks = sampler.stop()
+    value = GB * K / (ms * 1e-3)
+    rows_this_rank = int((idx >= 0).sum().item())
+    status = pn.C.c_int64(0)
+    pn.check(lib.per_status(h, pn.C.byref(status), sp))
+    assert status.value == 0, "device status word set during the bench: %d" % status.value
+    # the same steps launched one call at a time (shows what the graphs remove)
+    eager_value = None
+    if graphs is not None:
+        k2 = min(K, 300)
+        ms2, _ = timed(k2, False)
+        eager_value = GB * k2 / (ms2 * 1e-3)
 
     # ---- e2e: the public API with host buffers ---------------------------------------------
     e2e_steps = max(3, min(K, 100))
@@ -445,7 +498,7 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC if world == 1 else None,
                          "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3},
-            "cpu_baseline": cpu, "value_cuda_graph": graph_value,
+            "cpu_baseline": cpu, "launch": launch_mode, "value_eager_launches": eager_value,
             "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
         }
         print(json.dumps(line), flush=True)

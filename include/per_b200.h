@@ -215,6 +215,13 @@ int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank
  * n_shards*4 doubles to per_sample_sharded.  global_len = len(_storage) of the whole replay. */
 int per_shard_record(per_buffer *b, int64_t global_len, double *d_out, void *stream);
 
+/* Optional: from now on every call that changes this shard's trees (per_update_*,
+ * per_td_priority_update) also rewrites the record at d_record as its last step, computed
+ * for a whole-replay len of global_len, so the learner loop (update -> sample, no inserts in
+ * between) needs no per_shard_record launch.  Call again whenever the whole-replay len
+ * changes; d_record == NULL detaches. */
+int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len);
+
 /* memory.py:242-250 + 288-296 on the virtual global tree: every rank runs all `batch`
  * strata through the top log2(n_shards) levels (built from the gathered roots with the
  * reference's pairwise order), keeps the strata that land in its slice and finishes them on

@@ -65,7 +65,10 @@ def test_sharded_equals_single_tree(mods, size, world, n_add, batch):
     def exchange_all():
         recs = []
         for s in shards:
+            left_by_update = s._rec.clone() if s._rec_fresh else None
             pn.check(pn.lib.per_shard_record(s._h, len(s), pn.ptr(s._rec), pn.stream_ptr()))
+            if left_by_update is not None:  # the update kernel's tail must have left the same record
+                assert np.array_equal(bits(left_by_update.cpu().numpy()), bits(s._rec.cpu().numpy()))
             recs.append(s._rec.clone())
         store["all"] = torch.cat(recs)
 
