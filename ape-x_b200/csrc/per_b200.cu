@@ -5,6 +5,7 @@
 
 #include "common.cuh"
 #include "gather_kernels.cuh"
+#include "nstep_kernels.cuh"
 #include "td_kernels.cuh"
 #include "tree_kernels.cuh"
 #include "update_kernels.cuh"
@@ -673,6 +674,45 @@ int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
     DeviceGuard g(b->device);
     PER_CUDA(cudaMemcpyAsync(d_out, which == PER_TREE_SUM ? b->t.sum : b->t.mnn, sizeof(double) * 2 * b->t.cap,
                              cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PER_OK;
+}
+
+// ------------------------------------------------------------------------------ n-step assembly
+int nstep_assemble(int device, int64_t n_streams, const int64_t *d_offsets, const int64_t *d_emit_from, const double *d_reward,
+                   const int64_t *d_action, const uint8_t *d_done, const float *d_q, int64_t n_actions, int n_steps,
+                   const double *h_gamma_pow, int64_t *d_out_first, int64_t *d_out_next, int64_t *d_out_action,
+                   double *d_out_return, float *d_out_done, double *d_out_prio, int64_t *d_out_count, uint64_t *d_status,
+                   void *stream) {
+    if (n_streams < 0 || n_actions <= 0 || !h_gamma_pow || !d_status) return fail(PER_ERR_ARG, "nstep_assemble: bad argument");
+    if (n_steps < 1 || n_steps > NSTEP_MAX_N) return fail(PER_ERR_ARG, "nstep_assemble: n_steps must be in [1, %d]", NSTEP_MAX_N);
+    if (n_streams == 0) return PER_OK;
+    if (!d_offsets || !d_reward || !d_action || !d_done || !d_q || !d_out_first || !d_out_next || !d_out_action ||
+        !d_out_return || !d_out_done || !d_out_prio || !d_out_count)
+        return fail(PER_ERR_ARG, "nstep_assemble: null buffer");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "nstep_assemble: cannot select device %d", device);
+    NstepArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_streams = n_streams;
+    a.offsets = d_offsets;
+    a.emit_from = d_emit_from;
+    a.reward = d_reward;
+    a.action = d_action;
+    a.done = d_done;
+    a.q = d_q;
+    a.nA = n_actions;
+    a.n = n_steps;
+    for (int k = 0; k <= n_steps; ++k) a.gpow[k] = h_gamma_pow[k];
+    a.out_first = d_out_first;
+    a.out_next = d_out_next;
+    a.out_action = d_out_action;
+    a.out_return = d_out_return;
+    a.out_done = d_out_done;
+    a.out_prio = d_out_prio;
+    a.out_count = d_out_count;
+    a.status = reinterpret_cast<u64 *>(d_status);
+    k_nstep<<<(unsigned)((n_streams + 3) / 4), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
 

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libper_b200.so")
 
 PER_OK, PER_ERR_ASSERT, PER_ERR_CUDA, PER_ERR_ARG, PER_ERR_NOMEM = 0, -1, -2, -3, -4
-STATUS_BAD_PRIORITY, STATUS_BAD_INDEX, STATUS_BAD_PREFIXSUM = 1, 2, 4
+STATUS_BAD_PRIORITY, STATUS_BAD_INDEX, STATUS_BAD_PREFIXSUM, STATUS_NSTEP_EMPTY = 1, 2, 4, 8
 TREE_SUM, TREE_MIN = 0, 1
 SEG_NOALLOC_MAX_CAPACITY = 1 << 20
 PRIO_F64, PRIO_F32 = 0, 1
@@ -41,6 +41,7 @@ SIGNATURES = {
     "seg_read": (C.c_int, [_p, _p, _p]),
     "seg_capacity": (_i64, [_p]),
     "seg_status": (C.c_int, [_p, C.POINTER(_i64), _p]),
+    "nstep_assemble": (C.c_int, [C.c_int, _i64, _p, _p, _p, _p, _p, _p, _i64, C.c_int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "seg_set_noalloc": (C.c_int, [C.c_int, _p, _p, _i64, _p, _p, _i64, _p, _p]),
     "per_create": (C.c_int, [C.POINTER(_p), C.c_int, _i64, _f64, _i64, _i64]),
     "per_destroy": (C.c_int, [_p]),

@@ -44,6 +44,7 @@ extern "C" {
 #define PER_STATUS_BAD_PRIORITY   1   /* priority <= 0 or NaN      (memory.py:315) */
 #define PER_STATUS_BAD_INDEX      2   /* idx outside [0, len)      (memory.py:316, :90) */
 #define PER_STATUS_BAD_PREFIXSUM  4   /* mass outside [0, sum+1e-5] (memory.py:121) */
+#define PER_STATUS_NSTEP_EMPTY    8   /* done arrived on an empty n-step window (IndexError at memory.py:417) */
 
 #define PER_TREE_SUM 0
 #define PER_TREE_MIN 1
@@ -81,6 +82,26 @@ int seg_read(seg_tree *t, double *d_out, void *stream);
 int64_t seg_capacity(const seg_tree *t);
 /* Reads and clears the status word.  Synchronises `stream`. */
 int seg_status(seg_tree *t, int64_t *h_out, void *stream);
+
+/* ---------------------------------------------------------------- n-step assembly
+ * BatchStorage.add / multi_step_reward / compute_priorities (memory.py:415-440, 471-475,
+ * 451-464) for n_streams actor streams at once.  Stream s is the steps
+ * [d_offsets[s], d_offsets[s+1]) of the flat arrays d_reward (float64), d_action (int64),
+ * d_done (uint8), d_q (float32 [T, n_actions], the actor's Q row at each step); it is
+ * processed as by a BatchStorage created empty at its first step.  Emissions at steps before
+ * d_emit_from[s] are suppressed (NULL: none are): pass a few earlier steps as pre-roll to
+ * continue a stream whose windows are not empty.  h_gamma_pow: HOST table gamma**k for
+ * k = 0..n_steps (CPython's pow, so returns are bit-identical).  Outputs, at slots
+ * d_offsets[s] + e for the e-th emission of stream s (e < d_out_count[s]): step index of the
+ * transition's state and of its bootstrap state, its action, n-step return (float64), done
+ * (float32), actor priority (float64).  PER_STATUS_NSTEP_EMPTY is OR-ed into *d_status when a
+ * done arrives on an empty window (the reference raises IndexError there). */
+int nstep_assemble(int device, int64_t n_streams, const int64_t *d_offsets, const int64_t *d_emit_from,
+                   const double *d_reward, const int64_t *d_action, const uint8_t *d_done,
+                   const float *d_q, int64_t n_actions, int n_steps, const double *h_gamma_pow,
+                   int64_t *d_out_first, int64_t *d_out_next, int64_t *d_out_action,
+                   double *d_out_return, float *d_out_done, double *d_out_prio,
+                   int64_t *d_out_count, uint64_t *d_status, void *stream);
 
 /* Batched tree write for callers that cannot allocate device memory.  (No counterpart in
  * the reference, which has no device memory at all.)
