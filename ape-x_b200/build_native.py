@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libper_b200.so")
 SOURCES = ["per_b200.cu"]
-HEADERS = ["common.cuh", "tree_kernels.cuh", "update_kernels.cuh", "gather_kernels.cuh", "td_kernels.cuh",
+HEADERS = ["common.cuh", "tree_kernels.cuh", "update_kernels.cuh", "gather_kernels.cuh", "td_kernels.cuh", "nstep_kernels.cuh", "aql_kernels.cuh",
            os.path.join("..", "..", "include", "per_b200.h")]
 
 

@@ -5,6 +5,7 @@
 
 #include "common.cuh"
 #include "gather_kernels.cuh"
+#include "aql_kernels.cuh"
 #include "nstep_kernels.cuh"
 #include "td_kernels.cuh"
 #include "tree_kernels.cuh"
@@ -674,6 +675,103 @@ int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
     DeviceGuard g(b->device);
     PER_CUDA(cudaMemcpyAsync(d_out, which == PER_TREE_SUM ? b->t.sum : b->t.mnn, sizeof(double) * 2 * b->t.cap,
                              cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PER_OK;
+}
+
+// ------------------------------------------------------------------------------ AQL candidate Q
+struct aql_plan_s {
+    int device, continuous, A, sm_count;
+    uint8_t *img;        // swizzled TF32 hi/lo weight image
+    AqlSmall *small;     // small parameters
+    float *sv;           // [B, 64] state halves
+    int64_t sv_cap;
+    bool have_weights;
+};
+
+int aql_create(aql_plan **out, int device, int continuous, int action_dim) {
+    if (!out) return fail(PER_ERR_ARG, "aql_create: null out");
+    if (continuous && (action_dim < 1 || action_dim > AQL_MAX_A))
+        return fail(PER_ERR_ARG, "aql_create: action_dim must be in [1, %d]", AQL_MAX_A);
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "aql_create: cannot select device %d", device);
+    aql_plan *p = new aql_plan();
+    memset(p, 0, sizeof *p);
+    p->device = device;
+    p->continuous = continuous ? 1 : 0;
+    p->A = continuous ? action_dim : 1;
+    cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (cudaMalloc(&p->img, AQL_IMG_BYTES) != cudaSuccess || cudaMalloc(&p->small, sizeof(AqlSmall)) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(p->img);
+        delete p;
+        return fail(PER_ERR_NOMEM, "aql_create: cudaMalloc failed");
+    }
+    PER_CUDA(cudaFuncSetAttribute(k_aql_q, cudaFuncAttributeMaxDynamicSharedMemorySize, AQL_SMEM_BYTES));
+    *out = p;
+    return PER_OK;
+}
+
+int aql_destroy(aql_plan *p) {
+    if (!p) return PER_OK;
+    DeviceGuard g(p->device);
+    cudaFree(p->img);
+    cudaFree(p->small);
+    cudaFree(p->sv);
+    delete p;
+    return PER_OK;
+}
+
+int aql_set_weights(aql_plan *p, const float *d_wa1, const float *d_ba1, const float *d_wa2, const float *d_ba2,
+                    const float *d_wadv1, const float *d_badv1, const float *d_wadv2, const float *d_badv2, void *stream) {
+    if (!p || !d_wa1 || !d_ba1 || !d_wadv1 || !d_badv1 || !d_wadv2 || !d_badv2 || (p->continuous && (!d_wa2 || !d_ba2)))
+        return fail(PER_ERR_ARG, "aql_set_weights: null weight");
+    DeviceGuard g(p->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int e1 = p->continuous ? AQL_E1 : AQL_H;
+    char *sm = reinterpret_cast<char *>(p->small);
+    PER_CUDA(cudaMemsetAsync(p->small, 0, sizeof(AqlSmall), s));
+    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, wa1), d_wa1, sizeof(float) * e1 * p->A, cudaMemcpyDeviceToDevice, s));
+    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, ba1), d_ba1, sizeof(float) * e1, cudaMemcpyDeviceToDevice, s));
+    if (p->continuous)
+        PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, ba2), d_ba2, sizeof(float) * AQL_H, cudaMemcpyDeviceToDevice, s));
+    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, w2), d_wadv2, sizeof(float) * AQL_H, cudaMemcpyDeviceToDevice, s));
+    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, b2), d_badv2, sizeof(float), cudaMemcpyDeviceToDevice, s));
+    k_aql_prep_weights<<<(AQL_H * 48 + 127) / 128, 128, 0, s>>>(p->continuous ? d_wa2 : nullptr, d_wadv1, p->img);
+    PER_CUDA(cudaGetLastError());
+    p->have_weights = true;
+    return PER_OK;
+}
+
+int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, const float *d_f, const void *d_a_mu, int64_t B,
+                    int64_t K, float *d_q, int64_t *d_argmax, void *stream) {
+    if (!p || !d_wadv1 || !d_badv1 || !d_f || !d_a_mu || !d_q || B <= 0 || K <= 0) return fail(PER_ERR_ARG, "aql_candidate_q: bad argument");
+    if (!p->have_weights) return fail(PER_ERR_ARG, "aql_candidate_q: call aql_set_weights first");
+    DeviceGuard g(p->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (B > p->sv_cap) {
+        PER_CUDA(cudaStreamSynchronize(s));
+        cudaFree(p->sv);
+        p->sv = nullptr;
+        PER_CUDA(cudaMalloc(&p->sv, sizeof(float) * B * AQL_H));
+        p->sv_cap = B;
+    }
+    k_aql_state_half<<<(unsigned)((B * AQL_H + 255) / 256), 256, 0, s>>>(d_wadv1, d_badv1, d_f, B, p->sv);
+    AqlArgs a;
+    memset(&a, 0, sizeof a);
+    a.img = p->img;
+    a.small = p->small;
+    a.sv = p->sv;
+    a.a_mu = d_a_mu;
+    a.continuous = p->continuous;
+    a.A = p->A;
+    a.K = K;
+    a.total = B * K;
+    a.q = d_q;
+    int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
+    int64_t grid = tiles < p->sm_count ? tiles : p->sm_count;
+    k_aql_q<<<(unsigned)grid, AQL_TILE, AQL_SMEM_BYTES, s>>>(a);
+    if (d_argmax) k_aql_argmax<<<(unsigned)((B * 32 + 127) / 128), 128, 0, s>>>(d_q, B, K, d_argmax);
+    PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
 

@@ -54,6 +54,7 @@ extern "C" {
 
 typedef struct seg_tree_s seg_tree;      /* one SumSegmentTree / MinSegmentTree          */
 typedef struct per_buffer_s per_buffer;  /* one (Custom)PrioritizedReplayBuffer(_AQL)    */
+typedef struct aql_plan_s aql_plan;      /* weights of one AQL Q_Network, prepared for the fused forward */
 
 const char *per_last_error(void);
 int per_version(void);
@@ -82,6 +83,27 @@ int seg_read(seg_tree *t, double *d_out, void *stream);
 int64_t seg_capacity(const seg_tree *t);
 /* Reads and clears the status word.  Synchronises `stream`. */
 int seg_status(seg_tree *t, int64_t *h_out, void *stream);
+
+/* ---------------------------------------------------------------- AQL candidate Q + argmax
+ * Q_Network.act (model.py:294-335): for each state b and candidate action k,
+ *   e = action_out(a_bk); h = relu(advantage1(cat[e, f_b])); q = advantage2(h); argmax_k.
+ * f [B,64] = q_feature(state) stays PyTorch (a per-state MLP); everything per candidate is
+ * one fused kernel on the tensor cores (tcgen05, 3xTF32 for float32 parity).
+ * continuous != 0: a_mu float32 [B,K,action_dim], action_out = Linear(A,128)-ReLU-Linear(128,64)-ReLU
+ *                  (model.py:252-257); continuous == 0: a_mu int64 [B,K], action_out =
+ *                  Linear(1,64)-ReLU (model.py:260-263). */
+int aql_create(aql_plan **out, int device, int continuous, int action_dim);
+int aql_destroy(aql_plan *p);
+/* Device pointers to float32 weights in torch's [out, in] layout: action_out layers (d_wa2 /
+ * d_ba2 NULL when discrete), then the EFFECTIVE advantage1 / advantage2 weights — mu, or
+ * mu + sigma*epsilon in training mode (NoisyLinear.forward, model.py:132-143). */
+int aql_set_weights(aql_plan *p, const float *d_wa1, const float *d_ba1, const float *d_wa2,
+                    const float *d_ba2, const float *d_wadv1, const float *d_badv1,
+                    const float *d_wadv2, const float *d_badv2, void *stream);
+/* d_q float32 [B,K] out; d_argmax int64 [B] out or NULL (first maximum wins, torch.argmax). */
+int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, const float *d_f,
+                    const void *d_a_mu, int64_t B, int64_t K, float *d_q, int64_t *d_argmax,
+                    void *stream);
 
 /* ---------------------------------------------------------------- n-step assembly
  * BatchStorage.add / multi_step_reward / compute_priorities (memory.py:415-440, 471-475,
