@@ -40,7 +40,7 @@ constexpr int AQL_SM_A_LO = AQL_SM_A_HI + 4 * AQL_ATOM_A;
 constexpr int AQL_SM_SMALL = AQL_SM_A_LO + 4 * AQL_ATOM_A;     // 229 376: ba2[64] w2[64] barriers tmem slot
 constexpr int AQL_SMEM_BYTES = AQL_SM_SMALL + 1024 + 1024;      // + small area + alignment slack
 
-struct AqlSmall {  // small parameters, read through L1 (same address for the whole warp)
+struct AqlSmall {  // small parameters; passed to the kernel by value, i.e. through the constant bank
     float wa1[AQL_E1 * AQL_MAX_A];  // continuous: [128, A]; discrete: [64, 1]
     float ba1[AQL_E1];
     float ba2[AQL_H];
@@ -134,10 +134,8 @@ __global__ void k_aql_state_half(const float *wadv1, const float *badv1, const f
 // ---- the fused forward ---------------------------------------------------------------------
 struct AqlArgs {
     const uint8_t *img;      // swizzled weight image (AQL_IMG_BYTES)
-    const AqlSmall *small;
     const float *sv;         // [B, 64]
     const void *a_mu;        // continuous: float [B*K, A]; discrete: int64 [B*K]
-    int continuous, A;
     int64_t K, total;        // candidates per state, B*K
     float *q;                // [B*K]
 };
@@ -172,19 +170,26 @@ __device__ __forceinline__ void issue_3xtf32(uint32_t tmem_d, uint32_t a_hi, uin
     }
 }
 
-__global__ void __launch_bounds__(AQL_TILE, 1) k_aql_q(AqlArgs a) {
+constexpr int AQL_THREADS = 256;  // two threads per candidate row: each owns half of the columns
+
+// A = action dimension (continuous) at compile time so that layer 1 unrolls into FFMAs whose
+// weight operands come straight from the constant bank (`small` is a __grid_constant__ kernel
+// parameter, 5 KB); CONT = false is the discrete path (Linear(1,64), no second action layer).
+template <int A, bool CONT>
+__global__ void __launch_bounds__(AQL_THREADS, 1) k_aql_q(const AqlArgs a, const __grid_constant__ AqlSmall small) {
     extern __shared__ uint8_t aql_raw[];
     uint8_t *sm = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(aql_raw) + 1023) & ~uintptr_t(1023));
     uint8_t *a_hi = sm + AQL_SM_A_HI, *a_lo = sm + AQL_SM_A_LO;
-    float *s_ba2 = reinterpret_cast<float *>(sm + AQL_SM_SMALL);
-    float *s_w2 = s_ba2 + AQL_H;
-    uint64_t *bar_w = reinterpret_cast<uint64_t *>(s_w2 + AQL_H);  // weights landed
-    uint64_t *bar_m = bar_w + 1;                                    // MMAs of one layer done
+    float *s_part = reinterpret_cast<float *>(sm + AQL_SM_SMALL);   // [128] partial dot of the upper column half
+    uint64_t *bar_w = reinterpret_cast<uint64_t *>(s_part + AQL_TILE);  // weights landed
+    uint64_t *bar_m = bar_w + 1;                                        // MMAs of one layer done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_m + 1);
 
-    const int r = threadIdx.x;  // row of the tile = TMEM lane
-    const int warp = r >> 5;
-    if (r == 0) {
+    const int tid = threadIdx.x;
+    const int r = tid & (AQL_TILE - 1);   // row of the tile = TMEM lane
+    const int half = tid >> 7;            // which half of the columns this thread owns
+    const int warp = tid >> 5;
+    if (tid == 0) {
         mbar_init(smem_u32(bar_w), 1);
         mbar_init(smem_u32(bar_m), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -195,46 +200,43 @@ __global__ void __launch_bounds__(AQL_TILE, 1) k_aql_q(AqlArgs a) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(128));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    if (r < AQL_H) {
-        s_ba2[r] = a.small->ba2[r];
-        s_w2[r] = a.small->w2[r];
-    }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
-    const uint32_t d2 = tmem, d3 = tmem + AQL_H;                 // two 64-column accumulators
-    const uint32_t my_lane = (uint32_t)(warp * 32) << 16;         // this warp's TMEM lanes
+    const uint32_t d2 = tmem, d3 = tmem + AQL_H;                           // two 64-column accumulators
+    const uint32_t my_tmem = ((uint32_t)((warp & 3) * 32) << 16) + half * 32;  // this warp's lanes, this thread's columns
     mbar_wait(smem_u32(bar_w), 0);
-    const float b2 = a.small->b2;
     uint32_t phase = 0;
 
     const int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
     for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const int64_t c = tile * AQL_TILE + r;
         const bool live = c < a.total;
-        const int64_t cc_idx = live ? c : a.total - 1;  // dead rows recompute the last candidate; never stored
+        const int64_t ci = live ? c : a.total - 1;  // dead rows recompute the last candidate; never stored
         float v[4];
-        if (a.continuous) {
-            // layer 1 on CUDA cores (K = A <= 8): h1 = relu(Wa1 . a + ba1), 128 wide, split and staged
-            float act[AQL_MAX_A];
-            const float *ap = static_cast<const float *>(a.a_mu) + cc_idx * a.A;
-            for (int j = 0; j < a.A; ++j) act[j] = ap[j];
-#pragma unroll 1
-            for (int cc = 0; cc < AQL_E1 / 4; ++cc) {
+        if (CONT) {
+            // layer 1 on CUDA cores (K = A): h1 = relu(Wa1 . a + ba1); this thread's 64 of the 128 outputs
+            float act[A];
+            const float *ap = static_cast<const float *>(a.a_mu) + ci * A;
+#pragma unroll
+            for (int j = 0; j < A; ++j) act[j] = ap[j];
+#pragma unroll
+            for (int cc = 0; cc < 16; ++cc) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const int o = cc * 4 + e;
-                    float s = a.small->ba1[o];
-                    for (int j = 0; j < a.A; ++j) s = fmaf(a.small->wa1[o * a.A + j], act[j], s);
+                    const int o = half * 64 + cc * 4 + e;
+                    float s = small.ba1[o];
+#pragma unroll
+                    for (int j = 0; j < A; ++j) s = fmaf(small.wa1[o * A + j], act[j], s);
                     v[e] = fmaxf(s, 0.0f);
                 }
-                store_split(a_hi, a_lo, r, cc, v);
+                store_split(a_hi, a_lo, r, half * 16 + cc, v);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncthreads();
-            if (r == 0) {
+            if (tid == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 issue_3xtf32(d2, smem_u32(a_hi), smem_u32(a_lo), smem_u32(sm + AQL_IMG_W2_HI), smem_u32(sm + AQL_IMG_W2_LO), 4);
                 umma_commit(smem_u32(bar_m));
@@ -242,35 +244,32 @@ __global__ void __launch_bounds__(AQL_TILE, 1) k_aql_q(AqlArgs a) {
             mbar_wait(smem_u32(bar_m), phase);
             phase ^= 1u;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // layer 2 epilogue: e = relu(D2 + ba2) -> next A operand (K = 64: atoms 0..1)
+            // layer 2 epilogue: e = relu(D2 + ba2) -> next A operand (K = 64: atoms 0..1); 32 columns per thread
             float acc[32];
-#pragma unroll 1
-            for (int half = 0; half < 2; ++half) {
-                tmem_ld32(d2 + my_lane + half * 32, acc);
+            tmem_ld32(d2 + my_tmem, acc);
 #pragma unroll
-                for (int cc = 0; cc < 8; ++cc) {
+            for (int cc = 0; cc < 8; ++cc) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) v[e] = fmaxf(acc[cc * 4 + e] + s_ba2[half * 32 + cc * 4 + e], 0.0f);
-                    store_split(a_hi, a_lo, r, half * 8 + cc, v);
-                }
+                for (int e = 0; e < 4; ++e) v[e] = fmaxf(acc[cc * 4 + e] + small.ba2[half * 32 + cc * 4 + e], 0.0f);
+                store_split(a_hi, a_lo, r, half * 8 + cc, v);
             }
         } else {
-            // discrete: e = relu(Wa1[:,0] * float(a) + ba1), 64 wide (model.py:319-320)
-            const float av = (float)static_cast<const int64_t *>(a.a_mu)[cc_idx];
-#pragma unroll 1
-            for (int cc = 0; cc < AQL_H / 4; ++cc) {
+            // discrete: e = relu(Wa1[:,0] * float(a) + ba1), 64 wide (model.py:319-320); 32 outputs per thread
+            const float av = (float)static_cast<const int64_t *>(a.a_mu)[ci];
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    const int o = cc * 4 + e;
-                    v[e] = fmaxf(fmaf(a.small->wa1[o], av, a.small->ba1[o]), 0.0f);
+                    const int o = half * 32 + cc * 4 + e;
+                    v[e] = fmaxf(fmaf(small.wa1[o], av, small.ba1[o]), 0.0f);
                 }
-                store_split(a_hi, a_lo, r, cc, v);
+                store_split(a_hi, a_lo, r, half * 8 + cc, v);
             }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
-        if (r == 0) {
+        if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             issue_3xtf32(d3, smem_u32(a_hi), smem_u32(a_lo), smem_u32(sm + AQL_IMG_W1_HI), smem_u32(sm + AQL_IMG_W1_LO), 2);
             umma_commit(smem_u32(bar_m));
@@ -278,21 +277,28 @@ __global__ void __launch_bounds__(AQL_TILE, 1) k_aql_q(AqlArgs a) {
         mbar_wait(smem_u32(bar_m), phase);
         phase ^= 1u;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // layer 3 epilogue: q = w2 . relu(D3 + sv_b) + b2
-        const float *svb = a.sv + (cc_idx / a.K) * AQL_H;
+        // layer 3 epilogue: q = w2 . relu(D3 + sv_b) + b2; each thread sums its 32 columns
+        const float4 *svb = reinterpret_cast<const float4 *>(a.sv + (ci / a.K) * AQL_H + half * 32);
         float qv = 0.0f;
-        float acc[32];
-#pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-            tmem_ld32(d3 + my_lane + half * 32, acc);
+        {
+            float acc[32];
+            tmem_ld32(d3 + my_tmem, acc);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) qv = fmaf(s_w2[half * 32 + i], fmaxf(acc[i] + svb[half * 32 + i], 0.0f), qv);
+            for (int i4 = 0; i4 < 8; ++i4) {
+                const float4 s4 = svb[i4];
+                qv = fmaf(small.w2[half * 32 + i4 * 4 + 0], fmaxf(acc[i4 * 4 + 0] + s4.x, 0.0f), qv);
+                qv = fmaf(small.w2[half * 32 + i4 * 4 + 1], fmaxf(acc[i4 * 4 + 1] + s4.y, 0.0f), qv);
+                qv = fmaf(small.w2[half * 32 + i4 * 4 + 2], fmaxf(acc[i4 * 4 + 2] + s4.z, 0.0f), qv);
+                qv = fmaf(small.w2[half * 32 + i4 * 4 + 3], fmaxf(acc[i4 * 4 + 3] + s4.w, 0.0f), qv);
+            }
         }
-        if (live) a.q[c] = qv + b2;
+        if (half) s_part[r] = qv;
         // the next tile overwrites the staging buffers and the accumulators: everyone must be done reading
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
+        if (!half && live) a.q[c] = (qv + s_part[r]) + small.b2;
     }
+    __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128));
 }
 

@@ -682,7 +682,7 @@ int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
 struct aql_plan_s {
     int device, continuous, A, sm_count;
     uint8_t *img;        // swizzled TF32 hi/lo weight image
-    AqlSmall *small;     // small parameters
+    AqlSmall small;      // small parameters (host copy; travels to the kernel as a by-value parameter)
     float *sv;           // [B, 64] state halves
     int64_t sv_cap;
     bool have_weights;
@@ -700,13 +700,11 @@ int aql_create(aql_plan **out, int device, int continuous, int action_dim) {
     p->continuous = continuous ? 1 : 0;
     p->A = continuous ? action_dim : 1;
     cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, device);
-    if (cudaMalloc(&p->img, AQL_IMG_BYTES) != cudaSuccess || cudaMalloc(&p->small, sizeof(AqlSmall)) != cudaSuccess) {
+    if (cudaMalloc(&p->img, AQL_IMG_BYTES) != cudaSuccess) {
         cudaGetLastError();
-        cudaFree(p->img);
         delete p;
         return fail(PER_ERR_NOMEM, "aql_create: cudaMalloc failed");
     }
-    PER_CUDA(cudaFuncSetAttribute(k_aql_q, cudaFuncAttributeMaxDynamicSharedMemorySize, AQL_SMEM_BYTES));
     *out = p;
     return PER_OK;
 }
@@ -715,7 +713,6 @@ int aql_destroy(aql_plan *p) {
     if (!p) return PER_OK;
     DeviceGuard g(p->device);
     cudaFree(p->img);
-    cudaFree(p->small);
     cudaFree(p->sv);
     delete p;
     return PER_OK;
@@ -728,14 +725,13 @@ int aql_set_weights(aql_plan *p, const float *d_wa1, const float *d_ba1, const f
     DeviceGuard g(p->device);
     cudaStream_t s = (cudaStream_t)stream;
     const int e1 = p->continuous ? AQL_E1 : AQL_H;
-    char *sm = reinterpret_cast<char *>(p->small);
-    PER_CUDA(cudaMemsetAsync(p->small, 0, sizeof(AqlSmall), s));
-    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, wa1), d_wa1, sizeof(float) * e1 * p->A, cudaMemcpyDeviceToDevice, s));
-    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, ba1), d_ba1, sizeof(float) * e1, cudaMemcpyDeviceToDevice, s));
-    if (p->continuous)
-        PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, ba2), d_ba2, sizeof(float) * AQL_H, cudaMemcpyDeviceToDevice, s));
-    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, w2), d_wadv2, sizeof(float) * AQL_H, cudaMemcpyDeviceToDevice, s));
-    PER_CUDA(cudaMemcpyAsync(sm + offsetof(AqlSmall, b2), d_badv2, sizeof(float), cudaMemcpyDeviceToDevice, s));
+    memset(&p->small, 0, sizeof(AqlSmall));
+    PER_CUDA(cudaMemcpyAsync(p->small.wa1, d_wa1, sizeof(float) * e1 * p->A, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemcpyAsync(p->small.ba1, d_ba1, sizeof(float) * e1, cudaMemcpyDeviceToHost, s));
+    if (p->continuous) PER_CUDA(cudaMemcpyAsync(p->small.ba2, d_ba2, sizeof(float) * AQL_H, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemcpyAsync(p->small.w2, d_wadv2, sizeof(float) * AQL_H, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemcpyAsync(&p->small.b2, d_badv2, sizeof(float), cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaStreamSynchronize(s));  // the small weights ride in the kernel's parameter block from now on
     k_aql_prep_weights<<<(AQL_H * 48 + 127) / 128, 128, 0, s>>>(p->continuous ? d_wa2 : nullptr, d_wadv1, p->img);
     PER_CUDA(cudaGetLastError());
     p->have_weights = true;
@@ -759,17 +755,30 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
     AqlArgs a;
     memset(&a, 0, sizeof a);
     a.img = p->img;
-    a.small = p->small;
     a.sv = p->sv;
     a.a_mu = d_a_mu;
-    a.continuous = p->continuous;
-    a.A = p->A;
     a.K = K;
     a.total = B * K;
     a.q = d_q;
     int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
     int64_t grid = tiles < p->sm_count ? tiles : p->sm_count;
-    k_aql_q<<<(unsigned)grid, AQL_TILE, AQL_SMEM_BYTES, s>>>(a);
+#define AQL_LAUNCH(AA, CC)                                                                                          \
+    do {                                                                                                           \
+        PER_CUDA(cudaFuncSetAttribute(k_aql_q<AA, CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, AQL_SMEM_BYTES)); \
+        k_aql_q<AA, CC><<<(unsigned)grid, AQL_THREADS, AQL_SMEM_BYTES, s>>>(a, p->small);                           \
+    } while (0)
+    if (!p->continuous) AQL_LAUNCH(1, false);
+    else switch (p->A) {
+        case 1: AQL_LAUNCH(1, true); break;
+        case 2: AQL_LAUNCH(2, true); break;
+        case 3: AQL_LAUNCH(3, true); break;
+        case 4: AQL_LAUNCH(4, true); break;
+        case 5: AQL_LAUNCH(5, true); break;
+        case 6: AQL_LAUNCH(6, true); break;
+        case 7: AQL_LAUNCH(7, true); break;
+        default: AQL_LAUNCH(8, true); break;
+    }
+#undef AQL_LAUNCH
     if (d_argmax) k_aql_argmax<<<(unsigned)((B * 32 + 127) / 128), 128, 0, s>>>(d_q, B, K, d_argmax);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
