@@ -577,6 +577,25 @@ class CustomPrioritizedReplayBuffer(PrioritizedReplayBuffer):
         self._stage((state, action, reward, next_state, done), priority)
         self._max_priority = max(self._max_priority, priority)
 
+    def add_chunk(self, states, actions, rewards, next_states, dones, priorities):
+        """Extension: `for i: self.add(states[i], actions[i], rewards[i], next_states[i], dones[i],
+        priorities[i])` for one actor chunk (batchrecorder.py:133-137) as a single upload and
+        launch; same slots, same leaves (libm pow on the host), same running max."""
+        n = len(actions)
+        if n == 0:
+            return
+        self._sync_max_priority()
+        self._ensure_native(states[0])
+        self._flush()
+        pr = np.asarray(priorities, dtype=np.float64)
+        obs = np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in states])
+        nxt = np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in next_states])
+        up = self._host.up
+        self.add_batch_device(up("obs", obs), up("next", nxt), up("act", np.asarray(actions, dtype=np.int64)),
+                              up("rew", np.asarray(rewards, dtype=np.float32)), up("done", np.asarray(dones, dtype=np.float32)),
+                              leaves=up("leaf", _pow_alpha_exact(pr, self._alpha)), batch_max=float(pr.max()))
+        self._max_priority = max(self._max_priority, float(pr.max()))
+
 
 class CustomPrioritizedReplayBuffer_AQL(PrioritizedReplayBuffer):
     """memory.py:364-391: rows carry the K candidate actions `a_mu`; sample returns an 8-tuple."""

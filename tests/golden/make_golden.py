@@ -251,7 +251,42 @@ def gen_td(utl):
     np.savez_compressed(os.path.join(HERE, "td.npz"), **out)
 
 
+def gen_aql():
+    """Q_Network.act (model.py:294-335) of the real reference, continuous and discrete, NoisyLinear
+    in training mode.  model.py imports gym at module level; a two-line stand-in satisfies it
+    (Q_Network itself never touches gym)."""
+    import torch
+    gym = types.ModuleType("gym")
+    gym.spaces = types.SimpleNamespace(Box=type("Box", (), {}))
+    sys.modules.setdefault("gym", gym)
+    model = load_reference("model")
+    out = {}
+    for case, (cont, A, B, K, obs) in enumerate([(True, 2, 6, 45, 9), (False, 7, 5, 33, 4)]):
+        torch.manual_seed(900 + case)
+        net = model.Q_Network(input_shape=(obs,), num_actions=A, total_sample=K, env_iscontinuous=cont, device="cpu")
+        net.train()
+        state = torch.randn(B, obs)
+        a_mu = (torch.rand(B, K, A) * 2 - 1) if cont else torch.randint(0, A, (B, K))
+        with torch.no_grad():
+            _, q = net.act(state, a_mu, 0)
+            f = net.q_feature(state)
+        c = f"c{case}_"
+        out[c + "cont"], out[c + "A"] = cont, A
+        out[c + "f"], out[c + "a_mu"], out[c + "q"] = f.numpy(), a_mu.numpy(), q.numpy()
+        ao = net.action_out
+        out[c + "wa1"], out[c + "ba1"] = ao[0].weight.detach().numpy(), ao[0].bias.detach().numpy()
+        if cont:
+            out[c + "wa2"], out[c + "ba2"] = ao[2].weight.detach().numpy(), ao[2].bias.detach().numpy()
+        for name, layer in (("adv1", net.advantage1), ("adv2", net.advantage2)):
+            out[c + "w" + name] = (layer.weight_mu + layer.weight_sigma * layer.weight_epsilon).detach().numpy()
+            out[c + "b" + name] = (layer.bias_mu + layer.bias_sigma * layer.bias_epsilon).detach().numpy()
+    np.savez_compressed(os.path.join(HERE, "aql.npz"), **out)
+
+
 def main():
+    if "--only-aql" in sys.argv:
+        gen_aql()
+        return
     mem = load_reference("memory")
     mem.np = numpy1_shim()
     rnd = Replay()
@@ -264,6 +299,7 @@ def main():
     gen_nstep(mem)
     utl = load_reference("utils")
     gen_td(utl)
+    gen_aql()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -398,3 +398,30 @@ def test_quirks_and_asserts(memory, monkeypatch):
     for i in range(20):
         fb.add(o, 0, 0.0, o, 0.0, 1.0 + i)
     assert len(fb) == 8 and fb._next_idx == 4 and fb._max_priority == 20.0
+
+
+def test_add_chunk_equals_row_by_row_add(memory):
+    """The batchrecorder ingest path (batchrecorder.py:133-137): one add_chunk per actor chunk must
+    leave the buffer exactly as one add() per transition does, including ring wrap-around."""
+    rng = np.random.default_rng(21)
+    size, n = 300, 470
+    obs = rng.integers(0, 256, size=(n, 4, 84, 84), dtype=np.uint8)
+    nxt = rng.integers(0, 256, size=(n, 4, 84, 84), dtype=np.uint8)
+    act = rng.integers(0, 18, size=n)
+    rew = rng.standard_normal(n)
+    done = (rng.random(n) < 0.1).astype(np.float32)
+    prio = np.abs(rng.standard_normal(n)) + 1e-6
+    a = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    b = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    for i in range(n):
+        a.add(obs[i], int(act[i]), float(rew[i]), nxt[i], float(done[i]), float(prio[i]))
+    for lo in range(0, n, 50):
+        hi = min(n, lo + 50)
+        b.add_chunk(list(obs[lo:hi]), list(act[lo:hi]), list(rew[lo:hi]), list(nxt[lo:hi]), list(done[lo:hi]), prio[lo:hi])
+    assert len(a) == len(b) == size and a._next_idx == b._next_idx == n % size and a._max_priority == b._max_priority
+    assert np.array_equal(bits(a._it_sum._value), bits(b._it_sum._value))
+    assert np.array_equal(bits(a._it_min._value), bits(b._it_min._value))
+    idx = list(range(0, size, 7))
+    ea, eb = a._encode_sample(idx), b._encode_sample(idx)
+    for x, y in zip(ea, eb):
+        assert np.array_equal(x, y)
