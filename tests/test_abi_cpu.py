@@ -23,7 +23,7 @@ def built():
 def declared_functions():
     text = open(os.path.join(ROOT, "include", "per_b200.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b((?:per|seg)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b((?:per|seg|aql|nstep)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_exports_every_declared_symbol():
