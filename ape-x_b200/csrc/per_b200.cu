@@ -35,7 +35,8 @@ struct per_buffer_s {
     TreeRef t;
     u64 *stamps;
     u64 epoch;
-    // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5
+    // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5,
+    // word 3 exchange epoch, word 4 retired-warp counter
     u64 *scal;
     uint8_t *obs, *next, *extra;
     int64_t *act;
@@ -45,6 +46,8 @@ struct per_buffer_s {
     int64_t len, cursor;
     int sm_count;
     GatherTune tune;
+    double *mailbox;           // sharded replay, peer-memory exchange: this rank's mailbox (may be null)
+    double **d_peer_mailbox;   //   device array [n_shards] of all ranks' mailboxes
     double *rec_out;           // sharded replay: record refreshed by every tree-modifying call (may be null)
     int64_t global_len;        //   len(_storage) of the whole replay, as last told by the caller
     int shard_rank, n_shards;  // sharded replay: this buffer is slice shard_rank of n_shards (1: not sharded)
@@ -52,6 +55,8 @@ struct per_buffer_s {
     u64 *status() const { return scal; }
     double *max_prio() const { return reinterpret_cast<double *>(scal + 1); }
     float *td_red() const { return reinterpret_cast<float *>(scal + 2); }
+    u64 *xchg_epoch() const { return scal + 3; }                                   // exchange samples completed
+    unsigned *xchg_done() const { return reinterpret_cast<unsigned *>(scal + 4); }  // retired warps of the running sample
 };
 
 namespace {
@@ -305,7 +310,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
         }                                                                                          \
     } while (0)
     TRY_ALLOC(b->stamps, sizeof(u64) * cap);
-    TRY_ALLOC(b->scal, sizeof(u64) * 4);
+    TRY_ALLOC(b->scal, sizeof(u64) * 8);
     TRY_ALLOC(b->obs, b->obs_stride * ring_size);
     TRY_ALLOC(b->next, b->obs_stride * ring_size);
     TRY_ALLOC(b->extra, b->extra_stride * ring_size);
@@ -316,7 +321,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
-    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 4, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 8, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
@@ -359,6 +364,7 @@ int per_destroy(per_buffer *b) {
     cudaFree(b->rew);
     cudaFree(b->done);
     cudaFree(b->td_scratch);
+    cudaFree(b->d_peer_mailbox);
     delete b;
     return PER_OK;
 }
@@ -464,9 +470,65 @@ int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len)
     return PER_OK;
 }
 
+// ---- CUDA IPC helpers: buffers another process's GPU can write into / read from over NVLink ----
+int per_ipc_alloc(int device, int64_t bytes, void **d_ptr, uint8_t *h_handle64) {
+    if (!d_ptr || !h_handle64 || bytes <= 0) return fail(PER_ERR_ARG, "per_ipc_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "per_ipc_alloc: cannot select device %d", device);
+    PER_CUDA(cudaMalloc(d_ptr, (size_t)bytes));
+    PER_CUDA(cudaMemset(*d_ptr, 0, (size_t)bytes));
+    cudaIpcMemHandle_t hnd;
+    PER_CUDA(cudaIpcGetMemHandle(&hnd, *d_ptr));
+    memcpy(h_handle64, &hnd, 64);
+    return PER_OK;
+}
+
+int per_ipc_open(int device, const uint8_t *h_handle64, void **d_ptr) {
+    if (!d_ptr || !h_handle64) return fail(PER_ERR_ARG, "per_ipc_open: bad argument");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(PER_ERR_CUDA, "per_ipc_open: cannot select device %d", device);
+    cudaIpcMemHandle_t hnd;
+    memcpy(&hnd, h_handle64, 64);
+    PER_CUDA(cudaIpcOpenMemHandle(d_ptr, hnd, cudaIpcMemLazyEnablePeerAccess));
+    return PER_OK;
+}
+
+int per_ipc_close(int device, void *d_ptr) {
+    DeviceGuard g(device);
+    if (d_ptr) PER_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return PER_OK;
+}
+
+int per_ipc_free(int device, void *d_ptr) {
+    DeviceGuard g(device);
+    if (d_ptr) PER_CUDA(cudaFree(d_ptr));
+    return PER_OK;
+}
+
+int per_shard_attach_exchange(per_buffer *b, double *d_mailbox, void *const *h_peer_mailboxes) {
+    if (!b || !d_mailbox || !h_peer_mailboxes) return fail(PER_ERR_ARG, "per_shard_attach_exchange: bad argument");
+    DeviceGuard g(b->device);
+    if (!b->d_peer_mailbox) PER_CUDA(cudaMalloc(&b->d_peer_mailbox, sizeof(double *) * 16));
+    PER_CUDA(cudaMemcpy(b->d_peer_mailbox, h_peer_mailboxes, sizeof(double *) * b->n_shards, cudaMemcpyHostToDevice));
+    b->mailbox = d_mailbox;
+    PER_CUDA(cudaMemset(b->xchg_epoch(), 0, sizeof(u64) * 2));
+    return PER_OK;
+}
+
+int per_shard_publish(per_buffer *b, int64_t global_len, void *stream) {
+    if (!b || !b->mailbox) return fail(PER_ERR_ARG, "per_shard_publish: no exchange attached");
+    DeviceGuard g(b->device);
+    k_shard_publish<<<1, 32, 0, (cudaStream_t)stream>>>(b->t.sum, b->t.mnn, b->t.cap, shard_need(global_len, b->idx_base, b->t.cap),
+                                                        b->len, b->d_peer_mailbox, b->n_shards, b->shard_rank, b->xchg_epoch());
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
 int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch, double beta,
                        int64_t global_len, int64_t *d_out_idx, double *d_out_w64, float *d_out_w32, void *stream) {
-    if (!b || batch <= 0 || !d_u || !d_out_idx || !d_records) return fail(PER_ERR_ARG, "per_sample_sharded: bad argument");
+    if (!b || batch <= 0 || !d_u || !d_out_idx || (!d_records && !b->mailbox))
+        return fail(PER_ERR_ARG, "per_sample_sharded: bad argument");
     if (!(beta > 0)) return fail(PER_ERR_ASSERT, "beta > 0");
     if (global_len < 2) return fail(PER_ERR_ASSERT, "sample needs at least 2 stored transitions");
     DeviceGuard g(b->device);
@@ -487,6 +549,14 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     a.recs = d_records;
     a.n_shards = b->n_shards;
     a.rank = b->shard_rank;
+    if (!d_records) {  // records travel through the peer-memory mailboxes
+        a.mailbox = b->mailbox;
+        a.peer_mailbox = b->d_peer_mailbox;
+        a.d_epoch = b->xchg_epoch();
+        a.d_done = b->xchg_done();
+        a.rec_need = shard_need(global_len, b->idx_base, b->t.cap);
+        a.rec_len = b->len;
+    }
     k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
     PER_CUDA(cudaGetLastError());
     return PER_OK;

@@ -126,9 +126,66 @@ struct SampleArgs {
     const double *recs;    // null: not sharded.  n_shards records {root_sum, root_min, boundary_partial, len}
     int n_shards;          // power of two, <= 16
     int rank;
+    // Record exchange through peer memory instead of a collective (epoch != 0): this kernel
+    // publishes its own record into every rank's mailbox and waits for the others'.
+    double *mailbox;             // this rank's mailbox: [2 parities][n_shards] slots of MAIL_SLOT doubles
+    double *const *peer_mailbox; // device array [n_shards] of the mailboxes of all ranks (peer-mapped)
+    u64 *d_epoch;                // null: no exchange.  Device counter of completed exchange samples; this launch is
+                                 // sample number *d_epoch + 1 (slot parity = that & 1) and bumps it when its last warp retires,
+                                 // so the same captured launch can be replayed from a CUDA graph
+    unsigned *d_done;            // warps of this launch that have retired
+    int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
 };
 
-constexpr int SHARD_REC = 4;  // doubles per shard record
+constexpr int SHARD_REC = 4;   // doubles per shard record
+constexpr int MAIL_SLOT = 8;   // doubles per mailbox slot: record[4], flag (u64 bits), 3 pad  (64 B)
+
+__device__ __forceinline__ u64 global_timer_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// One warp: computes this shard's record and stores it, then the epoch flag, into the slot
+// [epoch & 1][rank] of every rank's mailbox (lane p -> rank p; plain stores to peer-mapped
+// addresses travel over NVLink).  The flag is written after a system-scope fence.
+__device__ __forceinline__ void publish_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
+                                               int64_t len_local, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
+    const int lane = threadIdx.x & 31;
+    double partial = 0.0;
+    if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
+    const double rs = __ldcg(sum + 1), rm = __ldcg(mnn + 1);
+    if (lane < n_shards) {
+        double *slot = peer_mailbox[lane] + ((epoch & 1) * n_shards + rank) * MAIL_SLOT;
+        reinterpret_cast<double2 *>(slot)[0] = make_double2(rs, rm);
+        reinterpret_cast<double2 *>(slot)[1] = make_double2(partial, (double)len_local);
+        __threadfence_system();
+        *reinterpret_cast<volatile u64 *>(slot + SHARD_REC) = epoch;
+    }
+}
+
+// All lanes of the calling warp return once every rank's slot of this epoch has arrived in the
+// local mailbox (or after 2 s, with PER_STATUS_EXCHANGE_TIMEOUT set — never a hang).
+__device__ __forceinline__ void await_records(const double *mailbox, int n_shards, u64 epoch, u64 *status) {
+    const int lane = threadIdx.x & 31;
+    if (lane < n_shards) {
+        const volatile u64 *flag = reinterpret_cast<const volatile u64 *>(mailbox + ((epoch & 1) * n_shards + lane) * MAIL_SLOT + SHARD_REC);
+        const u64 t0 = global_timer_ns();
+        while (*flag < epoch) {
+            if (global_timer_ns() - t0 > 2000000000ull) {
+                atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
+                break;
+            }
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+
+__global__ void k_shard_publish(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
+                                double *const *peer_mailbox, int n_shards, int rank, const u64 *d_epoch) {
+    publish_record(sum, mnn, cap, need_local, len_local, peer_mailbox, n_shards, rank, __ldcg(d_epoch) + 1);
+}
 
 // One record per shard and sample call, all-gathered across ranks: the two roots, and the
 // shard-local part of the reference's  sum(0, len-1)  chain (memory.py:244): the prefix over
@@ -151,20 +208,25 @@ __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap
     write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
-__global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
-    const int lane = threadIdx.x & 31;
-    const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    if (q >= a.batch) return;  // whole warp leaves together
-
+__device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q, const int lane) {
     double mass;
     double root_sum, root_min = 0.0;
     int64_t idx_base = 0;
-    if (a.recs) {
+    if (a.recs || a.d_epoch) {
+        const int N = a.n_shards;
+        const double *recs = a.recs;
+        int rec_stride = SHARD_REC;
+        if (a.d_epoch) {  // exchange through peer memory: publish (first warp of the grid), then wait for all ranks
+            const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
+            if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, N, a.rank, epoch);
+            await_records(a.mailbox, N, epoch, a.status);
+            recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
+            rec_stride = MAIL_SLOT;
+        }
         // Top of the virtual tree, one node per lane: lanes N..2N-1 hold the shard roots,
         // lanes 1..N-1 their pairwise sums built level by level like memory.py:82-87.
-        const int N = a.n_shards;
-        double top = (lane >= N && lane < 2 * N) ? a.recs[(lane - N) * SHARD_REC] : 0.0;
-        double mn = lane < N ? a.recs[lane * SHARD_REC + 1] : __longlong_as_double(0x7ff0000000000000LL);
+        double top = (lane >= N && lane < 2 * N) ? __ldcg(recs + (lane - N) * rec_stride) : 0.0;
+        double mn = lane < N ? __ldcg(recs + lane * rec_stride + 1) : __longlong_as_double(0x7ff0000000000000LL);
         for (int w = N >> 1; w >= 1; w >>= 1) {
             const double l = shfl_f64(top, (2 * lane) & 31), r = shfl_f64(top, (2 * lane + 1) & 31);
             if (lane >= w && lane < 2 * w) top = __dadd_rn(l, r);
@@ -180,7 +242,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         double acc = 0.0;
         bool first = true;
         if (need_lo) {
-            acc = a.recs[need_hi * SHARD_REC + 2];
+            acc = __ldcg(recs + need_hi * rec_stride + 2);
             first = false;
         }
 #pragma unroll 1
@@ -265,6 +327,22 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
             const double w = __ddiv_rn(r, max_w);
             if (a.out_w64) a.out_w64[q] = w;
             if (a.out_w32) a.out_w32[q] = (float)w;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (q < a.batch) sample_one(a, q, lane);  // whole warps take the same side
+    if (a.d_epoch && lane == 0) {
+        // last warp of the launch to retire advances the exchange epoch (every warp has read it by then)
+        __threadfence();
+        const unsigned total = gridDim.x * (blockDim.x >> 5);
+        if (atomicAdd(a.d_done, 1u) == total - 1) {
+            *a.d_done = 0;
+            __threadfence();
+            atomicAdd(a.d_epoch, 1ull);
         }
     }
 }

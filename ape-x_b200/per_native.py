@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libper_b200.so")
 
 PER_OK, PER_ERR_ASSERT, PER_ERR_CUDA, PER_ERR_ARG, PER_ERR_NOMEM = 0, -1, -2, -3, -4
 STATUS_BAD_PRIORITY, STATUS_BAD_INDEX, STATUS_BAD_PREFIXSUM, STATUS_NSTEP_EMPTY = 1, 2, 4, 8
+STATUS_EXCHANGE_TIMEOUT = 16
 TREE_SUM, TREE_MIN = 0, 1
 SEG_NOALLOC_MAX_CAPACITY = 1 << 20
 PRIO_F64, PRIO_F32 = 0, 1
@@ -52,6 +53,12 @@ SIGNATURES = {
     "per_create_shard": (C.c_int, [C.POINTER(_p), C.c_int, _i64, C.c_int, C.c_int, _f64, _i64, _i64]),
     "per_shard_record": (C.c_int, [_p, _i64, _p, _p]),
     "per_shard_attach_record": (C.c_int, [_p, _p, _i64]),
+    "per_ipc_alloc": (C.c_int, [C.c_int, _i64, C.POINTER(_p), _p]),
+    "per_ipc_open": (C.c_int, [C.c_int, _p, C.POINTER(_p)]),
+    "per_ipc_close": (C.c_int, [C.c_int, _p]),
+    "per_ipc_free": (C.c_int, [C.c_int, _p]),
+    "per_shard_attach_exchange": (C.c_int, [_p, _p, _p]),
+    "per_shard_publish": (C.c_int, [_p, _i64, _p]),
     "per_sample_sharded": (C.c_int, [_p, _p, _p, _i64, _f64, _i64, _p, _p, _p, _p]),
     "per_capacity": (_i64, [_p]),
     "per_len": (_i64, [_p]),

@@ -64,6 +64,42 @@ class ShardGeometry(object):
         return out
 
 
+class PeerBuffer(object):
+    """A raw device allocation that other processes' GPUs can map (CUDA IPC): passes for a tensor
+    where the C ABI only needs an address, and exposes __cuda_array_interface__ views."""
+
+    def __init__(self, ptr, nbytes, device, owned):
+        self.ptr, self.nbytes, self.device, self.owned = int(ptr), int(nbytes), int(device), owned
+
+    def data_ptr(self):
+        return self.ptr
+
+    def is_contiguous(self):
+        return True
+
+    def view(self, dtype, shape, offset=0):
+        """torch tensor view (no copy) of `shape` / torch `dtype` at byte `offset`."""
+        typestr = {torch.uint8: "|u1", torch.int64: "<i8", torch.float32: "<f4", torch.float64: "<f8"}[dtype]
+        holder = type("_CAI", (), {})()
+        holder.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (self.ptr + offset, False),
+                                           "version": 2}
+        holder._keep = self
+        return torch.as_tensor(holder, device=torch.device("cuda", self.device))
+
+    @staticmethod
+    def alloc(nbytes, device):
+        p, h = _n.C.c_void_p(), (_n.C.c_uint8 * 64)()
+        _n.check(_n.lib.per_ipc_alloc(int(device), int(nbytes), _n.C.byref(p), h))
+        return PeerBuffer(p.value, nbytes, device, True), bytes(h)
+
+    @staticmethod
+    def open(handle, nbytes, device):
+        p = _n.C.c_void_p()
+        h = (_n.C.c_uint8 * 64).from_buffer_copy(handle)
+        _n.check(_n.lib.per_ipc_open(int(device), h, _n.C.byref(p)))
+        return PeerBuffer(p.value, nbytes, device, False)
+
+
 def exchange_records(rec, group=None):
     """All-gather of one 4-double record per rank (the only collective of a sample)."""
     import torch.distributed as dist
@@ -98,6 +134,7 @@ class ShardedReplay(object):
         self._cursor = 0    # global _next_idx
         self._rec = torch.zeros(REC, dtype=torch.float64, device=self.device)
         self._rec_fresh = False  # True while the record at _rec reflects the current trees and len
+        self._peer_exchange = False
         self._attach()
 
     def __del__(self):
@@ -108,6 +145,40 @@ class ShardedReplay(object):
 
     def __len__(self):
         return self._len
+
+    # -- record exchange through peer memory (no collective in the sampling path) -------------------
+    MAILBOX_BYTES = 2 * 16 * 64
+
+    def enable_peer_exchange(self, group=None):
+        """One-time set-up across processes: every rank allocates a mailbox its peers can write
+        (CUDA IPC over NVLink), the 64-byte handles are all-gathered once, and from then on
+        sample_device() needs no collective: the sampling kernel publishes and awaits the records
+        itself (include/per_b200.h, per_shard_attach_exchange)."""
+        import torch.distributed as dist
+        mine, handle = PeerBuffer.alloc(self.MAILBOX_BYTES, self.device.index)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle, group=group)
+        peers = [mine if r == self.rank else PeerBuffer.open(handles[r], self.MAILBOX_BYTES, self.device.index)
+                 for r in range(self.world)]
+        self._attach_exchange(mine, peers)
+        dist.barrier(group=group)
+
+    def _attach_exchange(self, mine, peers):
+        arr = (_n.C.c_void_p * self.world)(*[p.data_ptr() for p in peers])
+        _n.check(_n.lib.per_shard_attach_exchange(self._h, _n.C.c_void_p(mine.data_ptr()), arr))
+        self._mailbox, self._peer_mailboxes, self._peer_exchange = mine, peers, True
+
+    @staticmethod
+    def enable_local_exchange(shards):
+        """All ranks in ONE process on one GPU (tests): mailboxes are ordinary local buffers.  Since
+        one rank's kernel cannot wait for another's on the same GPU, the caller must run
+        publish_record() on every shard before the shards sample."""
+        boxes = [PeerBuffer.alloc(ShardedReplay.MAILBOX_BYTES, s.device.index)[0] for s in shards]
+        for s in shards:
+            s._attach_exchange(boxes[s.rank], boxes)
+
+    def publish_record(self):
+        _n.check(_n.lib.per_shard_publish(self._h, self._len, _n.stream_ptr()))
 
     def _attach(self):
         """Every tree-changing call rewrites the record for the current whole-replay len."""
@@ -151,9 +222,12 @@ class ShardedReplay(object):
         u = uniforms if torch.is_tensor(uniforms) else torch.as_tensor(np.asarray(uniforms, dtype=np.float64))
         u = u.to(self.device, dtype=torch.float64)
         sp = _n.stream_ptr()
-        if not self._rec_fresh:  # inserts since the last update: recompute; otherwise the update left it current
-            _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
-        recs = self._exchange(self._rec)
+        if self._peer_exchange:
+            recs = None  # the sampling kernel publishes / awaits the records through the mailboxes
+        else:
+            if not self._rec_fresh:  # inserts since the last update: recompute; otherwise the update left it current
+                _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
+            recs = self._exchange(self._rec)
         idx = torch.empty(batch, dtype=torch.int64, device=self.device)
         w32 = torch.empty(batch, dtype=torch.float32, device=self.device)
         w64 = torch.empty(batch, dtype=torch.float64, device=self.device)

@@ -180,7 +180,8 @@ def workload_config(n_gpus):
                         "batch 512 per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions",
             "ring_per_gpu": RING, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
             "sharding": "none" if n_gpus == 1 else "one replay of %d x 2^20 transitions cut into %d contiguous slices; "
-                        "per step one 32-byte-per-rank NCCL all-gather, global stratified batch %d" % (n_gpus, n_gpus, BATCH * n_gpus),
+                        "per step one exchange of a 32-byte record per rank (peer-memory mailboxes written by the sampling kernel over "
+                        "NVLink, or --nccl-exchange), global stratified batch %d" % (n_gpus, n_gpus, BATCH * n_gpus),
             "l2": "inputs (59 GB ring) larger than L2; no flush", "parallelism": "shard%d" % n_gpus}
 
 
@@ -194,6 +195,8 @@ def main():
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eager", action="store_true", help="time plain launches instead of CUDA graphs")
+    ap.add_argument("--nccl-exchange", action="store_true",
+                    help="world > 1: exchange the shard records with an NCCL all-gather (eager launches) instead of peer-memory mailboxes")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -250,6 +253,9 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
+    use_mailbox = shard is not None and not args.nccl_exchange
+    if use_mailbox:
+        shard.enable_peer_exchange()  # CUDA-IPC mailboxes: the sampling kernel exchanges the records itself
     glen = world * ring
     torch.cuda.synchronize()
 
@@ -293,10 +299,23 @@ def main():
     a_rec, a_all = P(shard_rec), P(all_rec)
     # kernels per step: k_sample, k_gather_tma, k_update_cluster (TD fused in front); sharded adds
     # k_shard_record (+ NCCL's all-gather kernel, not ours) and B > 2048 uses the multi-launch update
-    launches_per_step = 3 if world == 1 else 4 + (0 if GB <= 2048 else 9)
+    launches_per_step = 3 if (world == 1 or use_mailbox) else 4
+
+    if use_mailbox:
+        # self-check: records through the mailboxes must give the indices the all-gathered records give
+        pn.check(lib.per_shard_record(h, glen, a_rec, sp))
+        dist.all_gather_into_tensor(all_rec, shard_rec)
+        pn.check(lib.per_sample_sharded(h, a_all, u_ptrs[0], GB, BETA, glen, a_idx, None, a_w32, sp))
+        idx_collective = idx.clone()
+        pn.check(lib.per_sample_sharded(h, None, u_ptrs[0], GB, BETA, glen, a_idx, None, a_w32, sp))
+        torch.cuda.synchronize()
+        assert torch.equal(idx, idx_collective), "peer-memory exchange and NCCL exchange disagree"
+        assert int((idx >= 0).sum().item()) > 0
 
     def step(i, ev=None):
-        if world > 1:  # the one exchange of the path: 32-byte record per rank
+        if use_mailbox:  # the sampling kernel publishes / awaits the 32-byte records over NVLink itself
+            rc = lib.per_sample_sharded(h, None, u_ptrs[i % n_u], GB, BETA, glen, a_idx, None, a_w32, sp)
+        elif world > 1:  # the one exchange of the path as an NCCL all-gather
             rc = lib.per_shard_record(h, glen, a_rec, sp)
             dist.all_gather_into_tensor(all_rec, shard_rec)
             rc |= lib.per_sample_sharded(h, a_all, u_ptrs[i % n_u], GB, BETA, glen, a_idx, None, a_w32, sp)
@@ -344,18 +363,16 @@ def main():
     def enqueue_head(j, sps):  # TD + tree update of the previous batch, record exchange, sample
         rc = lib.per_td_priority_update(*(a_td[:-1] + (sps,)))
         if world > 1:
-            dist.all_gather_into_tensor(all_rec, shard_rec)
-            rc |= lib.per_sample_sharded(h, a_all, u_ptrs[j % n_u], GB, BETA, glen, a_idx, None, a_w32, sps)
+            rc |= lib.per_sample_sharded(h, None, u_ptrs[j % n_u], GB, BETA, glen, a_idx, None, a_w32, sps)
         else:
             rc |= lib.per_sample_indices(h, u_ptrs[j % n_u], GB, BETA, a_idx, None, a_w32, sps)
         if rc:
             pn.check(rc)
 
-    # (capturing torch's NCCL all-gather inside the graph hung on 2 GPUs in round 1, so world > 1 stays on eager launches)
-    if not args.eager and world == 1:
+    # (capturing torch's NCCL all-gather inside a graph hung on 2 GPUs in round 1; with the mailbox exchange the
+    # step is kernels only, so world > 1 is captured too)
+    if not args.eager and (world == 1 or use_mailbox):
         try:
-            if shard is not None:
-                pn.check(lib.per_shard_attach_record(h, a_rec, glen))  # update kernels refresh the record themselves
             side = torch.cuda.Stream()
             side.wait_stream(stream)
             with torch.cuda.stream(side):

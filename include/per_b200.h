@@ -45,6 +45,7 @@ extern "C" {
 #define PER_STATUS_BAD_INDEX      2   /* idx outside [0, len)      (memory.py:316, :90) */
 #define PER_STATUS_BAD_PREFIXSUM  4   /* mass outside [0, sum+1e-5] (memory.py:121) */
 #define PER_STATUS_NSTEP_EMPTY    8   /* done arrived on an empty n-step window (IndexError at memory.py:417) */
+#define PER_STATUS_EXCHANGE_TIMEOUT 16 /* a peer's shard record did not arrive within 2 s (sharded replay) */
 
 #define PER_TREE_SUM 0
 #define PER_TREE_MIN 1
@@ -273,6 +274,27 @@ int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len)
 int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch,
                        double beta, int64_t global_len, int64_t *d_out_idx, double *d_out_w64,
                        float *d_out_w32, void *stream);
+
+/* Record exchange WITHOUT a collective.  Each rank owns a mailbox of 2 * n_shards * 64 bytes in
+ * memory its peers can write (per_ipc_alloc in one process, per_ipc_open in the others; NVLink
+ * peer access).  After per_shard_attach_exchange, per_sample_sharded may be called with
+ * d_records == NULL: the sampling kernel's first warp then computes this shard's record, stores
+ * it into every rank's mailbox (plain stores to peer-mapped addresses + a system-scope fence +
+ * an epoch flag), and every warp waits for the n_shards flags of this sample before it descends
+ * — compute and exchange in ONE kernel, no NCCL launch, capturable in a CUDA graph.  Slots are
+ * double-buffered by sample parity (a rank can be at most one sample ahead of its slowest peer,
+ * because its next sample needs that peer's next record).  A peer that never publishes does not
+ * hang the kernel: after 2 s PER_STATUS_EXCHANGE_TIMEOUT is set and the sample proceeds.
+ * h_peer_mailboxes: host array of n_shards device pointers, entry r = rank r's mailbox as mapped
+ * in THIS process (entry `rank` = d_mailbox).  Every rank must call per_sample_sharded the same
+ * number of times.  per_shard_publish publishes the record for the NEXT sample by itself (used to
+ * emulate several ranks on one GPU, where one rank's kernel cannot wait for another's). */
+int per_ipc_alloc(int device, int64_t bytes, void **d_ptr, uint8_t *h_handle64);
+int per_ipc_open(int device, const uint8_t *h_handle64, void **d_ptr);
+int per_ipc_close(int device, void *d_ptr);
+int per_ipc_free(int device, void *d_ptr);
+int per_shard_attach_exchange(per_buffer *b, double *d_mailbox, void *const *h_peer_mailboxes);
+int per_shard_publish(per_buffer *b, int64_t global_len, void *stream);
 
 /* Launch-shape knobs of the gather kernel, for the sweeps under profiles/ (not needed in
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies

@@ -138,3 +138,37 @@ def test_sharded_fused_td_update(mods):
     sv = single._it_sum._value
     for r, s in enumerate(shards):
         assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_peer_mailbox_exchange_matches_collective(mods, world):
+    """The record exchange through mailboxes (per_shard_attach_exchange) must give the same
+    indices as the all-gathered records.  Ranks share one GPU here, so every rank publishes with
+    per_shard_publish before any of them samples (on separate GPUs the sampling kernel does both)."""
+    memory, sharded, pn = mods
+    size, batch = 6000, 512
+    data = make_data(size, (2, 8), 11 + world)
+    single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    single.add_batch_device(*data[:5], priorities=data[5])
+    shards = [sharded.ShardedReplay(size, 0.6, r, world, obs_shape=(2, 8), exchange=None) for r in range(world)]
+    for s in shards:
+        s.add_batch_device(*data)
+    sharded.ShardedReplay.enable_local_exchange(shards)
+    rng = np.random.default_rng(5)
+    for step in range(4):  # several epochs: both mailbox parities, flags from earlier epochs left behind
+        u = rng.random(batch)
+        want = single.sample_device(batch, 0.4, uniforms=u, gather=False)
+        for s in shards:
+            s.publish_record()
+        merged = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        for s in shards:
+            d = s.sample_device(batch, 0.4, u, gather=False)
+            mine = d["idx"] >= 0
+            merged[mine] = d["idx"][mine]
+            assert s.status() == 0  # in particular no exchange timeout
+        assert torch.equal(merged, want["idx"])
+        newp = torch.rand(batch, device="cuda") + 1e-3
+        single.update_priorities_device(want["idx"], newp)
+        for s in shards:
+            own = torch.where((merged // s.tree_capacity_local) == s.rank, merged, torch.full_like(merged, -1))
+            s.update_priorities_device(own, newp)
