@@ -47,6 +47,7 @@ struct GatherArgs {
     int stages;  // TMA ring depth per warp
     int64_t idx_base;  // sharded replay: global index of this shard's row 0
     int skip_foreign;  // sharded replay: idx == -1 = another shard's row, skipped silently
+    const u64 *range;  // sharded replay: owned strata of the last sample (see owned_range); null = all queries
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -93,9 +94,10 @@ struct Piece {
     uint8_t *dst;
     uint32_t bytes;
 };
-__device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, int per_query) {
+__device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, int per_query, int64_t first_q = 0) {
     int64_t q = w / per_query;
     int r = (int)(w - q * per_query);
+    q += first_q;
     int c = 0;
     while (r >= a.rc[c].pieces) {
         r -= a.rc[c].pieces;
@@ -121,9 +123,22 @@ __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, in
     return p;
 }
 
-__device__ __forceinline__ void gather_scalars(const GatherArgs &a) {
+__device__ __forceinline__ void gather_range(const GatherArgs &a, int64_t &first, int64_t &last) {
+    first = 0;
+    last = a.batch;
+    if (!a.range) return;
+    const u64 epoch = __ldcg(a.range), tl = __ldcg(a.range + 2), th = __ldcg(a.range + 3);
+    if ((tl >> 32) != (epoch & 0xffffffffu) || (th >> 32) != (epoch & 0xffffffffu)) {
+        first = last = 0;
+        return;
+    }
+    first = (int64_t)(0xffffffffu - (unsigned)(tl & 0xffffffffu));
+    last = (int64_t)(th & 0xffffffffu);
+}
+
+__device__ __forceinline__ void gather_scalars(const GatherArgs &a, int64_t first, int64_t last) {
     // scalar columns (action / reward / done): plain coalesced loads, all threads
-    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < a.batch; q += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t q = first + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < last; q += (int64_t)gridDim.x * blockDim.x) {
         int64_t k = a.idx[q];
         if (a.skip_foreign && k == -1) continue;  // another shard's row
         k -= a.idx_base;
@@ -140,7 +155,9 @@ __device__ __forceinline__ void gather_scalars(const GatherArgs &a) {
 // Dynamic shared memory: [warps*stages mbarriers, padded to 128 B][warps*stages pieces].
 __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs a, int per_query) {
     extern __shared__ __align__(128) uint8_t g_smem[];
-    gather_scalars(a);
+    int64_t first_q, last_q;
+    gather_range(a, first_q, last_q);
+    gather_scalars(a, first_q, last_q);
     if (per_query == 0) return;
 
     const int warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
@@ -152,21 +169,21 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
     for (int s = 0; s < NS; ++s) mbar_init(bar0 + 8u * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 
-    const int64_t total = a.batch * per_query;
+    const int64_t total = (last_q - first_q) * per_query;
     const int64_t first = (int64_t)blockIdx.x * warps + warp;
     const int64_t stride = (int64_t)gridDim.x * warps;
     const int64_t mine = first < total ? (total - first + stride - 1) / stride : 0;
 
     // prologue: fill the ring
     for (int64_t i = 0; i < NS && i < mine; ++i) {
-        Piece p = decode_piece(a, first + i * stride, per_query);
+        Piece p = decode_piece(a, first + i * stride, per_query, first_q);
         mbar_expect_tx(bar0 + 8u * (uint32_t)i, p.bytes);  // 0 bytes (skipped row): the phase completes at once
         if (p.bytes) bulk_g2s(buf0 + (uint32_t)i * (uint32_t)a.piece, p.src, p.bytes, bar0 + 8u * (uint32_t)i);
     }
     int s = 0;
     uint32_t parity = 0;
     for (int64_t i = 0; i < mine; ++i) {
-        Piece p = decode_piece(a, first + i * stride, per_query);
+        Piece p = decode_piece(a, first + i * stride, per_query, first_q);
         mbar_wait(bar0 + 8u * s, parity);
         if (p.bytes) bulk_s2g(p.dst, buf0 + (uint32_t)s * (uint32_t)a.piece, p.bytes);
         bulk_commit();
@@ -174,7 +191,7 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
         if (i >= 1 && i - 1 + NS < mine) {
             bulk_wait_read<1>();  // all but the newest store have finished reading shared memory
             const int sp = s == 0 ? NS - 1 : s - 1;
-            Piece n = decode_piece(a, first + (i - 1 + NS) * stride, per_query);
+            Piece n = decode_piece(a, first + (i - 1 + NS) * stride, per_query, first_q);
             mbar_expect_tx(bar0 + 8u * sp, n.bytes);
             if (n.bytes) bulk_g2s(buf0 + (uint32_t)sp * (uint32_t)a.piece, n.src, n.bytes, bar0 + 8u * sp);
         }
@@ -195,13 +212,15 @@ __device__ __forceinline__ void st_stream(int4 *p, const int4 &v) {
 }
 
 __global__ void __launch_bounds__(256) k_gather_ldg(GatherArgs a, int per_query) {
-    gather_scalars(a);
+    int64_t first_q, last_q;
+    gather_range(a, first_q, last_q);
+    gather_scalars(a, first_q, last_q);
     if (per_query == 0) return;
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int64_t total = a.batch * per_query;
+    const int64_t total = (last_q - first_q) * per_query;
     for (int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; w < total; w += warps) {
-        Piece p = decode_piece(a, w, per_query);
+        Piece p = decode_piece(a, w, per_query, first_q);
         const int4 *src = reinterpret_cast<const int4 *>(p.src);
         int4 *dst = reinterpret_cast<int4 *>(p.dst);
         const int nv = (int)(p.bytes >> 4);

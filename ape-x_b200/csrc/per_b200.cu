@@ -36,7 +36,7 @@ struct per_buffer_s {
     u64 *stamps;
     u64 epoch;
     // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5,
-    // word 3 exchange epoch, word 4 retired-warp counter
+    // word 3 sharded-sample epoch, word 4 retired-warp counter, words 5-6 owned-strata range tags
     u64 *scal;
     uint8_t *obs, *next, *extra;
     int64_t *act;
@@ -46,6 +46,8 @@ struct per_buffer_s {
     int64_t len, cursor;
     int sm_count;
     GatherTune tune;
+    const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
+    int64_t last_sample_batch;       //   update calls that pass the same buffer visit only the strata this shard owns
     double *mailbox;           // sharded replay, peer-memory exchange: this rank's mailbox (may be null)
     double **d_peer_mailbox;   //   device array [n_shards] of all ranks' mailboxes
     double *rec_out;           // sharded replay: record refreshed by every tree-modifying call (may be null)
@@ -549,14 +551,18 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     a.recs = d_records;
     a.n_shards = b->n_shards;
     a.rank = b->shard_rank;
+    a.d_epoch = b->xchg_epoch();
+    a.d_done = b->xchg_done();
+    a.d_range = b->scal + 5;
     if (!d_records) {  // records travel through the peer-memory mailboxes
+        a.use_mailbox = 1;
         a.mailbox = b->mailbox;
         a.peer_mailbox = b->d_peer_mailbox;
-        a.d_epoch = b->xchg_epoch();
-        a.d_done = b->xchg_done();
         a.rec_need = shard_need(global_len, b->idx_base, b->t.cap);
         a.rec_len = b->len;
     }
+    b->last_sample_idx = d_out_idx;
+    b->last_sample_batch = batch;
     k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
@@ -609,6 +615,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.status = slow.status = b->status();
     a.idx_base = slow.idx_base = b->idx_base;
     a.skip_foreign = slow.skip_foreign = b->n_shards > 1;
+    a.range = (b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
     a.piece = slow.piece = tn.piece;
     a.stages = slow.stages = tn.stages;
     const int64_t items = batch * per_query;
@@ -669,6 +676,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.rec_out = b->rec_out;
     a.rec_need = shard_need(b->global_len, b->idx_base, b->t.cap);
     a.rec_len = b->len;
+    a.range = (b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch) ? b->scal + 3 : nullptr;
     return run_update(a, td, 0, b->sm_count, s);
 }
 

@@ -134,6 +134,8 @@ struct SampleArgs {
                                  // sample number *d_epoch + 1 (slot parity = that & 1) and bumps it when its last warp retires,
                                  // so the same captured launch can be replayed from a CUDA graph
     unsigned *d_done;            // warps of this launch that have retired
+    u64 *d_range;                // {lo tag, hi tag}: strata owned by this shard in this sample (see owned_range)
+    int use_mailbox;             // 1: exchange through the mailboxes; 0: records come in `recs`
     int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
 };
 
@@ -212,12 +214,12 @@ __device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q,
     double mass;
     double root_sum, root_min = 0.0;
     int64_t idx_base = 0;
-    if (a.recs || a.d_epoch) {
+    if (a.n_shards) {
         const int N = a.n_shards;
         const double *recs = a.recs;
         int rec_stride = SHARD_REC;
-        if (a.d_epoch) {  // exchange through peer memory: publish (first warp of the grid), then wait for all ranks
-            const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
+        const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
+        if (a.use_mailbox) {  // exchange through peer memory: publish (first warp of the grid), then wait for all ranks
             if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, N, a.rank, epoch);
             await_records(a.mailbox, N, epoch, a.status);
             recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
@@ -275,6 +277,10 @@ __device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q,
             return;
         }
         idx_base = (int64_t)a.rank * a.cap;
+        if (lane == 0) {  // record the range of strata this shard owns (they are contiguous: masses are sorted)
+            atomicMax(a.d_range, (epoch << 32) | (u64)(0xffffffffu - (unsigned)q));
+            atomicMax(a.d_range + 1, (epoch << 32) | (u64)(q + 1));
+        }
     } else {
         root_sum = a.sum[1];
         if (a.direct_mass) {

@@ -63,7 +63,24 @@ struct UpdArgs {
     double *rec_out;          // sharded replay: refresh this shard's 4-double record after the update (may be null)
     int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
     int64_t rec_len;          //   local len
+    const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
+                              // the strata [lo, hi) that this shard owns are visited (null: all n items)
 };
+
+// Owned strata of the last sharded sample: tags are (epoch << 32) | value, written with atomicMax
+// by the sampling kernel (lo is stored as 0xffffffff - lo), valid only if their epoch is current.
+__device__ __forceinline__ void owned_range(const u64 *range, int64_t n, int &lo, int &hi) {
+    lo = 0;
+    hi = (int)n;
+    if (!range) return;
+    const u64 epoch = __ldcg(range), tl = __ldcg(range + 2), th = __ldcg(range + 3);
+    if ((tl >> 32) != (epoch & 0xffffffffu) || (th >> 32) != (epoch & 0xffffffffu)) {
+        lo = hi = 0;  // this shard owned no stratum of that sample
+        return;
+    }
+    lo = (int)(0xffffffffu - (unsigned)(tl & 0xffffffffu));
+    hi = (int)(th & 0xffffffffu);
+}
 
 constexpr int64_t IDX_SKIP = INT64_MIN;
 
@@ -196,17 +213,24 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     const int rank = (int)cl.block_rank();
     const int T = blockDim.x, tid = threadIdx.x;
     const int nwarp = (T + 31) >> 5;
-    const int n = (int)a.n;
+    int first, last;  // items this launch visits: all of them, or the strata this shard owns
+    owned_range(a.range, a.n, first, last);
+    const int n = last - first;
     const int per = (n + ncta - 1) / ncta;  // slice of this CTA: items [lo, hi)
-    const int lo = rank * per < n ? rank * per : n;
-    const int hi = lo + per < n ? lo + per : n;
+    const int lo = first + (rank * per < n ? rank * per : n);
+    const int hi = lo + per < last ? lo + per : last;
     const int cnt = hi - lo;
 
-    if (fused_td) {  // a.n == td.batch: rows are partitioned like the items
+    if (fused_td) {  // rows of the WHOLE batch (the max is batch-wide), partitioned over the CTAs
         float *f_red = reinterpret_cast<float *>(s_red);
         float *s_q = s_raw;  // staged q_next rows of the slice
         float *s_td = s_tdv;
         const int nA = (int)td.nA;
+        const int nb = (int)td.batch;
+        const int tper = (nb + ncta - 1) / ncta;
+        const int lo = rank * tper < nb ? rank * tper : nb;  // shadows the item slice inside this block
+        const int hi = lo + tper < nb ? lo + tper : nb;
+        const int cnt = hi - lo;
         const bool staged = (int64_t)cnt * nA <= UPD_STAGE_FLOATS;
         if (staged) {
             const float *src = td.q_next + (int64_t)lo * nA;
@@ -257,11 +281,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             td.out_prio[lo + i] = td_prio(x, mx);
             if (td.out_td) td.out_td[lo + i] = x;
         }
-        if (skip_update) {
-            cl.sync();  // CTA 0's shared memory stays alive until every CTA has read it
-            return;
-        }
-        __syncthreads();  // this CTA's out_prio slice is read back below; s_k / s_tree are reused
+        cl.sync();  // out_prio is complete (items below may read another CTA's rows); CTA 0's s_clu may go
+        if (skip_update) return;
     }
 
     // phase 1

@@ -270,7 +270,11 @@ int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len)
  * strata through the top log2(n_shards) levels (built from the gathered roots with the
  * reference's pairwise order), keeps the strata that land in its slice and finishes them on
  * its local tree.  d_out_idx[i] = global index, or -1 if stratum i belongs to another shard
- * (weights 0 there).  The union over ranks equals the single-tree result bit for bit. */
+ * (weights 0 there).  The union over ranks equals the single-tree result bit for bit.
+ * The strata a shard owns are contiguous (masses ascend), and the kernel leaves their range
+ * on the device: per_gather / per_update_* / per_td_priority_update calls that are handed the
+ * SAME d_out_idx buffer and batch then visit only that range instead of skipping -1 entries one
+ * by one, so per-rank work stays proportional to the rank's share of the batch. */
 int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch,
                        double beta, int64_t global_len, int64_t *d_out_idx, double *d_out_w64,
                        float *d_out_w32, void *stream);
