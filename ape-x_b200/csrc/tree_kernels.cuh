@@ -172,11 +172,14 @@ __device__ __forceinline__ void await_records(const double *mailbox, int n_shard
     const int lane = threadIdx.x & 31;
     if (lane < n_shards) {
         const volatile u64 *flag = reinterpret_cast<const volatile u64 *>(mailbox + ((epoch & 1) * n_shards + lane) * MAIL_SLOT + SHARD_REC);
-        const u64 t0 = global_timer_ns();
-        while (*flag < epoch) {
-            if (global_timer_ns() - t0 > 2000000000ull) {
-                atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
-                break;
+        if (*flag < epoch) {
+            const u64 t0 = global_timer_ns();
+            while (*flag < epoch) {
+                __nanosleep(100);  // back off: thousands of pollers on one L2 line delay the very write they wait for
+                if (global_timer_ns() - t0 > 2000000000ull) {
+                    atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
+                    break;
+                }
             }
         }
     }
@@ -210,7 +213,7 @@ __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap
     write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
-__device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q, const int lane) {
+__device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q, const int lane, const u64 epoch) {
     double mass;
     double root_sum, root_min = 0.0;
     int64_t idx_base = 0;
@@ -218,10 +221,7 @@ __device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q,
         const int N = a.n_shards;
         const double *recs = a.recs;
         int rec_stride = SHARD_REC;
-        const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
-        if (a.use_mailbox) {  // exchange through peer memory: publish (first warp of the grid), then wait for all ranks
-            if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, N, a.rank, epoch);
-            await_records(a.mailbox, N, epoch, a.status);
+        if (a.use_mailbox) {  // the records of this epoch are in the mailbox (k_sample waited for them)
             recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
             rec_stride = MAIL_SLOT;
         }
@@ -340,7 +340,18 @@ __device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q,
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    if (q < a.batch) sample_one(a, q, lane);  // whole warps take the same side
+    u64 epoch = 0;
+    if (a.n_shards) {
+        epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
+        if (a.use_mailbox) {
+            // exchange through peer memory: the first warp of the grid publishes this shard's record to every
+            // rank, one warp per CTA waits for all ranks' records of this epoch, the CTA barrier releases the rest
+            if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
+            if ((threadIdx.x >> 5) == 0) await_records(a.mailbox, a.n_shards, epoch, a.status);
+            __syncthreads();
+        }
+    }
+    if (q < a.batch) sample_one(a, q, lane, epoch);  // whole warps take the same side
     if (a.d_epoch && lane == 0) {
         // last warp of the launch to retire advances the exchange epoch (every warp has read it by then)
         __threadfence();

@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--eager", action="store_true", help="time plain launches instead of CUDA graphs")
+    ap.add_argument("--trace", action="store_true", help="also print per-call GPU time of sample / gather / update (eager, events)")
     ap.add_argument("--nccl-exchange", action="store_true",
                     help="world > 1: exchange the shard records with an NCCL all-gather (eager launches) instead of peer-memory mailboxes")
     args = ap.parse_args()
@@ -345,6 +346,29 @@ def main():
     for i in range(W):
         step(i)
     barrier()
+
+    if args.trace:  # diagnostic: events between the three calls of a step
+        n_tr = 200
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(n_tr)]
+        for i in range(n_tr):
+            evs[i][0].record(stream)
+            if use_mailbox:
+                lib.per_sample_sharded(h, None, u_ptrs[i % n_u], GB, BETA, glen, a_idx, None, a_w32, sp)
+            elif world > 1:
+                lib.per_shard_record(h, glen, a_rec, sp)
+                dist.all_gather_into_tensor(all_rec, shard_rec)
+                lib.per_sample_sharded(h, a_all, u_ptrs[i % n_u], GB, BETA, glen, a_idx, None, a_w32, sp)
+            else:
+                lib.per_sample_indices(h, u_ptrs[i % n_u], GB, BETA, a_idx, None, a_w32, sp)
+            evs[i][1].record(stream)
+            lib.per_gather(*a_gather)
+            evs[i][2].record(stream)
+            lib.per_td_priority_update(*a_td)
+            evs[i][3].record(stream)
+        barrier()
+        tr = [float(np.median([e[k].elapsed_time(e[k + 1]) for e in evs[20:]])) * 1e3 for k in range(3)]
+        sys.stderr.write("rank %d trace (us, median): sample %.1f  gather %.1f  td+update %.1f  own rows %d\n"
+                         % (rank, tr[0], tr[1], tr[2], int((idx >= 0).sum().item())))
 
     # ---- CUDA graphs for the launch-bound loop ----------------------------------------------
     # The step is four small launches, so plain Python launches are CPU-bound.  Timed region =
