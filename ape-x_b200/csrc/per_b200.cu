@@ -312,7 +312,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
         }                                                                                          \
     } while (0)
     TRY_ALLOC(b->stamps, sizeof(u64) * cap);
-    TRY_ALLOC(b->scal, sizeof(u64) * 8);
+    TRY_ALLOC(b->scal, sizeof(u64) * 16);
     TRY_ALLOC(b->obs, b->obs_stride * ring_size);
     TRY_ALLOC(b->next, b->obs_stride * ring_size);
     TRY_ALLOC(b->extra, b->extra_stride * ring_size);
@@ -323,7 +323,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
-    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 8, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 16, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
@@ -518,6 +518,15 @@ int per_shard_attach_exchange(per_buffer *b, double *d_mailbox, void *const *h_p
     return PER_OK;
 }
 
+int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream) {
+    if (!b || !h_out3) return fail(PER_ERR_ARG, "per_shard_exchange_stats: bad argument");
+    DeviceGuard g(b->device);
+    PER_CUDA(cudaMemcpyAsync(h_out3, b->scal + 8, sizeof(u64) * 3, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PER_CUDA(cudaMemsetAsync(b->scal + 8, 0, sizeof(u64) * 3, (cudaStream_t)stream));
+    PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return PER_OK;
+}
+
 int per_shard_publish(per_buffer *b, int64_t global_len, void *stream) {
     if (!b || !b->mailbox) return fail(PER_ERR_ARG, "per_shard_publish: no exchange attached");
     DeviceGuard g(b->device);
@@ -556,6 +565,7 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     a.d_range = b->scal + 5;
     if (!d_records) {  // records travel through the peer-memory mailboxes
         a.use_mailbox = 1;
+        a.d_wait_stats = b->scal + 8;
         a.mailbox = b->mailbox;
         a.peer_mailbox = b->d_peer_mailbox;
         a.rec_need = shard_need(global_len, b->idx_base, b->t.cap);

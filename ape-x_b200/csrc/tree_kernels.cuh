@@ -136,6 +136,7 @@ struct SampleArgs {
     unsigned *d_done;            // warps of this launch that have retired
     u64 *d_range;                // {lo tag, hi tag}: strata owned by this shard in this sample (see owned_range)
     int use_mailbox;             // 1: exchange through the mailboxes; 0: records come in `recs`
+    u64 *d_wait_stats;           // {waits, total ns, max ns} spent by CTA 0 between kernel start and the last record's arrival
     int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
 };
 
@@ -346,8 +347,15 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         if (a.use_mailbox) {
             // exchange through peer memory: the first warp of the grid publishes this shard's record to every
             // rank, one warp per CTA waits for all ranks' records of this epoch, the CTA barrier releases the rest
+            const u64 t0 = (q == 0 && lane == 0) ? global_timer_ns() : 0;
             if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
             if ((threadIdx.x >> 5) == 0) await_records(a.mailbox, a.n_shards, epoch, a.status);
+            if (q == 0 && lane == 0 && a.d_wait_stats) {
+                const u64 dt = global_timer_ns() - t0;
+                atomicAdd(a.d_wait_stats, 1ull);
+                atomicAdd(a.d_wait_stats + 1, dt);
+                atomicMax(a.d_wait_stats + 2, dt);
+            }
             __syncthreads();
         }
     }

@@ -265,16 +265,22 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
         }
         cl.sync();
-        {
+        if (tid < 32) {
+            // one warp per CTA fetches the per-CTA partials from CTA 0 (DSMEM moves ~17 B/cycle: 4096 threads
+            // reading them all would cost microseconds) and leaves the batch max in local shared memory
             const float *home = cl.map_shared_rank(s_clu, 0);
-            mx = 0.0f;
-            for (int r = 0; r < ncta; ++r) mx = fmaxf(mx, home[r]);
-            if (td.out_loss && rank == 0 && tid == 0) {
-                float l = 0.0f;
-                for (int r = 0; r < ncta; ++r) l += home[UPD_MAX_CTAS + r];  // fixed order: deterministic
-                td.out_loss[0] = l / (float)td.batch;                         // .mean(), utils.py:80
+            float m = tid < ncta ? home[tid] : 0.0f;
+            float l = tid < ncta ? home[UPD_MAX_CTAS + tid] : 0.0f;
+            m = warp_max_f32(m);
+            if (tid == 0) f_red[32] = m;
+            if (td.out_loss && rank == 0) {
+                float acc_l = 0.0f;
+                for (int r = 0; r < ncta; ++r) acc_l += __shfl_sync(0xffffffffu, l, r);  // fixed order: deterministic
+                if (tid == 0) td.out_loss[0] = acc_l / (float)td.batch;               // .mean(), utils.py:80
             }
         }
+        __syncthreads();
+        mx = f_red[32];
 #pragma unroll 1
         for (int i = tid; i < cnt; i += T) {
             const float x = s_td[i];

@@ -456,8 +456,15 @@ def main():
     # ---- timed region: K steps, CUDA events on the launching stream --------------------------
     sampler = ClockSampler(local_rank)
     sampler.start()
+    if use_mailbox:
+        pn.check(lib.per_shard_exchange_stats(h, (pn.C.c_int64 * 3)(), sp))  # clear
     ms, gather_ms = timed(K, graphs is not None)
     clocks = sampler.stop()
+    exchange_us = None
+    if use_mailbox:
+        st3 = (pn.C.c_int64 * 3)()
+        pn.check(lib.per_shard_exchange_stats(h, st3, sp))
+        exchange_us = {"mean": st3[1] / max(st3[0], 1) / 1e3, "max": st3[2] / 1e3, "samples": int(st3[0])}
     value = GB * K / (ms * 1e-3)
     rows_this_rank = int((idx >= 0).sum().item())
     status = pn.C.c_int64(0)
@@ -542,6 +549,7 @@ def main():
                          "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3},
             "cpu_baseline": cpu, "launch": launch_mode, "value_eager_launches": eager_value,
             "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
+            "record_exchange_us": exchange_us,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -299,6 +299,10 @@ int per_ipc_close(int device, void *d_ptr);
 int per_ipc_free(int device, void *d_ptr);
 int per_shard_attach_exchange(per_buffer *b, double *d_mailbox, void *const *h_peer_mailboxes);
 int per_shard_publish(per_buffer *b, int64_t global_len, void *stream);
+/* Reads and clears {exchanges, total ns, max ns} that the sampling kernel's first CTA spent
+ * between its start and the arrival of the last peer record (publish + NVLink + skew between
+ * ranks).  Synchronises `stream`.  Diagnostics for profiles/. */
+int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
 
 /* Launch-shape knobs of the gather kernel, for the sweeps under profiles/ (not needed in
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies

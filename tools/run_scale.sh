@@ -8,7 +8,7 @@ import json
 for l in open("gpurun_out/bench_$TAG.log"):
     if l.startswith("{"):
         d = json.loads(l)
-        print("N=%d value=%.3g eager=%s us/step=%.1f gather_frac=%.3f e2e=%.3g launch=%s" % (d["n_gpus"], d["value"], d["value_eager_launches"], 1e3 * d["ms_per_step"], d["roofline"]["frac"], d["e2e"]["value"], d["launch"][:30]))
+        print("N=%d value=%.3g eager=%s us/step=%.1f gather_frac=%.3f e2e=%.3g launch=%s" % (d["n_gpus"], d["value"], d["value_eager_launches"], 1e3 * d["ms_per_step"], d["roofline"]["frac"], d["e2e"]["value"], d["launch"][:30]), "exchange_us", d.get("record_exchange_us"))
     elif l.strip() and not l.startswith("*") and "OMP_NUM" not in l:
         print(l[:300].rstrip())
 PY
