@@ -46,6 +46,8 @@ struct per_buffer_s {
     int64_t len, cursor;
     int sm_count;
     GatherTune tune;
+    int sharded;               // created by per_create_shard: samples leave the owned-strata range on the device
+    int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
     int64_t last_sample_batch;       //   update calls that pass the same buffer visit only the strata this shard owns
     double *mailbox;           // sharded replay, peer-memory exchange: this rank's mailbox (may be null)
@@ -312,7 +314,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
         }                                                                                          \
     } while (0)
     TRY_ALLOC(b->stamps, sizeof(u64) * cap);
-    TRY_ALLOC(b->scal, sizeof(u64) * 16);
+    TRY_ALLOC(b->scal, sizeof(u64) * 24);
     TRY_ALLOC(b->obs, b->obs_stride * ring_size);
     TRY_ALLOC(b->next, b->obs_stride * ring_size);
     TRY_ALLOC(b->extra, b->extra_stride * ring_size);
@@ -323,7 +325,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
-    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 16, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 24, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
@@ -349,7 +351,9 @@ int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank
     int64_t ring_l = global_size - (int64_t)rank * cap_l;  // ring slots that fall into this slice
     if (ring_l < 0) ring_l = 0;
     if (ring_l > cap_l) ring_l = cap_l;
-    return create_impl(out, device, ring_l, cap_l, alpha, obs_bytes, extra_bytes, rank, n_shards);
+    int rc = create_impl(out, device, ring_l, cap_l, alpha, obs_bytes, extra_bytes, rank, n_shards);
+    if (!rc) (*out)->sharded = 1;
+    return rc;
 }
 
 int per_destroy(per_buffer *b) {
@@ -453,6 +457,8 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.status = b->status();
     k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
     PER_CUDA(cudaGetLastError());
+    b->last_sample_idx = d_out_idx;
+    b->last_sample_batch = batch;
     return PER_OK;
 }
 
@@ -523,6 +529,14 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream) {
     DeviceGuard g(b->device);
     PER_CUDA(cudaMemcpyAsync(h_out3, b->scal + 8, sizeof(u64) * 3, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PER_CUDA(cudaMemsetAsync(b->scal + 8, 0, sizeof(u64) * 3, (cudaStream_t)stream));
+    PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return PER_OK;
+}
+
+int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream) {
+    if (!b || !h_out6) return fail(PER_ERR_ARG, "per_update_trace: bad argument");
+    DeviceGuard g(b->device);
+    PER_CUDA(cudaMemcpyAsync(h_out6, b->scal + 11, sizeof(u64) * 6, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return PER_OK;
 }
@@ -625,7 +639,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.status = slow.status = b->status();
     a.idx_base = slow.idx_base = b->idx_base;
     a.skip_foreign = slow.skip_foreign = b->n_shards > 1;
-    a.range = (b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
     a.piece = slow.piece = tn.piece;
     a.stages = slow.stages = tn.stages;
     const int64_t items = batch * per_query;
@@ -649,6 +663,10 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
 int per_tune(per_buffer *b, const char *key, int64_t value) {
     if (!b || !key) return fail(PER_ERR_ARG, "per_tune: bad argument");
     GatherTune t = b->tune;
+    if (!strcmp(key, "update_trace")) {
+        b->update_trace = value != 0;
+        return PER_OK;
+    }
     if (!strcmp(key, "gather_mode")) t.mode = (int)value;
     else if (!strcmp(key, "gather_warps")) t.warps = (int)value;
     else if (!strcmp(key, "gather_stages")) t.stages = (int)value;
@@ -686,7 +704,10 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.rec_out = b->rec_out;
     a.rec_need = shard_need(b->global_len, b->idx_base, b->t.cap);
     a.rec_len = b->len;
-    a.range = (b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    a.trace = b->update_trace ? b->scal + 11 : nullptr;
+    // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
+    a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     return run_update(a, td, 0, b->sm_count, s);
 }
 

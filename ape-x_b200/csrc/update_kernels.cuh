@@ -8,7 +8,7 @@
 // operations on one SM = 55 us.  This version
 //   * spreads the batch over a thread-block CLUSTER of up to 8 CTAs (8 SMs) that meet at
 //     hardware cluster barriers between phases, and
-//   * lets 8 adjacent lanes share one item: each lane loads 16 B of the item's 128-B line
+//   * lets 16 adjacent lanes share one item: each lane loads 16 B of the two 128-B lines below the item
 //     (one wavefront per 4 items instead of 8 per item) and the 4 generations are reduced
 //     with shuffles, left operand always the lower-numbered child.
 #pragma once
@@ -22,12 +22,12 @@ namespace cg = cooperative_groups;
 
 constexpr int TOP_LEVELS = 10;            // the dense top rebuild covers at most this many generations
 constexpr int TOP_NODES = 1 << TOP_LEVELS;
-constexpr int LIFT = 4;                    // generations recomputed per sparse round (16 nodes = one 128-B line)
-constexpr int LIFT_LANES = 8;              // lanes that share one item in a sparse round
+constexpr int LIFT = 5;                    // generations recomputed per sparse round (32 nodes = two 128-B lines)
+constexpr int LIFT_LANES = 16;             // lanes that share one item in a sparse round: 2^(LIFT-1), 16 B each
 constexpr int UPD_CLUSTER_MAX_ITEMS = 4096;  // largest batch the one-launch (cluster) form takes
 constexpr int UPD_SLICE_MAX = UPD_CLUSTER_MAX_ITEMS / 8;  // items per CTA at most (8 CTAs above 448 items)
 constexpr int UPD_STAGE_FLOATS = 10240;      // shared staging for Q rows (40 KB; its first 32 KB double as the top-of-tree buffers)
-constexpr int UPD_THREADS = 512;
+constexpr int UPD_THREADS = 1024;           // 64 items x 16 lanes per sparse pass
 constexpr int UPD_MAX_CTAS = 8;            // portable cluster size
 
 enum LeafSrc : int {
@@ -63,6 +63,9 @@ struct UpdArgs {
     double *rec_out;          // sharded replay: refresh this shard's 4-double record after the update (may be null)
     int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
     int64_t rec_len;          //   local len
+    int sorted_idx;           // the indices are non-decreasing (they are the stratified sample just drawn): equal
+                              // indices are adjacent, so "a later duplicate wins" needs one look at idx[j+1], no atomics
+    u64 *trace;               // diagnostics: CTA 0 / thread 0 stores globaltimer ns at phase boundaries (null: off)
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
 };
@@ -89,7 +92,7 @@ constexpr int64_t IDX_SKIP = INT64_MIN;
 __host__ __device__ __forceinline__ int top_depth(int L) {
     if (L <= TOP_LEVELS) return L;
     const int r = (L - TOP_LEVELS) % LIFT;
-    return r == 0 ? TOP_LEVELS : TOP_LEVELS - (LIFT - r);
+    return r == 0 ? TOP_LEVELS : TOP_LEVELS - (LIFT - r);  // >= TOP_LEVELS - LIFT + 1
 }
 
 __device__ __forceinline__ int64_t upd_index(const UpdArgs &a, int64_t j) {
@@ -131,24 +134,26 @@ __device__ __forceinline__ bool upd_item(const UpdArgs &a, int64_t j, int64_t &k
     return true;
 }
 
-// One sparse round for one item, executed by LIFT_LANES = 8 adjacent lanes (sub = lane & 7):
-// recompute the 4 generations of ancestors above the 16 contiguous nodes (g<<4)..(g<<4)+15.
+// One sparse round for one item, executed by LIFT_LANES adjacent lanes (sub = lane % LIFT_LANES):
+// recompute the LIFT generations of ancestors above the 2^LIFT contiguous nodes below node g.
+// Lane `sub` loads 16 B (two nodes); generation 1 is one add per lane, generations 2..LIFT halve
+// the owning lanes through xor-shuffles (the owning lane always holds the LEFT child).
 // Every lane of the warp must call this (shuffles); `valid` guards the memory traffic.
 template <bool IS_SUM>
 __device__ __forceinline__ void lift8(double *v, int64_t g, int sub, bool valid) {
     double x = 0.0, y = 0.0;
     if (valid) {
-        double2 c = ldcg_f64x2(v + (g << 4) + 2 * sub);
+        double2 c = ldcg_f64x2(v + (g << LIFT) + 2 * sub);
         x = c.x;
         y = c.y;
     }
-    double r = IS_SUM ? __dadd_rn(x, y) : fmin(x, y);  // generation 1: node (g<<3)+sub
-    if (valid) v[(g << 3) + sub] = r;
+    double r = IS_SUM ? __dadd_rn(x, y) : fmin(x, y);  // generation 1: node (g << (LIFT-1)) + sub
+    if (valid) v[(g << (LIFT - 1)) + sub] = r;
 #pragma unroll
-    for (int s = 1; s <= 3; ++s) {  // generations 2..4: lanes with the low s bits clear own a node
+    for (int s = 1; s < LIFT; ++s) {  // lanes with the low s bits clear own a node of generation s+1
         const double other = __shfl_xor_sync(0xffffffffu, r, 1 << (s - 1));
-        r = IS_SUM ? __dadd_rn(r, other) : fmin(r, other);  // on owning lanes r is the LEFT child
-        if (valid && (sub & ((1 << s) - 1)) == 0) v[(g << (3 - s)) + (sub >> s)] = r;
+        r = IS_SUM ? __dadd_rn(r, other) : fmin(r, other);
+        if (valid && (sub & ((1 << s) - 1)) == 0) v[(g << (LIFT - 1 - s)) + (sub >> s)] = r;
     }
 }
 
@@ -167,24 +172,41 @@ __device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, in
         if (t.mnn) s_min[n + i] = ldcg_f64(t.mnn + (a << k) + i);
     }
     __syncthreads();
+    // all generations in shared memory first (CTA barriers down to 32 nodes, then one warp) ...
 #pragma unroll 1
-    for (int j = k - 1; j >= 0; --j) {
+    for (int j = k - 1; j >= 5; --j) {
         const int m = 1 << j;
         for (int i = threadIdx.x; i < m; i += blockDim.x) {
             if (t.sum) {
                 double2 c = *reinterpret_cast<double2 *>(s_sum + 2 * (m + i));
-                double x = __dadd_rn(c.x, c.y);
-                s_sum[m + i] = x;
-                t.sum[(a << j) + i] = x;
+                s_sum[m + i] = __dadd_rn(c.x, c.y);
             }
             if (t.mnn) {
                 double2 c = *reinterpret_cast<double2 *>(s_min + 2 * (m + i));
-                double x = fmin(c.x, c.y);
-                s_min[m + i] = x;
-                t.mnn[(a << j) + i] = x;
+                s_min[m + i] = fmin(c.x, c.y);
             }
         }
         __syncthreads();
+    }
+    if (threadIdx.x < 32) {
+#pragma unroll 1
+        for (int j = (k - 1 < 4 ? k - 1 : 4); j >= 0; --j) {
+            const int m = 1 << j;
+            const int i = threadIdx.x;
+            if (i < m) {
+                if (t.sum) s_sum[m + i] = __dadd_rn(s_sum[2 * (m + i)], s_sum[2 * (m + i) + 1]);
+                if (t.mnn) s_min[m + i] = fmin(s_min[2 * (m + i)], s_min[2 * (m + i) + 1]);
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    // ... then one coalesced pass writes them out: relative heap slot (1<<j)+i  <->  node (a<<j)+i
+    for (int p = 1 + threadIdx.x; p < n; p += blockDim.x) {
+        const int j = 31 - __clz(p);
+        const int64_t node = (a << j) + (p - (1 << j));
+        if (t.sum) t.sum[node] = s_sum[p];
+        if (t.mnn) t.mnn[node] = s_min[p];
     }
 }
 
@@ -213,6 +235,15 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     const int rank = (int)cl.block_rank();
     const int T = blockDim.x, tid = threadIdx.x;
     const int nwarp = (T + 31) >> 5;
+#define UPD_TRACE(slot)                                                      \
+    do {                                                                     \
+        if (a.trace && rank == 0 && tid == 0) {                              \
+            u64 t__;                                                         \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));          \
+            a.trace[slot] = t__;                                             \
+        }                                                                    \
+    } while (0)
+    UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
     owned_range(a.range, a.n, first, last);
     const int n = last - first;
@@ -232,19 +263,41 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         const int hi = lo + tper < nb ? lo + tper : nb;
         const int cnt = hi - lo;
         const bool staged = (int64_t)cnt * nA <= UPD_STAGE_FLOATS;
+        // cnt <= UPD_SLICE_MAX == blockDim: one row per thread.  The scalar columns and Q(s, a) are
+        // requested first so their round trips overlap the staging of the Q(s', .) rows.
+        const bool have = tid < cnt;
+        const int64_t b = lo + tid;
+        int64_t act_b = 0;
+        float rew_b = 0.0f, done_b = 0.0f, w_b = 0.0f, q_a = 0.0f;
+        if (have) {
+            act_b = td.act[b];
+            rew_b = td.rew[b];
+            done_b = td.done[b];
+            if (td.out_loss) w_b = td.w[b];
+        }
         if (staged) {
             const float *src = td.q_next + (int64_t)lo * nA;
 #pragma unroll 1
             for (int e = tid; e < cnt * nA; e += T) s_q[e] = src[e];
-            __syncthreads();
         }
+        if (have) q_a = td.q[b * nA + act_b];
+        __syncthreads();
         float mx = 0.0f, acc = 0.0f;
+        if (have) {
+            const float *qn = staged ? s_q + tid * nA : td.q_next + b * nA;
+            int best = 0;
+            float bv = qn[0];
 #pragma unroll 1
-        for (int i = tid; i < cnt; i += T) {
-            const float x = staged ? td_row_from(td, lo + i, s_q + i * nA) : td_row(td, lo + i);
-            s_td[i] = x;
-            mx = fmaxf(mx, x);
-            if (td.out_loss) acc += __fmul_rn(td_huber(x), td.w[lo + i]);
+            for (int i = 1; i < nA; ++i) {  // first maximum wins, like argmax (utils.py:72)
+                const float x = qn[i];
+                if (x > bv) { bv = x; best = i; }
+            }
+            const float boot = td.q_tgt[b * nA + best];
+            const float y = __fadd_rn(rew_b, __fmul_rn(__fmul_rn(td.gamma_n, boot), __fsub_rn(1.0f, done_b)));
+            const float x = fabsf(__fsub_rn(y, q_a));
+            s_td[tid] = x;
+            mx = x;
+            if (td.out_loss) acc = __fmul_rn(td_huber(x), w_b);
         }
         mx = warp_max_f32(mx);
         acc = warp_sum_f32(acc);
@@ -287,10 +340,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             td.out_prio[lo + i] = td_prio(x, mx);
             if (td.out_td) td.out_td[lo + i] = x;
         }
-        cl.sync();  // out_prio is complete (items below may read another CTA's rows); CTA 0's s_clu may go
+        // out_prio must be complete before the items below read it: they are this CTA's own rows unless the
+        // owned-range mode re-partitions the items (then another CTA may have produced them)
+        if (a.range || skip_update) cl.sync();
+        else __syncthreads();
         if (skip_update) return;
     }
 
+    UPD_TRACE(1);
     // phase 1
     double *s_leaf = s_sum;
     double my_max = 0.0;
@@ -303,11 +360,15 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             kk = (int)k;
             s_leaf[i] = leaf;
             my_max = fmax(my_max, raw);
-            if (a.stamps) atomicMax(a.stamps + k, a.epoch_hi | (u64)(lo + i));
+            if (a.sorted_idx) {
+                if (lo + i + 1 < (int)a.n && a.idx[lo + i + 1] == a.idx[lo + i]) kk = -1;  // the next item overwrites this one
+            } else if (a.stamps) {
+                atomicMax(a.stamps + k, a.epoch_hi | (u64)(lo + i));
+            }
         }
         s_k[i] = kk;
     }
-    if (a.stamps) {
+    if (a.stamps && !a.sorted_idx) {
         cl.sync();
 #pragma unroll 1
         for (int i = tid; i < cnt; i += T) {
@@ -315,6 +376,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             if (kk >= 0 && __ldcg(a.stamps + kk) != (a.epoch_hi | (u64)(lo + i))) s_k[i] = -1;  // a later item wins
         }
     }
+    UPD_TRACE(2);
     // phase 2 (each thread revisits the items it handled itself)
 #pragma unroll 1
     for (int i = tid; i < cnt; i += T) {
@@ -337,6 +399,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         }
     }
     cl.sync();
+    UPD_TRACE(3);
     // phase 3
     const int top = top_depth(a.t.L);
     const int sub = tid & (LIFT_LANES - 1);
@@ -350,9 +413,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         }
         cl.sync();
     }
+    UPD_TRACE(4);
     // phase 4
     if (rank == 0) {
         dense_lift_block(a.t, 1, top, s_sum, s_min);
+        UPD_TRACE(5);
         if (a.rec_out && tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
     }
 }
@@ -389,7 +454,7 @@ __global__ void k_upd_leaf(UpdArgs a) {
     }
 }
 
-// One sparse round above depth (L - done) for every valid item, 8 lanes per item.
+// One sparse round above depth (L - done) for every valid item, LIFT_LANES lanes per item.
 __global__ void __launch_bounds__(256) k_upd_sparse(UpdArgs a, int done) {
     const int sub = threadIdx.x & (LIFT_LANES - 1);
     const int64_t group = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) / LIFT_LANES;

@@ -75,6 +75,7 @@ SIGNATURES = {
     "per_td_priority_update": (C.c_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, C.c_float, _p, _i64, _p, _p, _p, _p]),
     "per_tree_read": (C.c_int, [_p, C.c_int, _p, _p]),
     "per_tune": (C.c_int, [_p, C.c_char_p, _i64]),
+    "per_update_trace": (C.c_int, [_p, C.POINTER(_i64), _p]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -310,6 +310,11 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm".  No reference counterpart. */
 int per_tune(per_buffer *b, const char *key, int64_t value);
 
+/* Diagnostics: after per_tune(b, "update_trace", 1) the one-launch update kernel stores the GPU
+ * global timer (ns) at its phase boundaries {start, TD done, arbitration done, leaves written,
+ * sparse rounds done, top rebuilt}; this reads the six stamps of the last launch.  Synchronises. */
+int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream);
+
 /* Copies one tree's node array (`_it_sum._value` / `_it_min._value`) to d_out[2*capacity]. */
 int per_tree_read(per_buffer *b, int which, double *d_out, void *stream);
 

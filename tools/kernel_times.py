@@ -80,7 +80,20 @@ for B in args.batch:
     ridx = torch.randint(0, args.cap, (B,), device=dev, generator=gen)
     t["update_leaves (random idx)"] = timeit(lambda: lib.per_update_leaves(h, P(ridx), P(leaf), 1.0, B, sp))
     t["torch empty-ish kernel (launch floor)"] = timeit(lambda: w32.add_(0.0))
+    # phase stamps of the update kernel (GPU global timer), median over 50 launches
+    pn.check(lib.per_tune(h, b"update_trace", 1))
+    tr = []
+    for _ in range(50):
+        lib.per_td_priority_update(h, P(q), P(qn), P(qt), 18, P(act), P(rew), P(done), P(w32), 0.97, P(idx), B, P(o_prio), None,
+                                   P(o_loss), sp)
+        st6 = (pn.C.c_int64 * 6)()
+        pn.check(lib.per_update_trace(h, st6, sp))
+        tr.append([st6[i + 1] - st6[i] for i in range(5)])
+    pn.check(lib.per_tune(h, b"update_trace", 0))
+    med = np.median(np.array(tr), axis=0) / 1e3
     print("batch %d" % B)
+    print("   td+update phases (us): TD %.2f | stamps %.2f | leaves+max %.2f | sparse rounds %.2f | top %.2f | sum %.2f"
+          % (med[0], med[1], med[2], med[3], med[4], med.sum()))
     for k, v in t.items():
         print("   %-40s %8.2f us" % (k, v))
 st = pn.C.c_int64(0)
