@@ -10,6 +10,9 @@
 // through an mbarrier ring.  Algorithmic traffic per sampled transition: read 2*28 224+16 B,
 // write the same.
 #pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace perb {
@@ -48,6 +51,7 @@ struct GatherArgs {
     int64_t idx_base;  // sharded replay: global index of this shard's row 0
     int skip_foreign;  // sharded replay: idx == -1 = another shard's row, skipped silently
     const u64 *range;  // sharded replay: owned strata of the last sample (see owned_range); null = all queries
+    uint8_t *cast_out[2];  // k_gather_cast: widened obs / next_obs batches (rc[0..1].dst then only define offsets)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -93,6 +97,8 @@ struct Piece {
     const uint8_t *src;
     uint8_t *dst;
     uint32_t bytes;
+    int cls;       // row class (0 obs, 1 next_obs, 2 extra)
+    int64_t elem;  // byte offset of the piece inside the (uint8) batch array of its class
 };
 __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, int per_query, int64_t first_q = 0) {
     int64_t q = w / per_query;
@@ -111,6 +117,8 @@ __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, in
     int64_t off = (int64_t)r * a.piece;
     int64_t left = rc.row_bytes - off;
     Piece p;
+    p.cls = c;
+    p.elem = q * rc.dst_stride + off;
     if (foreign) {
         p.src = nullptr;
         p.dst = nullptr;
@@ -237,6 +245,80 @@ __global__ void __launch_bounds__(256) k_gather_ldg(GatherArgs a, int per_query)
                 if (e < nv) st_stream(dst + e, v[j]);
             }
         }
+    }
+}
+
+// Gather + widen: the learner turns every sampled uint8 frame stack into
+// float32 before the first conv (`torch.FloatTensor(states).to(device)`, ApeX.py:50,53 — a 4x
+// inflation done on the host in the reference).  This variant writes float32 / bfloat16 / float16
+// rows (value * scale) straight from the ring: pieces arrive by TMA bulk copy as above, the warp
+// that owns the piece converts them out of shared memory (lane l takes word k*32+l, so the 16-byte
+// stores of a warp cover 512 contiguous bytes) — the uint8 batch is never written or re-read.
+enum GatherCastDtype : int { CAST_F32 = 0, CAST_BF16 = 1, CAST_F16 = 2 };
+
+__device__ __forceinline__ float u8_to_f32(uint32_t word, int byte) {
+    // 0x4B000000 | b is the float 8388608 + b: exact for 0..255, no I2F
+    return __uint_as_float(0x4B000000u | ((word >> (8 * byte)) & 0xffu)) - 8388608.0f;
+}
+
+__global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_cast(GatherArgs a, int per_query, int dtype, float scale) {
+    extern __shared__ __align__(128) uint8_t g_smem[];
+    int64_t first_q, last_q;
+    gather_range(a, first_q, last_q);
+    gather_scalars(a, first_q, last_q);
+    if (per_query == 0) return;
+    const int warp = threadIdx.x >> 5, warps = blockDim.x >> 5, lane = threadIdx.x & 31;
+    const int NS = a.stages;
+    const uint32_t bar0 = smem_u32(g_smem) + (uint32_t)(warp * NS) * 8u;
+    const uint32_t data0 = (uint32_t)round_up_dev(warps * NS * 8, 128) + (uint32_t)(warp * NS) * (uint32_t)a.piece;
+    if (lane == 0) {
+        for (int s = 0; s < NS; ++s) mbar_init(bar0 + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    const int64_t total = (last_q - first_q) * per_query;
+    const int64_t first = (int64_t)blockIdx.x * warps + warp;
+    const int64_t stride = (int64_t)gridDim.x * warps;
+    const int64_t mine = first < total ? (total - first + stride - 1) / stride : 0;
+    const int esz = dtype == CAST_F32 ? 4 : 2;
+    if (lane == 0) {
+        for (int64_t i = 0; i < NS && i < mine; ++i) {
+            Piece p = decode_piece(a, first + i * stride, per_query, first_q);
+            mbar_expect_tx(bar0 + 8u * (uint32_t)i, p.bytes);
+            if (p.bytes) bulk_g2s(smem_u32(g_smem) + data0 + (uint32_t)i * (uint32_t)a.piece, p.src, p.bytes, bar0 + 8u * (uint32_t)i);
+        }
+    }
+    int s = 0;
+    uint32_t parity = 0;
+    for (int64_t i = 0; i < mine; ++i) {
+        Piece p = decode_piece(a, first + i * stride, per_query, first_q);
+        mbar_wait(bar0 + 8u * s, parity);  // every lane waits: the data must be visible to all of them
+        if (p.bytes) {
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(g_smem + data0 + (size_t)s * a.piece);
+            uint8_t *out = a.cast_out[p.cls] + p.elem * esz;  // same element offset, esz bytes per element
+            const int words = (int)(p.bytes >> 2);
+            for (int w = lane; w < words; w += 32) {
+                const uint32_t x = src[w];
+                const float f0 = u8_to_f32(x, 0) * scale, f1 = u8_to_f32(x, 1) * scale, f2 = u8_to_f32(x, 2) * scale,
+                            f3 = u8_to_f32(x, 3) * scale;
+                if (dtype == CAST_F32) {
+                    reinterpret_cast<float4 *>(out)[w] = make_float4(f0, f1, f2, f3);
+                } else if (dtype == CAST_BF16) {
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(f0, f1), hi = __floats2bfloat162_rn(f2, f3);
+                    reinterpret_cast<uint2 *>(out)[w] = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+                } else {
+                    __half2 lo = __floats2half2_rn(f0, f1), hi = __floats2half2_rn(f2, f3);
+                    reinterpret_cast<uint2 *>(out)[w] = make_uint2(*reinterpret_cast<uint32_t *>(&lo), *reinterpret_cast<uint32_t *>(&hi));
+                }
+            }
+        }
+        __syncwarp();  // all lanes are done with this stage
+        if (lane == 0 && i + NS < mine) {
+            Piece n = decode_piece(a, first + (i + NS) * stride, per_query, first_q);
+            mbar_expect_tx(bar0 + 8u * s, n.bytes);
+            if (n.bytes) bulk_g2s(smem_u32(g_smem) + data0 + (uint32_t)s * (uint32_t)a.piece, n.src, n.bytes, bar0 + 8u * s);
+        }
+        if (++s == NS) { s = 0; parity ^= 1u; }
     }
 }
 

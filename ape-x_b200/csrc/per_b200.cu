@@ -329,6 +329,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
+    PER_CUDA(cudaFuncSetAttribute(k_gather_cast, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
     b->tune = GatherTune();
     PER_CUDA(cudaStreamSynchronize(0));
     *out = b;
@@ -656,6 +657,50 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
         k_gather_ldg<<<(unsigned)grid, 256, 0, s>>>(a, per_query);
     }
     if (any_slow) k_gather_bytes<<<grid_for(batch * 3 * 32, 256, b->sm_count), 256, 0, s>>>(slow);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int per_gather_cast(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_dtype, float scale, void *d_out_obs,
+                    void *d_out_next, int64_t *d_out_act, float *d_out_rew, float *d_out_done, void *stream) {
+    if (!b || batch < 0 || (batch && !d_idx) || out_dtype < 0 || out_dtype > 2) return fail(PER_ERR_ARG, "per_gather_cast: bad argument");
+    if (b->obs_bytes % 16) return fail(PER_ERR_ARG, "per_gather_cast: observation rows must be a multiple of 16 bytes");
+    if (batch == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    const GatherTune &tn = b->tune;
+    GatherArgs a;
+    memset(&a, 0, sizeof a);
+    void *outs[2] = {d_out_obs, d_out_next};
+    const uint8_t *srcs[2] = {b->obs, b->next};
+    int per_query = 0;
+    for (int c = 0; c < 2; ++c) {
+        if (!outs[c]) continue;
+        a.rc[c].src = srcs[c];
+        a.rc[c].dst = (uint8_t *)outs[c];
+        a.rc[c].src_stride = b->obs_stride;
+        a.rc[c].dst_stride = b->obs_bytes;
+        a.rc[c].row_bytes = b->obs_bytes;
+        a.rc[c].pieces = (int)((b->obs_bytes + tn.piece - 1) / tn.piece);
+        a.cast_out[c] = (uint8_t *)outs[c];
+        per_query += a.rc[c].pieces;
+    }
+    a.idx = d_idx;
+    a.batch = batch;
+    a.n_rows = b->len;
+    a.act = b->act; a.rew = b->rew; a.done = b->done;
+    a.out_act = d_out_act; a.out_rew = d_out_rew; a.out_done = d_out_done;
+    a.status = b->status();
+    a.idx_base = b->idx_base;
+    a.skip_foreign = b->n_shards > 1;
+    a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    a.piece = tn.piece;
+    a.stages = tn.stages;
+    int64_t grid = (batch * per_query + tn.warps - 1) / tn.warps;
+    if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;
+    if (grid < 1) grid = 1;
+    const size_t smem = per_query ? (size_t)round_up(tn.warps * tn.stages * 8, 128) + (size_t)tn.warps * tn.stages * tn.piece : 0;
+    k_gather_cast<<<(unsigned)grid, tn.warps * 32, smem, s>>>(a, per_query, out_dtype, scale);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }

@@ -396,6 +396,19 @@ class ReplayBuffer(object):
                                    _n.ptr(done), _n.ptr(extra), _n.stream_ptr()))
         return obs, act, rew, nxt, done, extra
 
+    def _gather_cast_device(self, idx_t, dtype, scale):
+        """Extension: the gather fused with the learner's uint8 -> float widening (ApeX.py:50,53)."""
+        code = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[dtype]
+        b = idx_t.numel()
+        obs = torch.empty((b,) + tuple(self._obs_shape), dtype=dtype, device=self._device)
+        nxt = torch.empty_like(obs)
+        act = torch.empty(b, dtype=torch.int64, device=self._device)
+        rew = torch.empty(b, dtype=torch.float32, device=self._device)
+        done = torch.empty(b, dtype=torch.float32, device=self._device)
+        _n.check(_n.lib.per_gather_cast(self._h, _n.ptr(idx_t), b, code, float(scale), _n.ptr(obs), _n.ptr(nxt), _n.ptr(act),
+                                        _n.ptr(rew), _n.ptr(done), _n.stream_ptr()))
+        return obs, act, rew, nxt, done, None
+
     def _encode_sample(self, idxes):
         """memory.py:171-182: (obs, actions, rewards, next_obs, dones) as host arrays."""
         self._flush()
@@ -470,10 +483,12 @@ class PrioritizedReplayBuffer(ReplayBuffer):
     def _draw_uniforms(self, batch_size):
         return np.array([random.random() for _ in range(batch_size)], dtype=np.float64)  # memory.py:247
 
-    def sample_device(self, batch_size, beta, uniforms=None, gather=True):
+    def sample_device(self, batch_size, beta, uniforms=None, gather=True, obs_dtype=None, obs_scale=1.0):
         """Extension: sample() with every output left on the GPU.  Returns a dict with
         idx (int64), weights (float32), weights64, and — if gather — obs, act, rew, next_obs,
-        done (and a_mu).  `uniforms`: optional float64 CUDA / host vector replacing the draws."""
+        done (and a_mu).  `uniforms`: optional float64 CUDA / host vector replacing the draws.
+        obs_dtype = torch.float32 / bfloat16 / float16 widens the uint8 frames inside the gather
+        (value * obs_scale), replacing the learner's torch.FloatTensor(states) (ApeX.py:50,53)."""
         assert beta > 0
         self._flush()
         if uniforms is None:
@@ -489,7 +504,10 @@ class PrioritizedReplayBuffer(ReplayBuffer):
                                            _n.ptr(w32), _n.stream_ptr()))
         out = {"idx": idx, "weights": w32, "weights64": w64}
         if gather:
-            obs, act, rew, nxt, done, extra = self._gather_device(idx)
+            if obs_dtype is not None and self._obs_dtype == np.uint8:
+                obs, act, rew, nxt, done, extra = self._gather_cast_device(idx, obs_dtype, obs_scale)
+            else:
+                obs, act, rew, nxt, done, extra = self._gather_device(idx)
             out.update(obs=obs, act=act, rew=rew, next_obs=nxt, done=done)
             if extra is not None:
                 out["a_mu"] = extra

@@ -208,6 +208,16 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch,
                void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew,
                float *d_out_done, void *d_out_extra, void *stream);
 
+/* per_gather fused with the learner's widening of the frames (`torch.FloatTensor(states)`,
+ * ApeX.py:50,53; origin_repo/learner.py:102-110): observation rows are written as
+ * out_dtype 0 = float32, 1 = bfloat16, 2 = float16, value * scale (scale 1.0 reproduces the
+ * reference's 0..255 floats; 1/255 normalises).  d_out_obs / d_out_next: batch rows of
+ * obs_bytes ELEMENTS each (either may be NULL); the scalar columns as in per_gather.
+ * Observation rows must be a multiple of 16 bytes (uint8[4,84,84] is). */
+int per_gather_cast(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_dtype, float scale,
+                    void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew,
+                    float *d_out_done, void *stream);
+
 /* PrioritizedReplayBuffer.update_priorities (memory.py:300-320), sequential
  * semantics (a later duplicate wins), running max raised.  Priorities are float64
  * (prio_dtype PER_PRIO_F64) or float32 (PER_PRIO_F32, what utils.py:77 hands back);

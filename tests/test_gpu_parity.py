@@ -425,3 +425,23 @@ def test_add_chunk_equals_row_by_row_add(memory):
     ea, eb = a._encode_sample(idx), b._encode_sample(idx)
     for x, y in zip(ea, eb):
         assert np.array_equal(x, y)
+
+
+@pytest.mark.parametrize("dtype,scale", [(torch.float32, 1.0), (torch.float32, 1.0 / 255.0), (torch.bfloat16, 1.0), (torch.float16, 1.0 / 255.0)])
+def test_gather_cast_equals_torch_widening(memory, dtype, scale):
+    """Gather fused with the learner's uint8 -> float conversion (ApeX.py:50,53): must equal
+    gathering uint8 and converting with torch (float32 exact; 16-bit types = torch's rounding)."""
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    size, batch = 3000, 257
+    buf = memory.PrioritizedReplayBuffer(size, 0.6)
+    obs = torch.randint(0, 256, (size, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=gen)
+    nxt = torch.randint(0, 256, (size, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=gen)
+    z = torch.zeros(size, device="cuda")
+    buf.add_batch_device(obs, nxt, torch.arange(size, device="cuda"), z, z)
+    u = np.random.default_rng(2).random(batch)
+    plain = buf.sample_device(batch, 0.4, uniforms=u)
+    cast = buf.sample_device(batch, 0.4, uniforms=u, obs_dtype=dtype, obs_scale=scale)
+    assert torch.equal(plain["idx"], cast["idx"]) and torch.equal(plain["act"], cast["act"])
+    for k in ("obs", "next_obs"):
+        want = (plain[k].float() * np.float32(scale)).to(dtype)
+        assert cast[k].dtype == dtype and torch.equal(cast[k], want), k
