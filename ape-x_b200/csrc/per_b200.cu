@@ -380,6 +380,16 @@ int64_t per_capacity(const per_buffer *b) { return b ? b->t.cap : -1; }
 int64_t per_len(const per_buffer *b) { return b ? b->len : -1; }
 int64_t per_cursor(const per_buffer *b) { return b ? b->cursor : -1; }
 
+int per_set_cursor(per_buffer *b, int64_t cursor, double max_priority, void *stream) {
+    if (!b || cursor < 0 || cursor >= (b->ring_size > 0 ? b->ring_size : 1)) return fail(PER_ERR_ARG, "per_set_cursor: bad cursor");
+    DeviceGuard g(b->device);
+    b->cursor = cursor;
+    if (max_priority > 0.0)
+        PER_CUDA(cudaMemcpyAsync(b->max_prio(), &max_priority, sizeof(double), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return PER_OK;
+}
+
 int per_max_priority(per_buffer *b, double *h_out, void *stream) {
     if (!b || !h_out) return fail(PER_ERR_ARG, "per_max_priority: bad argument");
     DeviceGuard g(b->device);

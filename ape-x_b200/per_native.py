@@ -64,6 +64,7 @@ SIGNATURES = {
     "per_capacity": (_i64, [_p]),
     "per_len": (_i64, [_p]),
     "per_cursor": (_i64, [_p]),
+    "per_set_cursor": (C.c_int, [_p, _i64, _f64, _p]),
     "per_max_priority": (C.c_int, [_p, C.POINTER(_f64), _p]),
     "per_status": (C.c_int, [_p, C.POINTER(_i64), _p]),
     "per_add_batch": (C.c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _f64, _i64, _p]),

@@ -173,6 +173,10 @@ int per_destroy(per_buffer *b);
 int64_t per_capacity(const per_buffer *b);   /* tree capacity (power of two)          */
 int64_t per_len(const per_buffer *b);        /* len(_storage)      (memory.py:159-160) */
 int64_t per_cursor(const per_buffer *b);     /* _next_idx          (memory.py:157,169) */
+/* Restore support (the reference never saves its replay): after the rows
+ * have been re-inserted with per_add_batch (saved leaves as d_leaf), puts `_next_idx` back
+ * where it was and, if max_priority > 0, `_max_priority` too.  Synchronises `stream`. */
+int per_set_cursor(per_buffer *b, int64_t cursor, double max_priority, void *stream);
 /* _max_priority (memory.py:233,320).  Synchronises `stream`. */
 int per_max_priority(per_buffer *b, double *h_out, void *stream);
 int per_status(per_buffer *b, int64_t *h_out, void *stream);

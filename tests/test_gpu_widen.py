@@ -1,0 +1,90 @@
+"""Rows SURVEY.md §8(f) marks "next": replay-server operations with the upstream wire format
+(origin_repo/replay.py:19-45) and snapshot / restore of the GPU replay."""
+import _pickle as pickle
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import __graft_entry__ as entry
+    entry.build()
+    import memory
+    import replay_checkpoint
+    import replay_ops
+    return memory, replay_ops, replay_checkpoint
+
+
+def bits(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64)).view(np.uint64)
+
+
+def actor_chunk(rng, n, shape=(4, 84, 84)):
+    states = [rng.integers(0, 256, size=shape, dtype=np.uint8) for _ in range(n)]
+    nexts = [rng.integers(0, 256, size=shape, dtype=np.uint8) for _ in range(n)]
+    batch = [states, [int(a) for a in rng.integers(0, 18, size=n)], [float(r) for r in rng.standard_normal(n)], nexts,
+             [np.float32(d) for d in (rng.random(n) < 0.1)]]
+    prios = np.abs(rng.standard_normal(n)) + 1e-6
+    return batch, prios
+
+
+def test_replay_server_ops_wire_format(mods):
+    memory, ops, _ = mods
+    rng = np.random.default_rng(0)
+    a, b = memory.CustomPrioritizedReplayBuffer(400, 0.6), memory.CustomPrioritizedReplayBuffer(400, 0.6)
+    for _ in range(11):  # 550 transitions: wraps the ring
+        batch, prios = actor_chunk(rng, 50)
+        ops.push_batch(a, pickle.dumps((batch, prios)))
+        for sample in zip(*batch, prios):  # what origin_repo/replay.py:23-25 does
+            b.add(*sample)
+    assert len(a) == len(b) == 400 and a._next_idx == b._next_idx
+    assert np.array_equal(bits(a._it_sum._value), bits(b._it_sum._value))
+    import random
+    random.seed(5)
+    wire = ops.sample_batch(a, 64, 0.4)
+    random.seed(5)
+    want = b.sample(64, 0.4)
+    got = pickle.loads(wire)
+    assert len(got) == 7 and list(got[-1]) == list(want[-1])
+    for x, y in zip(got[:-1], want[:-1]):
+        assert np.array_equal(np.asarray(x), np.asarray(y))
+    newp = np.abs(rng.standard_normal(64)).astype(np.float32) + 1e-6
+    ops.update_prios(a, pickle.dumps((got[-1], newp)))
+    b.update_priorities(want[-1], newp)
+    assert np.array_equal(bits(a._it_sum._value), bits(b._it_sum._value)) and a._max_priority == b._max_priority
+
+
+@pytest.mark.parametrize("cls_name,fill", [("CustomPrioritizedReplayBuffer", 700), ("CustomPrioritizedReplayBuffer", 260),
+                                           ("CustomPrioritizedReplayBuffer_AQL", 333)])
+def test_snapshot_restore_is_exact(mods, tmp_path, cls_name, fill):
+    memory, _, ckpt = mods
+    rng = np.random.default_rng(1)
+    size = 500
+    buf = getattr(memory, cls_name)(size, 0.6)
+    for i in range(fill):
+        o, o2 = rng.integers(0, 256, size=(4, 12, 12), dtype=np.uint8), rng.integers(0, 256, size=(4, 12, 12), dtype=np.uint8)
+        if cls_name.endswith("_AQL"):
+            buf.add(o, int(i % 5), float(i % 3), o2, float(i % 17 == 0), rng.standard_normal(6).astype(np.float32))
+        else:
+            buf.add(o, int(i % 5), float(i % 3), o2, float(i % 17 == 0), float(abs(rng.standard_normal()) + 1e-6))
+    idx = list(rng.integers(0, len(buf), size=40))
+    buf.update_priorities(idx, np.abs(rng.standard_normal(40)) + 1e-6)
+    path = str(tmp_path / "replay.npz")
+    ckpt.save(buf, path)
+    back = ckpt.load(path, memory)
+    assert type(back) is type(buf) and len(back) == len(buf) and back._next_idx == buf._next_idx
+    assert back._max_priority == buf._max_priority
+    assert np.array_equal(bits(back._it_sum._value), bits(buf._it_sum._value))
+    assert np.array_equal(bits(back._it_min._value), bits(buf._it_min._value))
+    probe = list(range(0, len(buf), 13))
+    for x, y in zip(buf._encode_sample(probe), back._encode_sample(probe)):
+        assert np.array_equal(x, y)
+    # both continue identically: same draws, same next insert slot
+    import random
+    random.seed(9); s1 = buf.sample(32, 0.5)
+    random.seed(9); s2 = back.sample(32, 0.5)
+    assert list(s1[-1]) == list(s2[-1]) and np.array_equal(s1[-2], s2[-2])

@@ -116,6 +116,38 @@ for mode, warps, stages, piece, ctas in shapes:
     if best is None or us < best[0]:
         best = (us, mode, warps, stages, piece, ctas)
 print("best:", best)
+# fused widening (per_gather_cast) against gather + torch .float() on the same rows
+tune(gather_mode=0, gather_warps=4, gather_stages=2, gather_piece=7056, gather_ctas_per_sm=4)
+f_obs = torch.empty((B,) + OBS, dtype=torch.float32, device="cuda")
+f_nxt = torch.empty_like(f_obs)
+h_obs = torch.empty((B,) + OBS, dtype=torch.bfloat16, device="cuda")
+h_nxt = torch.empty_like(h_obs)
+
+
+def t_of(fn):
+    for _ in range(5):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(100):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 10.0
+
+
+def two_step():
+    run(1)
+    f_obs.copy_(o_obs)
+    f_nxt.copy_(o_nxt)
+
+
+t2 = t_of(two_step)
+t32 = t_of(lambda: pn.lib.per_gather_cast(h, pn.ptr(idxs[0]), B, 0, 1.0, pn.ptr(f_obs), pn.ptr(f_nxt), pn.ptr(o_act), pn.ptr(o_rew), pn.ptr(o_done), sp))
+t16 = t_of(lambda: pn.lib.per_gather_cast(h, pn.ptr(idxs[0]), B, 1, 1.0, pn.ptr(h_obs), pn.ptr(h_nxt), pn.ptr(o_act), pn.ptr(o_rew), pn.ptr(o_done), sp))
+print("widening: gather u8 + 2x torch copy_ to f32 %.1f us | per_gather_cast f32 %.1f us (%.0f GB/s algorithmic: read 28.9 MB, write 115.6 MB) | bf16 %.1f us"
+      % (t2, t32, (B * 2 * 28224 * 5) / t32 / 1e3, t16))
 # final correctness check of the best shape against torch indexing
 us, mode, warps, stages, piece, ctas = best
 tune(gather_mode=mode, gather_warps=warps, gather_stages=max(stages, 2), gather_piece=piece, gather_ctas_per_sm=ctas)
