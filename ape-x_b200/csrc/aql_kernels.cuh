@@ -38,7 +38,7 @@ constexpr int AQL_IMG_BYTES = 12 * AQL_ATOM_W;                 // 98 304
 constexpr int AQL_SM_A_HI = AQL_IMG_BYTES;                     // activations, up to 4 atoms each
 constexpr int AQL_SM_A_LO = AQL_SM_A_HI + 4 * AQL_ATOM_A;
 constexpr int AQL_SM_SMALL = AQL_SM_A_LO + 4 * AQL_ATOM_A;     // 229 376: ba2[64] w2[64] barriers tmem slot
-constexpr int AQL_SMEM_BYTES = AQL_SM_SMALL + 1024 + 1024;      // + small area + alignment slack
+constexpr int AQL_SMEM_BYTES = AQL_IMG_BYTES + 1024 + 1024;     // weight image + small area + alignment slack (activations live in TMEM)
 
 struct AqlSmall {  // small parameters; passed to the kernel by value, i.e. through the constant bank
     float wa1[AQL_E1 * AQL_MAX_A];  // continuous: [128, A]; discrete: [64, 1]
@@ -138,6 +138,7 @@ struct AqlArgs {
     const void *a_mu;        // continuous: float [B*K, A]; discrete: int64 [B*K]
     int64_t K, total;        // candidates per state, B*K
     float *q;                // [B*K]
+    unsigned long long *trace;  // diagnostics (may be null): CTA 0 / thread 0 accumulates clock cycles per phase
 };
 
 __device__ __forceinline__ void store_split(uint8_t *a_hi, uint8_t *a_lo, int r, int cc, const float *v) {
@@ -170,19 +171,87 @@ __device__ __forceinline__ void issue_3xtf32(uint32_t tmem_d, uint32_t a_hi, uin
     }
 }
 
+// One K-atom (32 columns) of the 3xTF32 product, 12 MMAs.  MMAs that accumulate into the same TMEM
+// columns form a dependent chain (K is only 8 per instruction), so the three partial products
+// lo.hi / hi.lo / hi.hi go to three different accumulators (AQL_H columns apart, starting at
+// tmem_d) and are interleaved; the epilogue adds the partials.  `first`: overwrite, do not accumulate.
+__device__ __forceinline__ void issue_atom(uint32_t tmem_d, uint32_t a_hi, uint32_t a_lo, uint32_t w_hi, uint32_t w_lo, bool first) {
+#pragma unroll
+    for (int k4 = 0; k4 < 4; ++k4) {
+        const uint32_t acc = (first && k4 == 0) ? 0u : 1u;
+        umma_tf32(tmem_d + 0 * AQL_H, umma_desc(a_lo + k4 * 32), umma_desc(w_hi + k4 * 32), acc);
+        umma_tf32(tmem_d + 1 * AQL_H, umma_desc(a_hi + k4 * 32), umma_desc(w_lo + k4 * 32), acc);
+        umma_tf32(tmem_d + 2 * AQL_H, umma_desc(a_hi + k4 * 32), umma_desc(w_hi + k4 * 32), acc);
+    }
+}
+
+// Sum of the AQL_PARTS partial accumulators (32 columns of this thread's row each).
+constexpr int AQL_PARTS = 6;  // 3 products x 2 K groups
+__device__ __forceinline__ void tmem_ld32_sum(uint32_t taddr, float *acc) {
+    tmem_ld32(taddr, acc);
+#pragma unroll 1
+    for (int part = 1; part < AQL_PARTS; ++part) {
+        float t[32];
+        tmem_ld32(taddr + part * AQL_H, t);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] += t[i];
+    }
+}
+
 constexpr int AQL_THREADS = 256;  // two threads per candidate row: each owns half of the columns
+
+// tcgen05.st: this thread's TMEM lane, N consecutive 32-bit columns starting at taddr
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float *v) {
+    const uint32_t *r = reinterpret_cast<const uint32_t *>(v);
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// A operand from TMEM (lane = row, 8 consecutive columns = the K slice), B from shared memory
+__device__ __forceinline__ void umma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t db, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(db), "r"(AQL_IDESC), "r"(accumulate)
+        : "memory");
+}
+
+// One K-atom (32 columns) of the 3xTF32 product with A in TMEM: lo.hi + hi.lo + hi.hi, 12 MMAs.
+__device__ __forceinline__ void issue_atom_ts(uint32_t tmem_d, uint32_t a_hi, uint32_t a_lo, uint32_t w_hi, uint32_t w_lo, bool first) {
+#pragma unroll
+    for (int k4 = 0; k4 < 4; ++k4) {
+        const uint64_t bh = umma_desc(w_hi + k4 * 32), bl = umma_desc(w_lo + k4 * 32);
+        umma_tf32_ts(tmem_d, a_lo + k4 * 8, bh, (first && k4 == 0) ? 0u : 1u);
+        umma_tf32_ts(tmem_d, a_hi + k4 * 8, bl, 1u);
+        umma_tf32_ts(tmem_d, a_hi + k4 * 8, bh, 1u);
+    }
+}
+
+// TMEM columns (512 allocated): activations of layer 1 (hi | lo, 128 each), accumulators of the two
+// dense layers, activations of layer 2 (hi | lo, 64 each)
+constexpr uint32_t AQL_T_A1H = 0, AQL_T_A1L = 128, AQL_T_D2 = 256, AQL_T_D3 = 320, AQL_T_A2H = 384, AQL_T_A2L = 448;
 
 // A = action dimension (continuous) at compile time so that layer 1 unrolls into FFMAs whose
 // weight operands come straight from the constant bank (`small` is a __grid_constant__ kernel
 // parameter, 5 KB); CONT = false is the discrete path (Linear(1,64), no second action layer).
+// Activations never touch shared memory: the thread that owns a row writes its TF32 hi / lo
+// halves into its TMEM lane (tcgen05.st) and the MMAs take A from TMEM, B (weights) from the
+// swizzled image in shared memory — the SS form re-read 6 KB of shared memory per K=8 MMA
+// and was bound by that (profiles/r01_notes.md).
 template <int A, bool CONT>
 __global__ void __launch_bounds__(AQL_THREADS, 1) k_aql_q(const AqlArgs a, const __grid_constant__ AqlSmall small) {
     extern __shared__ uint8_t aql_raw[];
     uint8_t *sm = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(aql_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t *a_hi = sm + AQL_SM_A_HI, *a_lo = sm + AQL_SM_A_LO;
-    float *s_part = reinterpret_cast<float *>(sm + AQL_SM_SMALL);   // [128] partial dot of the upper column half
-    uint64_t *bar_w = reinterpret_cast<uint64_t *>(s_part + AQL_TILE);  // weights landed
-    uint64_t *bar_m = bar_w + 1;                                        // MMAs of one layer done
+    float *s_part = reinterpret_cast<float *>(sm + AQL_IMG_BYTES);          // [128] partial dot of the upper column half
+    uint64_t *bar_w = reinterpret_cast<uint64_t *>(s_part + AQL_TILE);      // weights landed
+    uint64_t *bar_m = bar_w + 1;                                            // MMAs of one layer done
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bar_m + 1);
 
     const int tid = threadIdx.x;
@@ -197,92 +266,121 @@ __global__ void __launch_bounds__(AQL_THREADS, 1) k_aql_q(const AqlArgs a, const
         bulk_g2s(smem_u32(sm), a.img, AQL_IMG_BYTES, smem_u32(bar_w));
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(128));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
-    const uint32_t d2 = tmem, d3 = tmem + AQL_H;                           // two 64-column accumulators
-    const uint32_t my_tmem = ((uint32_t)((warp & 3) * 32) << 16) + half * 32;  // this warp's lanes, this thread's columns
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);  // this warp's 32 TMEM lanes, column 0
+    const uint32_t w2h = smem_u32(sm + AQL_IMG_W2_HI), w2l = smem_u32(sm + AQL_IMG_W2_LO);
+    const uint32_t w1h = smem_u32(sm + AQL_IMG_W1_HI), w1l = smem_u32(sm + AQL_IMG_W1_LO);
     mbar_wait(smem_u32(bar_w), 0);
     uint32_t phase = 0;
 
     const int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
     for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        long long t_mark = clock64();
+#define AQL_TRACE(slot)                                                     \
+    do {                                                                    \
+        if (a.trace && blockIdx.x == 0 && tid == 0) {                       \
+            const long long now__ = clock64();                              \
+            a.trace[slot] += (unsigned long long)(now__ - t_mark);          \
+            t_mark = now__;                                                 \
+        }                                                                   \
+    } while (0)
         const int64_t c = tile * AQL_TILE + r;
         const bool live = c < a.total;
         const int64_t ci = live ? c : a.total - 1;  // dead rows recompute the last candidate; never stored
-        float v[4];
+        float hi[16], lo[16];
         if (CONT) {
-            // layer 1 on CUDA cores (K = A): h1 = relu(Wa1 . a + ba1); this thread's 64 of the 128 outputs
+            // layer 1 on CUDA cores (K = A): h1 = relu(Wa1 . a + ba1), one 32-column K-atom at a time (16 columns per
+            // thread); the 12 MMAs of an atom are issued as soon as it sits in TMEM
             float act[A];
             const float *ap = static_cast<const float *>(a.a_mu) + ci * A;
 #pragma unroll
             for (int j = 0; j < A; ++j) act[j] = ap[j];
 #pragma unroll
-            for (int cc = 0; cc < 16; ++cc) {
+            for (int kb = 0; kb < 4; ++kb) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int o = half * 64 + cc * 4 + e;
+                for (int e = 0; e < 16; ++e) {
+                    const int o = kb * 32 + half * 16 + e;
                     float s = small.ba1[o];
 #pragma unroll
                     for (int j = 0; j < A; ++j) s = fmaf(small.wa1[o * A + j], act[j], s);
-                    v[e] = fmaxf(s, 0.0f);
+                    s = fmaxf(s, 0.0f);
+                    hi[e] = tf32_hi(s);
+                    lo[e] = tf32_hi(s - hi[e]);
                 }
-                store_split(a_hi, a_lo, r, half * 16 + cc, v);
+                tmem_st16(lane_base + AQL_T_A1H + kb * 32 + half * 16, hi);
+                tmem_st16(lane_base + AQL_T_A1L + kb * 32 + half * 16, lo);
+                tmem_st_wait();
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncthreads();
+                if (tid == 0) {
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    issue_atom_ts(tmem + AQL_T_D2, tmem + AQL_T_A1H + kb * 32, tmem + AQL_T_A1L + kb * 32, w2h + kb * AQL_ATOM_W,
+                                  w2l + kb * AQL_ATOM_W, kb == 0);
+                    if (kb == 3) umma_commit(smem_u32(bar_m));
+                }
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncthreads();
-            if (tid == 0) {
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                issue_3xtf32(d2, smem_u32(a_hi), smem_u32(a_lo), smem_u32(sm + AQL_IMG_W2_HI), smem_u32(sm + AQL_IMG_W2_LO), 4);
-                umma_commit(smem_u32(bar_m));
-            }
+            AQL_TRACE(0);  // layer 1 + MMA issue
             mbar_wait(smem_u32(bar_m), phase);
             phase ^= 1u;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // layer 2 epilogue: e = relu(D2 + ba2) -> next A operand (K = 64: atoms 0..1); 32 columns per thread
+            AQL_TRACE(1);  // wait for layer-2 MMAs
+            // layer 2 epilogue: e = relu(D2 + ba2) -> A operand of layer 3 (K = 64), 32 columns per thread
             float acc[32];
-            tmem_ld32(d2 + my_tmem, acc);
+            tmem_ld32(lane_base + AQL_T_D2 + half * 32, acc);
 #pragma unroll
-            for (int cc = 0; cc < 8; ++cc) {
+            for (int g = 0; g < 2; ++g) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) v[e] = fmaxf(acc[cc * 4 + e] + small.ba2[half * 32 + cc * 4 + e], 0.0f);
-                store_split(a_hi, a_lo, r, half * 8 + cc, v);
+                for (int e = 0; e < 16; ++e) {
+                    const float s = fmaxf(acc[g * 16 + e] + small.ba2[half * 32 + g * 16 + e], 0.0f);
+                    hi[e] = tf32_hi(s);
+                    lo[e] = tf32_hi(s - hi[e]);
+                }
+                tmem_st16(lane_base + AQL_T_A2H + half * 32 + g * 16, hi);
+                tmem_st16(lane_base + AQL_T_A2L + half * 32 + g * 16, lo);
             }
         } else {
             // discrete: e = relu(Wa1[:,0] * float(a) + ba1), 64 wide (model.py:319-320); 32 outputs per thread
             const float av = (float)static_cast<const int64_t *>(a.a_mu)[ci];
 #pragma unroll
-            for (int cc = 0; cc < 8; ++cc) {
+            for (int g = 0; g < 2; ++g) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int o = half * 32 + cc * 4 + e;
-                    v[e] = fmaxf(fmaf(small.wa1[o], av, small.ba1[o]), 0.0f);
+                for (int e = 0; e < 16; ++e) {
+                    const int o = half * 32 + g * 16 + e;
+                    const float s = fmaxf(fmaf(small.wa1[o], av, small.ba1[o]), 0.0f);
+                    hi[e] = tf32_hi(s);
+                    lo[e] = tf32_hi(s - hi[e]);
                 }
-                store_split(a_hi, a_lo, r, half * 8 + cc, v);
+                tmem_st16(lane_base + AQL_T_A2H + half * 32 + g * 16, hi);
+                tmem_st16(lane_base + AQL_T_A2L + half * 32 + g * 16, lo);
             }
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        tmem_st_wait();
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (tid == 0) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            issue_3xtf32(d3, smem_u32(a_hi), smem_u32(a_lo), smem_u32(sm + AQL_IMG_W1_HI), smem_u32(sm + AQL_IMG_W1_LO), 2);
+            for (int kb = 0; kb < 2; ++kb)
+                issue_atom_ts(tmem + AQL_T_D3, tmem + AQL_T_A2H + kb * 32, tmem + AQL_T_A2L + kb * 32, w1h + kb * AQL_ATOM_W,
+                              w1l + kb * AQL_ATOM_W, kb == 0);
             umma_commit(smem_u32(bar_m));
         }
+        AQL_TRACE(2);  // layer-2 epilogue (or discrete layer 1) + MMA issue
         mbar_wait(smem_u32(bar_m), phase);
         phase ^= 1u;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        AQL_TRACE(3);  // wait for layer-3 MMAs
         // layer 3 epilogue: q = w2 . relu(D3 + sv_b) + b2; each thread sums its 32 columns
         const float4 *svb = reinterpret_cast<const float4 *>(a.sv + (ci / a.K) * AQL_H + half * 32);
         float qv = 0.0f;
         {
             float acc[32];
-            tmem_ld32(d3 + my_tmem, acc);
+            tmem_ld32(lane_base + AQL_T_D3 + half * 32, acc);
 #pragma unroll
             for (int i4 = 0; i4 < 8; ++i4) {
                 const float4 s4 = svb[i4];
@@ -293,13 +391,15 @@ __global__ void __launch_bounds__(AQL_THREADS, 1) k_aql_q(const AqlArgs a, const
             }
         }
         if (half) s_part[r] = qv;
-        // the next tile overwrites the staging buffers and the accumulators: everyone must be done reading
+        // the next tile overwrites the TMEM activations and accumulators: everyone must be done reading
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (!half && live) a.q[c] = (qv + s_part[r]) + small.b2;
+        AQL_TRACE(4);  // layer-3 epilogue
+        if (a.trace && blockIdx.x == 0 && tid == 0) a.trace[5] += 1;
     }
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(128));
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(512));
 }
 
 // argmax over the K candidates of each state, one warp per state; the first maximum wins

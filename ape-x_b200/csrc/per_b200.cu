@@ -847,6 +847,7 @@ struct aql_plan_s {
     int device, continuous, A, sm_count;
     uint8_t *img;        // swizzled TF32 hi/lo weight image
     AqlSmall small;      // small parameters (host copy; travels to the kernel as a by-value parameter)
+    unsigned long long *trace;  // 8 words of phase cycle counters (diagnostics)
     float *sv;           // [B, 64] state halves
     int64_t sv_cap;
     bool have_weights;
@@ -864,6 +865,7 @@ int aql_create(aql_plan **out, int device, int continuous, int action_dim) {
     p->continuous = continuous ? 1 : 0;
     p->A = continuous ? action_dim : 1;
     cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (cudaMalloc(&p->trace, 64) == cudaSuccess) cudaMemset(p->trace, 0, 64);
     if (cudaMalloc(&p->img, AQL_IMG_BYTES) != cudaSuccess) {
         cudaGetLastError();
         delete p;
@@ -924,6 +926,7 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
     a.K = K;
     a.total = B * K;
     a.q = d_q;
+    a.trace = p->trace;
     int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
     int64_t grid = tiles < p->sm_count ? tiles : p->sm_count;
 #define AQL_LAUNCH(AA, CC)                                                                                          \
@@ -945,6 +948,15 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
 #undef AQL_LAUNCH
     if (d_argmax) k_aql_argmax<<<(unsigned)((B * 32 + 127) / 128), 128, 0, s>>>(d_q, B, K, d_argmax);
     PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
+int aql_trace(aql_plan *p, int64_t *h_out6, void *stream) {
+    if (!p || !h_out6 || !p->trace) return fail(PER_ERR_ARG, "aql_trace: bad argument");
+    DeviceGuard g(p->device);
+    PER_CUDA(cudaMemcpyAsync(h_out6, p->trace, 48, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PER_CUDA(cudaMemsetAsync(p->trace, 0, 64, (cudaStream_t)stream));
+    PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return PER_OK;
 }
 

@@ -106,6 +106,11 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
                     const void *d_a_mu, int64_t B, int64_t K, float *d_q, int64_t *d_argmax,
                     void *stream);
 
+/* Diagnostics: reads and clears the SM-clock cycles CTA 0 spent, summed over its tiles, in
+ * {layer 1 + MMA issue, wait for layer-2 MMAs, layer-2 epilogue + issue, wait for layer-3 MMAs,
+ * layer-3 epilogue} and the number of tiles it processed.  Synchronises `stream`. */
+int aql_trace(aql_plan *p, int64_t *h_out6, void *stream);
+
 /* ---------------------------------------------------------------- n-step assembly
  * BatchStorage.add / multi_step_reward / compute_priorities (memory.py:415-440, 471-475,
  * 451-464) for n_streams actor streams at once.  Stream s is the steps
