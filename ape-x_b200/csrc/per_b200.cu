@@ -928,7 +928,8 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
     a.q = d_q;
     a.trace = p->trace;
     int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
-    int64_t grid = tiles < p->sm_count ? tiles : p->sm_count;
+    const int64_t slots = (int64_t)p->sm_count * AQL_CTAS_PER_SM;
+    int64_t grid = tiles < slots ? tiles : slots;
 #define AQL_LAUNCH(AA, CC)                                                                                          \
     do {                                                                                                           \
         PER_CUDA(cudaFuncSetAttribute(k_aql_q<AA, CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, AQL_SMEM_BYTES)); \
