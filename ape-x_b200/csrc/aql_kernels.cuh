@@ -177,13 +177,28 @@ __global__ void k_aql_prep_weights(const float *wa2, const float *wadv1, uint8_t
 }
 
 // sv[b][j] = b1[j] + sum_i W1[j][64 + i] * f[b][i]   (f is post-ReLU already, model.py:244-249)
+// One thread per output; the 16 + 16 float4 loads are independent, the FMA chain runs in column order.
 __global__ void k_aql_state_half(const float *wadv1, const float *badv1, const float *f, int64_t B, float *sv) {
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= B * AQL_H) return;
     const int64_t b = t / AQL_H;
     const int j = (int)(t % AQL_H);
+    const float4 *w4 = reinterpret_cast<const float4 *>(wadv1 + j * (2 * AQL_H) + AQL_H);
+    const float4 *f4 = reinterpret_cast<const float4 *>(f + b * AQL_H);
+    float4 w[AQL_H / 4], x[AQL_H / 4];
+#pragma unroll
+    for (int i = 0; i < AQL_H / 4; ++i) {
+        w[i] = w4[i];
+        x[i] = f4[i];
+    }
     float acc = 0.0f;
-    for (int i = 0; i < AQL_H; ++i) acc = fmaf(wadv1[j * (2 * AQL_H) + AQL_H + i], fmaxf(f[b * AQL_H + i], 0.0f), acc);
+#pragma unroll
+    for (int i = 0; i < AQL_H / 4; ++i) {
+        acc = fmaf(w[i].x, fmaxf(x[i].x, 0.0f), acc);
+        acc = fmaf(w[i].y, fmaxf(x[i].y, 0.0f), acc);
+        acc = fmaf(w[i].z, fmaxf(x[i].z, 0.0f), acc);
+        acc = fmaf(w[i].w, fmaxf(x[i].w, 0.0f), acc);
+    }
     sv[t] = acc + badv1[j];
 }
 
@@ -400,24 +415,49 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
 #undef AQL_BAR
 }
 
-// argmax over the K candidates of each state, one warp per state; the first maximum wins
-// (torch.argmax, model.py:330-332).
-__global__ void k_aql_argmax(const float *q, int64_t B, int64_t K, int64_t *out) {
-    const int lane = threadIdx.x & 31;
-    const int64_t b = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    if (b >= B) return;
+// argmax over the K candidates of each state, one CTA of AQL_ARGMAX_THREADS per state; the first
+// maximum wins (torch.argmax, model.py:330-332).
+constexpr int AQL_ARGMAX_THREADS = 128;
+__device__ __forceinline__ void argmax_merge(float &bv, int64_t &bi, float ov, int64_t oi) {
+    if (ov > bv || (ov == bv && oi < bi)) {
+        bv = ov;
+        bi = oi;
+    }
+}
+__global__ void __launch_bounds__(AQL_ARGMAX_THREADS) k_aql_argmax(const float *q, int64_t B, int64_t K, int64_t *out) {
+    __shared__ float s_v[AQL_ARGMAX_THREADS / 32];
+    __shared__ int64_t s_i[AQL_ARGMAX_THREADS / 32];
+    const int64_t b = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float *row = q + b * K;
     float bv = -INFINITY;
     int64_t bi = K;
-    for (int64_t k = lane; k < K; k += 32) {
-        const float x = q[b * K + k];
-        if (x > bv) { bv = x; bi = k; }
+    for (int64_t k0 = 0; k0 < K; k0 += 8 * AQL_ARGMAX_THREADS) {
+        float x[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {  // eight independent loads in flight per thread
+            const int64_t k = k0 + u * AQL_ARGMAX_THREADS + tid;
+            x[u] = k < K ? row[k] : -INFINITY;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int64_t k = k0 + u * AQL_ARGMAX_THREADS + tid;
+            if (k < K && x[u] > bv) {  // ascending k per thread: strict > keeps the first maximum
+                bv = x[u];
+                bi = k;
+            }
+        }
     }
-    for (int o = 16; o; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-        const int64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    for (int o = 16; o; o >>= 1) argmax_merge(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    if (lane == 0) {
+        s_v[warp] = bv;
+        s_i[warp] = bi;
     }
-    if (lane == 0) out[b] = bi;
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < AQL_ARGMAX_THREADS / 32; ++w) argmax_merge(bv, bi, s_v[w], s_i[w]);
+        out[b] = bi;
+    }
 }
 
 }  // namespace perb

@@ -947,7 +947,7 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
         default: AQL_LAUNCH(8, true); break;
     }
 #undef AQL_LAUNCH
-    if (d_argmax) k_aql_argmax<<<(unsigned)((B * 32 + 127) / 128), 128, 0, s>>>(d_q, B, K, d_argmax);
+    if (d_argmax) k_aql_argmax<<<(unsigned)B, AQL_ARGMAX_THREADS, 0, s>>>(d_q, B, K, d_argmax);
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
