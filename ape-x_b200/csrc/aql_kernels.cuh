@@ -151,6 +151,10 @@ __device__ __forceinline__ void issue_atom_ts(uint32_t tmem_d, uint32_t a_hi, ui
     }
 }
 
+// Programmatic dependent launch (aql_candidate_q chains its three kernels with it)
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- one-off preparation ---------------------------------------------------------------
 // Splits Wa2 [64,128] and W1[:, :64] [64,64] into TF32 hi / lo and lays them out as the
 // swizzled shared-memory image.  One thread per (matrix row n, 16-byte chunk).
@@ -179,6 +183,7 @@ __global__ void k_aql_prep_weights(const float *wa2, const float *wadv1, uint8_t
 // sv[b][j] = b1[j] + sum_i W1[j][64 + i] * f[b][i]   (f is post-ReLU already, model.py:244-249)
 // One thread per output; the 16 + 16 float4 loads are independent, the FMA chain runs in column order.
 __global__ void k_aql_state_half(const float *wadv1, const float *badv1, const float *f, int64_t B, float *sv) {
+    pdl_launch_dependents();  // the Q kernel may start its prologue and first layers now (it waits before reading sv)
     const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (t >= B * AQL_H) return;
     const int64_t b = t / AQL_H;
@@ -240,6 +245,7 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
     const uint32_t bar0 = smem_u32(bars);
 #define AQL_BAR(i) (bar0 + 8u * (uint32_t)(i))
 
+    const long long t_entry = clock64();
     const int tid = threadIdx.x;
     const int r = tid & (AQL_TILE - 1);   // row of the tile = TMEM lane
     const int half = (tid >> 7) & 1;      // which half of the columns this thread owns
@@ -266,6 +272,7 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
+    pdl_launch_dependents();  // the argmax grid may become resident; it waits for this grid to retire before reading q
 
     if (warp == AQL_ISSUER_WARP) {
         // ---- MMA issuer ------------------------------------------------------------------------
@@ -302,6 +309,7 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
         // ---- CUDA-core side: 256 threads ---------------------------------------------------------
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);  // this warp's 32 TMEM lanes, column 0
         uint32_t it = 0;
+        if (a.trace && blockIdx.x == 0 && tid == 0) a.trace[6] += (unsigned long long)(clock64() - t_entry);
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const uint32_t tp = it & 1u;
             long long t_mark = clock64();
@@ -381,6 +389,7 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
             AQL_TRACE(2);  // layer-2 epilogue (or discrete layer 1)
             const float4 *svb = reinterpret_cast<const float4 *>(a.sv + (ci / a.K) * AQL_H + half * 32);
             float4 s4[8];
+            if (it == 0) pdl_wait();  // sv comes from the state-half kernel launched just before this one
 #pragma unroll
             for (int i4 = 0; i4 < 8; ++i4) s4[i4] = svb[i4];  // in flight while the layer-3 MMAs run
             mbar_wait(AQL_BAR(AQL_BAR_DONE3), tp);
@@ -412,6 +421,7 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
     tc_fence_before();
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(AQL_T_COLS));
+    if (a.trace && blockIdx.x == 0 && tid == 0) a.trace[7] += (unsigned long long)(clock64() - t_entry);
 #undef AQL_BAR
 }
 
@@ -430,6 +440,7 @@ __global__ void __launch_bounds__(AQL_ARGMAX_THREADS) k_aql_argmax(const float *
     const int64_t b = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float *row = q + b * K;
+    pdl_wait();  // q is complete and visible once the Q kernel has retired
     float bv = -INFINITY;
     int64_t bi = K;
     for (int64_t k0 = 0; k0 < K; k0 += 8 * AQL_ARGMAX_THREADS) {

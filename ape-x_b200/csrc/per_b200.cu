@@ -848,6 +848,7 @@ struct aql_plan_s {
     uint8_t *img;        // swizzled TF32 hi/lo weight image
     AqlSmall small;      // small parameters (host copy; travels to the kernel as a by-value parameter)
     unsigned long long *trace;  // 8 words of phase cycle counters (diagnostics)
+    bool trace_on;       // set by the first aql_trace call
     float *sv;           // [B, 64] state halves
     int64_t sv_cap;
     bool have_weights;
@@ -926,14 +927,29 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
     a.K = K;
     a.total = B * K;
     a.q = d_q;
-    a.trace = p->trace;
+    a.trace = p->trace_on ? p->trace : nullptr;
     int64_t tiles = (a.total + AQL_TILE - 1) / AQL_TILE;
     const int64_t slots = (int64_t)p->sm_count * AQL_CTAS_PER_SM;
     int64_t grid = tiles < slots ? tiles : slots;
+    // The three launches are chained with programmatic dependent launch: the state-half kernel releases its
+    // dependents at once, so the Q kernel's prologue (barriers, TMEM, 96 KB weight image) and its first two
+    // layers run beside it and only the first read of sv waits (griddepcontrol.wait); likewise the argmax grid
+    // is resident and waiting when the Q kernel retires.
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.stream = s;
+    cfg.attrs = pdl;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(AQL_THREADS);
+    cfg.dynamicSmemBytes = AQL_SMEM_BYTES;
 #define AQL_LAUNCH(AA, CC)                                                                                          \
     do {                                                                                                           \
         PER_CUDA(cudaFuncSetAttribute(k_aql_q<AA, CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, AQL_SMEM_BYTES)); \
-        k_aql_q<AA, CC><<<(unsigned)grid, AQL_THREADS, AQL_SMEM_BYTES, s>>>(a, p->small);                           \
+        PER_CUDA(cudaLaunchKernelEx(&cfg, k_aql_q<AA, CC>, a, p->small));                                          \
     } while (0)
     if (!p->continuous) AQL_LAUNCH(1, false);
     else switch (p->A) {
@@ -947,15 +963,21 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
         default: AQL_LAUNCH(8, true); break;
     }
 #undef AQL_LAUNCH
-    if (d_argmax) k_aql_argmax<<<(unsigned)B, AQL_ARGMAX_THREADS, 0, s>>>(d_q, B, K, d_argmax);
+    if (d_argmax) {
+        cfg.gridDim = dim3((unsigned)B);
+        cfg.blockDim = dim3(AQL_ARGMAX_THREADS);
+        cfg.dynamicSmemBytes = 0;
+        PER_CUDA(cudaLaunchKernelEx(&cfg, k_aql_argmax, (const float *)d_q, B, K, d_argmax));
+    }
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
 
-int aql_trace(aql_plan *p, int64_t *h_out6, void *stream) {
-    if (!p || !h_out6 || !p->trace) return fail(PER_ERR_ARG, "aql_trace: bad argument");
+int aql_trace(aql_plan *p, int64_t *h_out8, void *stream) {
+    if (!p || !h_out8 || !p->trace) return fail(PER_ERR_ARG, "aql_trace: bad argument");
+    p->trace_on = true;  // the stamps cost the traced CTA a global read-modify-write per phase: off until asked for
     DeviceGuard g(p->device);
-    PER_CUDA(cudaMemcpyAsync(h_out6, p->trace, 48, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PER_CUDA(cudaMemcpyAsync(h_out8, p->trace, 64, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PER_CUDA(cudaMemsetAsync(p->trace, 0, 64, (cudaStream_t)stream));
     PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return PER_OK;

@@ -108,8 +108,10 @@ int aql_candidate_q(aql_plan *p, const float *d_wadv1, const float *d_badv1, con
 
 /* Diagnostics: reads and clears the SM-clock cycles CTA 0 spent, summed over its tiles, in
  * {layer 1 + MMA issue, wait for layer-2 MMAs, layer-2 epilogue + issue, wait for layer-3 MMAs,
- * layer-3 epilogue} and the number of tiles it processed.  Synchronises `stream`. */
-int aql_trace(aql_plan *p, int64_t *h_out6, void *stream);
+ * layer-3 epilogue}, the number of tiles it processed, and the cycles from kernel entry to its
+ * first tile and to its exit (summed over launches).  The stamps are off until the first call
+ * (they cost the traced CTA a global read-modify-write per phase).  Synchronises `stream`. */
+int aql_trace(aql_plan *p, int64_t *h_out8, void *stream);
 
 /* ---------------------------------------------------------------- n-step assembly
  * BatchStorage.add / multi_step_reward / compute_priorities (memory.py:415-440, 471-475,
