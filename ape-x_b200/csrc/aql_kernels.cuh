@@ -151,10 +151,6 @@ __device__ __forceinline__ void issue_atom_ts(uint32_t tmem_d, uint32_t a_hi, ui
     }
 }
 
-// Programmatic dependent launch (aql_candidate_q chains its three kernels with it)
-__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-
 // ---- one-off preparation ---------------------------------------------------------------
 // Splits Wa2 [64,128] and W1[:, :64] [64,64] into TF32 hi / lo and lays them out as the
 // swizzled shared-memory image.  One thread per (matrix row n, 16-byte chunk).

@@ -57,7 +57,32 @@ inline int ilog2_exact(int64_t x) {
 }
 inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
+// Launch with (or without) programmatic stream serialization: a kernel launched this way may become
+// resident while its predecessor in the stream is still running and must execute pdl_wait() before it
+// touches anything the predecessor reads or writes.  Only kernels that do so are launched through here
+// with pdl = true.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- device helpers -------------------------------------------------------------------
+// Programmatic dependent launch: let the next kernel of the stream become resident / wait until the
+// previous one has completed and its writes are visible.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // 64-bit L2-only loads: tree nodes are rewritten by other CTAs / earlier phases of the
 // same kernel, so the update path never reads them through L1.
 __device__ __forceinline__ double ldcg_f64(const double *p) { return __ldcg(p); }

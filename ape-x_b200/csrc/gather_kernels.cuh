@@ -163,6 +163,8 @@ __device__ __forceinline__ void gather_scalars(const GatherArgs &a, int64_t firs
 // Dynamic shared memory: [warps*stages mbarriers, padded to 128 B][warps*stages pieces].
 __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs a, int per_query) {
     extern __shared__ __align__(128) uint8_t g_smem[];
+    pdl_launch_dependents();
+    pdl_wait();  // indices and range tags come from the sampling kernel in front of this one
     int64_t first_q, last_q;
     gather_range(a, first_q, last_q);
     gather_scalars(a, first_q, last_q);

@@ -47,6 +47,7 @@ struct per_buffer_s {
     int sm_count;
     GatherTune tune;
     int sharded;               // created by per_create_shard: samples leave the owned-strata range on the device
+    int pdl;                   // per_tune("pdl", 0/1): chain sample / gather / update launches with programmatic dependent launch
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
     int64_t last_sample_batch;       //   update calls that pass the same buffer visit only the strata this shard owns
@@ -97,7 +98,7 @@ int grid_for(int64_t n, int threads, int sm_count) {
 }
 
 // Batched leaf update + re-reduction (K1).  `td` non-null fuses K5 in front (one-CTA form only).
-int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s) {
+int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s, bool pdl = false) {
     TdArgs none;
     memset(&none, 0, sizeof none);
     if (a.n <= UPD_CLUSTER_MAX_ITEMS) {
@@ -110,13 +111,15 @@ int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cuda
         cfg.gridDim = dim3(ncta);
         cfg.blockDim = dim3(UPD_THREADS);
         cfg.stream = s;
-        cudaLaunchAttribute attr[1];
+        cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
         attr[0].val.clusterDim.x = ncta;
         attr[0].val.clusterDim.y = 1;
         attr[0].val.clusterDim.z = 1;
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // the kernel starts with pdl_wait()
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        cfg.numAttrs = pdl ? 2 : 1;
         PER_CUDA(cudaLaunchKernelEx(&cfg, k_update_cluster, a, td ? *td : none, td ? 1 : 0, skip_update));
         return PER_OK;
     }
@@ -258,7 +261,7 @@ int seg_find_prefixsum(seg_tree *t, const double *d_mass, int64_t n, int64_t *d_
     a.batch = n;
     a.out_idx = d_out_idx;
     a.status = t->status;
-    k_sample<<<(unsigned)((n * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((n * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, false, a));
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
@@ -287,6 +290,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     per_buffer *b = new per_buffer();
     memset(b, 0, sizeof *b);
     b->device = device;
+    b->pdl = 1;
     b->ring_size = ring_size;
     b->alpha = alpha;
     b->obs_bytes = obs_bytes;
@@ -466,7 +470,7 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.out_w64 = d_out_w64;
     a.out_w32 = d_out_w32;
     a.status = b->status();
-    k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, b->pdl != 0, a));
     PER_CUDA(cudaGetLastError());
     b->last_sample_idx = d_out_idx;
     b->last_sample_batch = batch;
@@ -598,7 +602,12 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     }
     b->last_sample_idx = d_out_idx;
     b->last_sample_batch = batch;
-    k_sample<<<(unsigned)((batch * 32 + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
+    // one warp per OWNED stratum in the expected case (batch / n_shards of them, plus slack); a shard that owns
+    // more loops over them
+    int64_t warps = batch / b->n_shards + batch / (4 * b->n_shards) + 4;
+    if (warps > batch) warps = batch;
+    const int64_t ctas = (warps * 32 + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
+    PER_CUDA(launch_pdl(k_sample_sharded, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, b->pdl != 0, a));
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
@@ -659,7 +668,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;  // persistent CTAs
         if (grid < 1) grid = 1;
         const size_t smem = per_query ? (size_t)round_up(tn.warps * tn.stages * 8, 128) + (size_t)tn.warps * tn.stages * tn.piece : 0;
-        k_gather_tma<<<(unsigned)grid, tn.warps * 32, smem, s>>>(a, per_query);
+        PER_CUDA(launch_pdl(k_gather_tma, dim3((unsigned)grid), dim3(tn.warps * 32), smem, s, b->pdl != 0, a, per_query));
     } else {
         int64_t grid = (items + 7) / 8;
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;
@@ -722,6 +731,10 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->update_trace = value != 0;
         return PER_OK;
     }
+    if (!strcmp(key, "pdl")) {
+        b->pdl = value != 0;
+        return PER_OK;
+    }
     if (!strcmp(key, "gather_mode")) t.mode = (int)value;
     else if (!strcmp(key, "gather_warps")) t.warps = (int)value;
     else if (!strcmp(key, "gather_stages")) t.stages = (int)value;
@@ -763,7 +776,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.trace = b->update_trace ? b->scal + 11 : nullptr;
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
-    return run_update(a, td, 0, b->sm_count, s);
+    return run_update(a, td, 0, b->sm_count, s, b->pdl != 0);
 }
 
 int per_update_priorities(per_buffer *b, const int64_t *d_idx, const void *d_prio, int prio_dtype, int64_t n, void *stream) {
@@ -822,7 +835,7 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
         memset(&a, 0, sizeof a);
         a.t = b->t;
         a.n = batch;
-        return run_update(a, &t, 1, b->sm_count, s);
+        return run_update(a, &t, 1, b->sm_count, s, b->pdl != 0);
     }
     const int grid = grid_for(batch, 256, b->sm_count);
     k_td_reset<<<1, 1, 0, s>>>(t.red);

@@ -138,6 +138,7 @@ struct SampleArgs {
     int use_mailbox;             // 1: exchange through the mailboxes; 0: records come in `recs`
     u64 *d_wait_stats;           // {waits, total ns, max ns} spent by CTA 0 between kernel start and the last record's arrival
     int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
+    int skip_publish;            // 1: this epoch's record is in the mailboxes already (published by the update kernel)
 };
 
 constexpr int SHARD_REC = 4;   // doubles per shard record
@@ -149,9 +150,18 @@ __device__ __forceinline__ u64 global_timer_ns() {
     return t;
 }
 
+__device__ __forceinline__ u64 ld_acquire_sys(const u64 *p) {
+    u64 v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(u64 *p, u64 v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 // One warp: computes this shard's record and stores it, then the epoch flag, into the slot
 // [epoch & 1][rank] of every rank's mailbox (lane p -> rank p; plain stores to peer-mapped
-// addresses travel over NVLink).  The flag is written after a system-scope fence.
+// addresses travel over NVLink).  The flag is a system-scope release store, polled with acquire loads.
 __device__ __forceinline__ void publish_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
                                                int64_t len_local, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
     const int lane = threadIdx.x & 31;
@@ -162,8 +172,7 @@ __device__ __forceinline__ void publish_record(const double *sum, const double *
         double *slot = peer_mailbox[lane] + ((epoch & 1) * n_shards + rank) * MAIL_SLOT;
         reinterpret_cast<double2 *>(slot)[0] = make_double2(rs, rm);
         reinterpret_cast<double2 *>(slot)[1] = make_double2(partial, (double)len_local);
-        __threadfence_system();
-        *reinterpret_cast<volatile u64 *>(slot + SHARD_REC) = epoch;
+        st_release_sys(reinterpret_cast<u64 *>(slot + SHARD_REC), epoch);  // orders the record in front of the flag
     }
 }
 
@@ -172,10 +181,10 @@ __device__ __forceinline__ void publish_record(const double *sum, const double *
 __device__ __forceinline__ void await_records(const double *mailbox, int n_shards, u64 epoch, u64 *status) {
     const int lane = threadIdx.x & 31;
     if (lane < n_shards) {
-        const volatile u64 *flag = reinterpret_cast<const volatile u64 *>(mailbox + ((epoch & 1) * n_shards + lane) * MAIL_SLOT + SHARD_REC);
-        if (*flag < epoch) {
+        const u64 *flag = reinterpret_cast<const u64 *>(mailbox + ((epoch & 1) * n_shards + lane) * MAIL_SLOT + SHARD_REC);
+        if (ld_acquire_sys(flag) < epoch) {
             const u64 t0 = global_timer_ns();
-            while (*flag < epoch) {
+            while (ld_acquire_sys(flag) < epoch) {
                 __nanosleep(100);  // back off: thousands of pollers on one L2 line delay the very write they wait for
                 if (global_timer_ns() - t0 > 2000000000ull) {
                     atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
@@ -185,7 +194,6 @@ __device__ __forceinline__ void await_records(const double *mailbox, int n_shard
         }
     }
     __syncwarp();
-    __threadfence_system();
 }
 
 __global__ void k_shard_publish(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
@@ -214,87 +222,10 @@ __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap
     write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
-__device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q, const int lane, const u64 epoch) {
-    double mass;
-    double root_sum, root_min = 0.0;
-    int64_t idx_base = 0;
-    if (a.n_shards) {
-        const int N = a.n_shards;
-        const double *recs = a.recs;
-        int rec_stride = SHARD_REC;
-        if (a.use_mailbox) {  // the records of this epoch are in the mailbox (k_sample waited for them)
-            recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
-            rec_stride = MAIL_SLOT;
-        }
-        // Top of the virtual tree, one node per lane: lanes N..2N-1 hold the shard roots,
-        // lanes 1..N-1 their pairwise sums built level by level like memory.py:82-87.
-        double top = (lane >= N && lane < 2 * N) ? __ldcg(recs + (lane - N) * rec_stride) : 0.0;
-        double mn = lane < N ? __ldcg(recs + lane * rec_stride + 1) : __longlong_as_double(0x7ff0000000000000LL);
-        for (int w = N >> 1; w >= 1; w >>= 1) {
-            const double l = shfl_f64(top, (2 * lane) & 31), r = shfl_f64(top, (2 * lane + 1) & 31);
-            if (lane >= w && lane < 2 * w) top = __dadd_rn(l, r);
-        }
-        for (int o = 16; o; o >>= 1) mn = fmin(mn, shfl_f64(mn, lane ^ o));
-        root_sum = shfl_f64(top, 1);
-        root_min = mn;
-        // p_total = sum over global leaves [0, need): shard-aligned blocks come from the top
-        // tree (one per set bit of need / cap), the rest from the owning shard's record.
-        const int64_t need = a.n_rows - 1;
-        const int64_t need_hi = need >> a.L;  // whole shards covered
-        const int64_t need_lo = need & (a.cap - 1);
-        double acc = 0.0;
-        bool first = true;
-        if (need_lo) {
-            acc = __ldcg(recs + need_hi * rec_stride + 2);
-            first = false;
-        }
-#pragma unroll 1
-        for (int b = 0; (int64_t(1) << b) <= need_hi; ++b) {
-            if ((need_hi >> b) & 1) {
-                const double t = shfl_f64(top, (int)((N >> b) + ((need_hi >> (b + 1)) << 1)));
-                acc = first ? t : __dadd_rn(t, acc);
-                first = false;
-            }
-        }
-        const double seg = __ddiv_rn(acc, (double)a.batch);
-        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));
-        // descent through the top tree
-        int node = 1;
-        while (node < N) {
-            const double lv = shfl_f64(top, 2 * node);
-            if (lv > mass) {
-                node = 2 * node;
-            } else {
-                mass = __dsub_rn(mass, lv);
-                node = 2 * node + 1;
-            }
-        }
-        if (node - N != a.rank) {  // another shard owns this stratum
-            if (lane == 0) {
-                a.out_idx[q] = -1;
-                if (a.out_w64) a.out_w64[q] = 0.0;
-                if (a.out_w32) a.out_w32[q] = 0.0f;
-            }
-            return;
-        }
-        idx_base = (int64_t)a.rank * a.cap;
-        if (lane == 0) {  // record the range of strata this shard owns (they are contiguous: masses are sorted)
-            atomicMax(a.d_range, (epoch << 32) | (u64)(0xffffffffu - (unsigned)q));
-            atomicMax(a.d_range + 1, (epoch << 32) | (u64)(q + 1));
-        }
-    } else {
-        root_sum = a.sum[1];
-        if (a.direct_mass) {
-            mass = a.u[q];
-            if (lane == 0 && !(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
-        } else {
-            const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
-            const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
-            mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
-        }
-        if (a.mnn) root_min = a.mnn[1];
-    }
-
+// The local descent of one query (all 32 lanes) from the root of this tree, then the index and
+// the importance weight.  `mass` is the prefix sum looked for inside this tree.
+__device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int64_t q, const int lane, double mass, const double root_sum,
+                                                 const double root_min, const int64_t idx_base) {
     // lane -> (generation j in 1..5, pair qg): lane 0 -> 1, lanes 1-2 -> 2, 3-6 -> 3, 7-14 -> 4, 15-30 -> 5
     const int j = 32 - __clz(lane + 1);
     const int qg = lane + 1 - (1 << (j - 1));
@@ -338,33 +269,205 @@ __device__ __forceinline__ void sample_one(const SampleArgs &a, const int64_t q,
     }
 }
 
+// Unsharded: one warp per query.
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();  // the tree is written by the kernel in front of this one
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
-    u64 epoch = 0;
-    if (a.n_shards) {
-        epoch = __ldcg(a.d_epoch) + 1;  // stable until the last warp of this launch retires
+    if (q >= a.batch) return;  // whole warps take the same side
+    const double root_sum = a.sum[1];
+    double mass;
+    if (a.direct_mass) {
+        mass = a.u[q];
+        if (lane == 0 && !(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
+    } else {
+        const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
+        const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
+        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
+    }
+    descend_and_emit(a, q, lane, mass, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
+}
+
+// ---------------------------------------------------------------------------------------
+// Sharded form.  The view of the virtual tree above the shard roots is built ONCE per CTA (not
+// per query): wait for the records, top tree, p_total, segment width.  Stratum masses grow with
+// the stratum number and the top descent is monotone in the mass, so the strata one shard owns
+// are a contiguous range [lo, hi); warp 0 finds it with the exact ownership test (32 probes
+// around the position the shard-root prefix predicts, one round trip; a 32-ary search otherwise)
+// and only those strata are descended.  Everything else gets index -1.
+// ---------------------------------------------------------------------------------------
+struct ShardView {
+    double top;       // lane i: node i of the top tree (lanes N..2N-1 the shard roots)
+    double root_sum, root_min, seg;
+};
+
+__device__ __forceinline__ ShardView shard_view(const SampleArgs &a, const u64 epoch, const int lane) {
+    const int N = a.n_shards;
+    const double *recs = a.recs;
+    int rec_stride = SHARD_REC;
+    if (a.use_mailbox) {  // the records of this epoch are in the mailbox (the caller waited for them)
+        recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
+        rec_stride = MAIL_SLOT;
+    }
+    ShardView v;
+    // Top of the virtual tree, one node per lane: lanes N..2N-1 hold the shard roots,
+    // lanes 1..N-1 their pairwise sums built level by level like memory.py:82-87.
+    double top = (lane >= N && lane < 2 * N) ? __ldcg(recs + (lane - N) * rec_stride) : 0.0;
+    double mn = lane < N ? __ldcg(recs + lane * rec_stride + 1) : __longlong_as_double(0x7ff0000000000000LL);
+    // p_total = sum over global leaves [0, need): shard-aligned blocks come from the top
+    // tree (one per set bit of need / cap), the rest from the owning shard's record.
+    const int64_t need = a.n_rows - 1;
+    const int64_t need_hi = need >> a.L;  // whole shards covered
+    const int64_t need_lo = need & (a.cap - 1);
+    double acc = 0.0;
+    bool first = true;
+    if (need_lo) {
+        acc = __ldcg(recs + need_hi * rec_stride + 2);
+        first = false;
+    }
+    for (int w = N >> 1; w >= 1; w >>= 1) {
+        const double l = shfl_f64(top, (2 * lane) & 31), r = shfl_f64(top, (2 * lane + 1) & 31);
+        if (lane >= w && lane < 2 * w) top = __dadd_rn(l, r);
+    }
+    for (int o = 16; o; o >>= 1) mn = fmin(mn, shfl_f64(mn, lane ^ o));
+#pragma unroll 1
+    for (int b = 0; (int64_t(1) << b) <= need_hi; ++b) {
+        if ((need_hi >> b) & 1) {
+            const double t = shfl_f64(top, (int)((N >> b) + ((need_hi >> (b + 1)) << 1)));
+            acc = first ? t : __dadd_rn(t, acc);
+            first = false;
+        }
+    }
+    v.top = top;
+    v.root_sum = shfl_f64(top, 1);
+    v.root_min = mn;
+    v.seg = __ddiv_rn(acc, (double)a.batch);
+    return v;
+}
+
+// Mass of stratum q (memory.py:247) and its descent through the top tree: returns the owning
+// shard and leaves in `mass` the prefix sum inside that shard.  Every lane may ask for a different q.
+__device__ __forceinline__ int shard_owner(const SampleArgs &a, const double top, const double seg, const int64_t q, double &mass) {
+    const int N = a.n_shards;
+    mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));
+    int node = 1;
+    while (node < N) {  // log2(N) rounds on every lane
+        const double lv = shfl_f64(top, 2 * node);
+        if (lv > mass) {
+            node = 2 * node;
+        } else {
+            mass = __dsub_rn(mass, lv);
+            node = 2 * node + 1;
+        }
+    }
+    return node - N;
+}
+
+// First stratum whose owner is >= r (a.batch if there is none); all lanes return it.
+__device__ __forceinline__ int64_t first_stratum_of(const SampleArgs &a, const ShardView &v, const int r, const int lane) {
+    const int N = a.n_shards;
+    if (r <= 0) return 0;
+    if (r >= N) return a.batch;
+    double mass;
+    // prediction: the prefix of the shard roots below r, in units of the segment width
+    double below = (lane >= N && lane < N + r) ? v.top : 0.0;
+    for (int o = 16; o; o >>= 1) below += shfl_f64(below, lane ^ o);
+    const double guess = below / v.seg;
+    if (guess >= 0.0 && guess <= (double)a.batch) {  // also false for NaN (seg == 0)
+        const int64_t q = (int64_t)guess - 16 + lane;
+        const int64_t qc = q < 0 ? 0 : (q >= a.batch ? a.batch - 1 : q);
+        const bool own = shard_owner(a, v.top, v.seg, qc, mass) >= r;
+        const bool p = q >= a.batch || (q >= 0 && own);
+        const unsigned m = __ballot_sync(0xffffffffu, p);
+        if (m != 0 && !(m & 1u)) return (int64_t)guess - 16 + (__ffs(m) - 1);  // bracketed: lane 0 false, some lane true
+    }
+    int64_t base = 0, n = a.batch;  // answer in [base, base + n]
+    while (n > 0) {
+        const int64_t step = (n + 31) >> 5;
+        int64_t q = base + (lane + 1) * step - 1;  // last stratum of this lane's chunk
+        if (q > base + n - 1) q = base + n - 1;
+        const bool p = shard_owner(a, v.top, v.seg, q, mass) >= r;
+        const unsigned m = __ballot_sync(0xffffffffu, p);
+        if (m == 0) {
+            base += n;
+            break;
+        }
+        const int f = __ffs(m) - 1;
+        const int64_t cb = base + f * step;
+        int64_t ce = cb + step - 1;
+        if (ce > base + n - 1) ce = base + n - 1;
+        base = cb;  // strata cb .. ce-1 undecided, ce satisfies the predicate
+        n = ce - cb;
+    }
+    return base;
+}
+
+constexpr int SAMPLE_THREADS = 128;
+
+__global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
+    __shared__ double s_top[32];
+    __shared__ double s_scal[3];
+    __shared__ int64_t s_range[2];
+    pdl_launch_dependents();
+    pdl_wait();  // the tree is written by the kernel in front of this one
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last CTA of this launch retires
+    if (warp == 0) {
         if (a.use_mailbox) {
             // exchange through peer memory: the first warp of the grid publishes this shard's record to every
-            // rank, one warp per CTA waits for all ranks' records of this epoch, the CTA barrier releases the rest
-            const u64 t0 = (q == 0 && lane == 0) ? global_timer_ns() : 0;
-            if (q == 0) publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
-            if ((threadIdx.x >> 5) == 0) await_records(a.mailbox, a.n_shards, epoch, a.status);
-            if (q == 0 && lane == 0 && a.d_wait_stats) {
+            // rank; warp 0 of every CTA waits for all ranks' records of this epoch
+            const u64 t0 = (blockIdx.x == 0 && lane == 0) ? global_timer_ns() : 0;
+            if (blockIdx.x == 0 && !a.skip_publish)
+                publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
+            await_records(a.mailbox, a.n_shards, epoch, a.status);
+            if (blockIdx.x == 0 && lane == 0 && a.d_wait_stats) {
                 const u64 dt = global_timer_ns() - t0;
                 atomicAdd(a.d_wait_stats, 1ull);
                 atomicAdd(a.d_wait_stats + 1, dt);
                 atomicMax(a.d_wait_stats + 2, dt);
             }
-            __syncthreads();
+        }
+        const ShardView v = shard_view(a, epoch, lane);
+        const int64_t lo = first_stratum_of(a, v, a.rank, lane);
+        const int64_t hi = first_stratum_of(a, v, a.rank + 1, lane);
+        s_top[lane] = v.top;
+        if (lane == 0) {
+            s_scal[0] = v.root_sum;
+            s_scal[1] = v.root_min;
+            s_scal[2] = v.seg;
+            s_range[0] = lo;
+            s_range[1] = hi;
+            if (blockIdx.x == 0) {  // tags for the gather / update kernels that follow (owned_range)
+                a.d_range[0] = (epoch << 32) | (u64)(0xffffffffu - (unsigned)lo);
+                a.d_range[1] = (epoch << 32) | (u64)hi;
+            }
         }
     }
-    if (q < a.batch) sample_one(a, q, lane, epoch);  // whole warps take the same side
-    if (a.d_epoch && lane == 0) {
-        // last warp of the launch to retire advances the exchange epoch (every warp has read it by then)
+    __syncthreads();
+    const double top = s_top[lane], root_sum = s_scal[0], root_min = s_scal[1], seg = s_scal[2];
+    const int64_t lo = s_range[0], hi = s_range[1];
+    // strata of other shards
+    for (int64_t q = blockIdx.x * (int64_t)SAMPLE_THREADS + threadIdx.x; q < a.batch; q += (int64_t)gridDim.x * SAMPLE_THREADS) {
+        if (q < lo || q >= hi) {
+            a.out_idx[q] = -1;
+            if (a.out_w64) a.out_w64[q] = 0.0;
+            if (a.out_w32) a.out_w32[q] = 0.0f;
+        }
+    }
+    // own strata, one warp per query
+    const int64_t idx_base = (int64_t)a.rank * a.cap;
+    const int64_t warps = (int64_t)gridDim.x * (SAMPLE_THREADS / 32);
+    for (int64_t q = lo + blockIdx.x * (SAMPLE_THREADS / 32) + warp; q < hi; q += warps) {
+        double mass;
+        shard_owner(a, top, seg, q, mass);  // == a.rank by construction of [lo, hi)
+        descend_and_emit(a, q, lane, mass, root_sum, root_min, idx_base);
+    }
+    // the last CTA of the launch to retire advances the exchange epoch (every CTA has read it by then)
+    __syncthreads();
+    if (threadIdx.x == 0) {
         __threadfence();
-        const unsigned total = gridDim.x * (blockDim.x >> 5);
-        if (atomicAdd(a.d_done, 1u) == total - 1) {
+        if (atomicAdd(a.d_done, 1u) == gridDim.x - 1) {
             *a.d_done = 0;
             __threadfence();
             atomicAdd(a.d_epoch, 1ull);

@@ -243,6 +243,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             a.trace[slot] = t__;                                             \
         }                                                                    \
     } while (0)
+    pdl_launch_dependents();
+    pdl_wait();  // indices / Q tables / the tree itself come from the kernels in front of this one
     UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
     owned_range(a.range, a.n, first, last);

@@ -254,6 +254,8 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
+    if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
+        pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"pdl", int(os.environ["PER_PDL"])))
     use_mailbox = shard is not None and not args.nccl_exchange
     if use_mailbox:
         shard.enable_peer_exchange()  # CUDA-IPC mailboxes: the sampling kernel exchanges the records itself

@@ -328,7 +328,11 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
 /* Launch-shape knobs of the gather kernel, for the sweeps under profiles/ (not needed in
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies
  * through shared memory, 1 register-staged LDG/STG), "gather_warps", "gather_stages",
- * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm".  No reference counterpart. */
+ * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm"; "update_trace" (0/1, see
+ * per_update_trace); "pdl" (default 1: the sample, gather and update kernels are launched with
+ * programmatic stream serialization and begin with griddepcontrol.wait, so each one's launch
+ * and prologue overlap the tail of the kernel in front of it; 0 = plain launches).
+ * No reference counterpart. */
 int per_tune(per_buffer *b, const char *key, int64_t value);
 
 /* Diagnostics: after per_tune(b, "update_trace", 1) the one-launch update kernel stores the GPU
