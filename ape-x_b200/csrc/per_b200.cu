@@ -47,6 +47,8 @@ struct per_buffer_s {
     int sm_count;
     GatherTune tune;
     int sharded;               // created by per_create_shard: samples leave the owned-strata range on the device
+    int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
+    bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", 0/1): chain sample / gather / update launches with programmatic dependent launch
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
@@ -414,6 +416,7 @@ int per_add_batch(per_buffer *b, const void *d_obs, const void *d_next, const in
     if (!b || n < 0) return fail(PER_ERR_ARG, "per_add_batch: bad argument");
     if (n > b->ring_size) return fail(PER_ERR_ARG, "per_add_batch: n=%lld exceeds the ring size %lld", (long long)n, (long long)b->ring_size);
     if (n == 0) return PER_OK;
+    if (b->rec_published) return fail(PER_ERR_ARG, "early publish: the record of the next sample is already in the peers' mailboxes; sample before adding");
     DeviceGuard g(b->device);
     cudaStream_t s = (cudaStream_t)stream;
     AddArgs r;
@@ -488,6 +491,8 @@ int per_shard_record(per_buffer *b, int64_t global_len, double *d_out, void *str
 
 int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len) {
     if (!b || global_len < 0) return fail(PER_ERR_ARG, "per_shard_attach_record: bad argument");
+    if (b->rec_published && global_len != b->global_len)
+        return fail(PER_ERR_ARG, "early publish: the record of the next sample is already in the peers' mailboxes; sample before changing len");
     b->rec_out = d_record;
     b->global_len = global_len;
     return PER_OK;
@@ -599,7 +604,13 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
         a.peer_mailbox = b->d_peer_mailbox;
         a.rec_need = shard_need(global_len, b->idx_base, b->t.cap);
         a.rec_len = b->len;
+        if (b->rec_published) {
+            if (global_len != b->global_len)
+                return fail(PER_ERR_ARG, "early publish: the published record was computed for global_len %lld, not %lld", (long long)b->global_len, (long long)global_len);
+            a.skip_publish = 1;
+        }
     }
+    b->rec_published = false;
     b->last_sample_idx = d_out_idx;
     b->last_sample_batch = batch;
     // one warp per OWNED stratum in the expected case (batch / n_shards of them, plus slack); a shard that owns
@@ -731,6 +742,11 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->update_trace = value != 0;
         return PER_OK;
     }
+    if (!strcmp(key, "early_publish")) {
+        if (b->rec_published) return fail(PER_ERR_ARG, "early publish: a published record is pending; sample first");
+        b->early_publish = value != 0;
+        return PER_OK;
+    }
     if (!strcmp(key, "pdl")) {
         b->pdl = value != 0;
         return PER_OK;
@@ -773,6 +789,14 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.rec_need = shard_need(b->global_len, b->idx_base, b->t.cap);
     a.rec_len = b->len;
     a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    if (b->early_publish && b->mailbox && n <= UPD_CLUSTER_MAX_ITEMS) {
+        if (b->rec_published) return fail(PER_ERR_ARG, "early publish: the record of the next sample is already in the peers' mailboxes; sample before updating again");
+        a.publish_to = b->d_peer_mailbox;
+        a.n_shards = b->n_shards;
+        a.shard_rank = b->shard_rank;
+        a.d_epoch = b->xchg_epoch();
+        b->rec_published = true;
+    }
     a.trace = b->update_trace ? b->scal + 11 : nullptr;
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;

@@ -222,10 +222,20 @@ __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap
     write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
+// Left children of the first five generations below the root, lane layout of the descent
+// (generation j, pair qg -> lane 2^(j-1)-1+qg).  The same for every query, so callers load it
+// before they know the query's mass.
+__device__ __forceinline__ double root_block(const SampleArgs &a, const int lane) {
+    const int j = 32 - __clz(lane + 1);
+    const int qg = lane + 1 - (1 << (j - 1));
+    const int s = a.L < 5 ? a.L : 5;
+    return (j <= s && lane < 31) ? a.sum[(int64_t(1) << j) + 2 * qg] : 0.0;
+}
+
 // The local descent of one query (all 32 lanes) from the root of this tree, then the index and
-// the importance weight.  `mass` is the prefix sum looked for inside this tree.
-__device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int64_t q, const int lane, double mass, const double root_sum,
-                                                 const double root_min, const int64_t idx_base) {
+// the importance weight.  `mass` is the prefix sum looked for inside this tree, `left` = root_block().
+__device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int64_t q, const int lane, double mass, double left,
+                                                 const double root_sum, const double root_min, const int64_t idx_base) {
     // lane -> (generation j in 1..5, pair qg): lane 0 -> 1, lanes 1-2 -> 2, 3-6 -> 3, 7-14 -> 4, 15-30 -> 5
     const int j = 32 - __clz(lane + 1);
     const int qg = lane + 1 - (1 << (j - 1));
@@ -234,8 +244,7 @@ __device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int6
 #pragma unroll 1
     while (depth < a.L) {
         const int s = a.L - depth < 5 ? a.L - depth : 5;
-        double left = 0.0;
-        if (j <= s && lane < 31) left = a.sum[(node << j) + 2 * qg];
+        if (depth) left = (j <= s && lane < 31) ? a.sum[(node << j) + 2 * qg] : 0.0;
         int m = 0;  // path inside this 5-generation block
 #pragma unroll
         for (int g = 1; g <= 5; ++g) {
@@ -276,6 +285,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= a.batch) return;  // whole warps take the same side
+    const double left = root_block(a, lane);  // in flight together with the loads of the prefix total
     const double root_sum = a.sum[1];
     double mass;
     if (a.direct_mass) {
@@ -286,7 +296,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
         mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
     }
-    descend_and_emit(a, q, lane, mass, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
+    descend_and_emit(a, q, lane, mass, left, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -364,24 +374,11 @@ __device__ __forceinline__ int shard_owner(const SampleArgs &a, const double top
     return node - N;
 }
 
-// First stratum whose owner is >= r (a.batch if there is none); all lanes return it.
-__device__ __forceinline__ int64_t first_stratum_of(const SampleArgs &a, const ShardView &v, const int r, const int lane) {
-    const int N = a.n_shards;
+// First stratum whose owner is >= r (a.batch if there is none) by 32-ary search; all lanes return it.
+__device__ __forceinline__ int64_t first_stratum_search(const SampleArgs &a, const ShardView &v, const int r, const int lane) {
     if (r <= 0) return 0;
-    if (r >= N) return a.batch;
+    if (r >= a.n_shards) return a.batch;
     double mass;
-    // prediction: the prefix of the shard roots below r, in units of the segment width
-    double below = (lane >= N && lane < N + r) ? v.top : 0.0;
-    for (int o = 16; o; o >>= 1) below += shfl_f64(below, lane ^ o);
-    const double guess = below / v.seg;
-    if (guess >= 0.0 && guess <= (double)a.batch) {  // also false for NaN (seg == 0)
-        const int64_t q = (int64_t)guess - 16 + lane;
-        const int64_t qc = q < 0 ? 0 : (q >= a.batch ? a.batch - 1 : q);
-        const bool own = shard_owner(a, v.top, v.seg, qc, mass) >= r;
-        const bool p = q >= a.batch || (q >= 0 && own);
-        const unsigned m = __ballot_sync(0xffffffffu, p);
-        if (m != 0 && !(m & 1u)) return (int64_t)guess - 16 + (__ffs(m) - 1);  // bracketed: lane 0 false, some lane true
-    }
     int64_t base = 0, n = a.batch;  // answer in [base, base + n]
     while (n > 0) {
         const int64_t step = (n + 31) >> 5;
@@ -403,6 +400,37 @@ __device__ __forceinline__ int64_t first_stratum_of(const SampleArgs &a, const S
     return base;
 }
 
+// The strata [lo, hi) this shard owns.  One round trip in the expected case: the prefix of the shard
+// roots below rank (lanes 0..15) and below rank + 1 (lanes 16..31), in units of the segment width,
+// predicts each border to within a stratum; 16 strata around each prediction take the exact ownership
+// test, and a border counts as found only if it is bracketed (a false probe below a true one).
+__device__ __forceinline__ void owned_strata(const SampleArgs &a, const ShardView &v, const int lane, int64_t &lo, int64_t &hi) {
+    const int N = a.n_shards;
+    const int half = lane >> 4;            // 0: border below this shard, 1: border above it
+    const int r = a.rank + half;           // the predicate of this half-warp: owner >= r
+    double below = 0.0;                    // sum of the shard roots 0 .. r-1 (prediction only: any order will do)
+    for (int sidx = 0; sidx < N; ++sidx) {
+        const double root = shfl_f64(v.top, N + sidx);
+        if (sidx < r) below += root;
+    }
+    const double guess = below / v.seg;
+    const bool usable = guess >= 0.0 && guess <= (double)a.batch;  // false for NaN (seg == 0)
+    const int64_t g0 = usable ? (int64_t)guess : 0;
+    const int64_t q = g0 - 8 + (lane & 15);
+    const int64_t qc = q < 0 ? 0 : (q >= a.batch ? a.batch - 1 : q);
+    double mass;
+    const bool own = shard_owner(a, v.top, v.seg, qc, mass) >= r;
+    const bool p = r >= N ? q >= a.batch : (r <= 0 ? q >= 0 : (q >= a.batch || (q >= 0 && own)));
+    const unsigned m = __ballot_sync(0xffffffffu, p);
+    const unsigned ok = __ballot_sync(0xffffffffu, usable);
+    const unsigned m_lo = m & 0xffffu, m_hi = m >> 16;
+    const int64_t g_lo = __shfl_sync(0xffffffffu, g0, 0), g_hi = __shfl_sync(0xffffffffu, g0, 16);
+    if ((ok & 1u) && m_lo != 0 && !(m_lo & 1u)) lo = g_lo - 8 + (__ffs(m_lo) - 1);
+    else lo = first_stratum_search(a, v, a.rank, lane);
+    if ((ok & 0x10000u) && m_hi != 0 && !(m_hi & 1u)) hi = g_hi - 8 + (__ffs(m_hi) - 1);
+    else hi = first_stratum_search(a, v, a.rank + 1, lane);
+}
+
 constexpr int SAMPLE_THREADS = 128;
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
@@ -412,11 +440,13 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
     pdl_launch_dependents();
     pdl_wait();  // the tree is written by the kernel in front of this one
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u64 epoch = __ldcg(a.d_epoch) + 1;  // stable until the last CTA of this launch retires
+    const double left = root_block(a, lane);  // needed after the exchange; requested before it
     if (warp == 0) {
+        // only this warp reads the epoch counter, so that it can be advanced as soon as every CTA's warp 0 has it
+        const u64 epoch = __ldcg(a.d_epoch) + 1;
         if (a.use_mailbox) {
             // exchange through peer memory: the first warp of the grid publishes this shard's record to every
-            // rank; warp 0 of every CTA waits for all ranks' records of this epoch
+            // rank (unless the update kernel in front has done so); warp 0 of every CTA waits for all ranks' records
             const u64 t0 = (blockIdx.x == 0 && lane == 0) ? global_timer_ns() : 0;
             if (blockIdx.x == 0 && !a.skip_publish)
                 publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
@@ -429,8 +459,8 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
             }
         }
         const ShardView v = shard_view(a, epoch, lane);
-        const int64_t lo = first_stratum_of(a, v, a.rank, lane);
-        const int64_t hi = first_stratum_of(a, v, a.rank + 1, lane);
+        int64_t lo, hi;
+        owned_strata(a, v, lane, lo, hi);
         s_top[lane] = v.top;
         if (lane == 0) {
             s_scal[0] = v.root_sum;
@@ -445,6 +475,15 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         }
     }
     __syncthreads();
+    if (threadIdx.x == 32 || (blockDim.x == 32 && threadIdx.x == 0)) {
+        // warp 0 of this CTA has consumed the epoch: the last CTA to say so advances it (nothing in this launch
+        // reads it again; the kernels behind this one see the new value)
+        if (atomicAdd(a.d_done, 1u) == gridDim.x - 1) {
+            *a.d_done = 0;
+            __threadfence();
+            atomicAdd(a.d_epoch, 1ull);
+        }
+    }
     const double top = s_top[lane], root_sum = s_scal[0], root_min = s_scal[1], seg = s_scal[2];
     const int64_t lo = s_range[0], hi = s_range[1];
     // strata of other shards
@@ -461,17 +500,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
     for (int64_t q = lo + blockIdx.x * (SAMPLE_THREADS / 32) + warp; q < hi; q += warps) {
         double mass;
         shard_owner(a, top, seg, q, mass);  // == a.rank by construction of [lo, hi)
-        descend_and_emit(a, q, lane, mass, root_sum, root_min, idx_base);
-    }
-    // the last CTA of the launch to retire advances the exchange epoch (every CTA has read it by then)
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(a.d_done, 1u) == gridDim.x - 1) {
-            *a.d_done = 0;
-            __threadfence();
-            atomicAdd(a.d_epoch, 1ull);
-        }
+        descend_and_emit(a, q, lane, mass, left, root_sum, root_min, idx_base);
     }
 }
 

@@ -66,6 +66,9 @@ struct UpdArgs {
     int sorted_idx;           // the indices are non-decreasing (they are the stratified sample just drawn): equal
                               // indices are adjacent, so "a later duplicate wins" needs one look at idx[j+1], no atomics
     u64 *trace;               // diagnostics: CTA 0 / thread 0 stores globaltimer ns at phase boundaries (null: off)
+    double *const *publish_to; // sharded replay, early publish: the mailboxes of all ranks (null: the next sample publishes)
+    int n_shards, shard_rank;  //   this launch's tail stores the refreshed record, tagged with the NEXT exchange epoch
+    const u64 *d_epoch;        //   (completed exchange samples + 1), straight into them
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
 };
@@ -420,7 +423,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     if (rank == 0) {
         dense_lift_block(a.t, 1, top, s_sum, s_min);
         UPD_TRACE(5);
+        if (a.rec_out || a.publish_to) {  // the record's prefix chain reads nodes other threads have just written
+            __threadfence();
+            __syncthreads();
+        }
         if (a.rec_out && tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
+        if (a.publish_to && tid < 32)
+            publish_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.publish_to, a.n_shards, a.shard_rank, __ldcg(a.d_epoch) + 1);
     }
 }
 
@@ -481,6 +490,10 @@ __global__ void __launch_bounds__(1024) k_dense_top(TreeRef t, int top, double *
     __shared__ __align__(16) double s_sum[2 * TOP_NODES];
     __shared__ __align__(16) double s_min[2 * TOP_NODES];
     dense_lift_block(t, 1, top, s_sum, s_min);
+    if (rec_out) {  // the record's prefix chain reads nodes other threads have just written
+        __threadfence();
+        __syncthreads();
+    }
     if (rec_out && threadIdx.x < 32) write_shard_record(t.sum, t.mnn, t.cap, rec_need, rec_len, rec_out);
 }
 

@@ -177,6 +177,13 @@ class ShardedReplay(object):
         for s in shards:
             s._attach_exchange(boxes[s.rank], boxes)
 
+    def enable_early_publish(self, on=True):
+        """Every priority update then ends by storing the refreshed record straight into the peers'
+        mailboxes (per_tune "early_publish", include/per_b200.h): the next sample only waits for
+        the records.  All ranks switch together, and nothing may modify the replay between an
+        update and the next sample while it is on (the native calls refuse)."""
+        _n.check(_n.lib.per_tune(self._h, b"early_publish", 1 if on else 0))
+
     def publish_record(self):
         _n.check(_n.lib.per_shard_publish(self._h, self._len, _n.stream_ptr()))
 

@@ -194,6 +194,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-early-publish", action="store_true",
+                    help="world > 1: the sampling kernel publishes its own record instead of the preceding update kernel")
     ap.add_argument("--eager", action="store_true", help="time plain launches instead of CUDA graphs")
     ap.add_argument("--trace", action="store_true", help="also print per-call GPU time of sample / gather / update (eager, events)")
     ap.add_argument("--nccl-exchange", action="store_true",
@@ -314,6 +316,8 @@ def main():
         torch.cuda.synchronize()
         assert torch.equal(idx, idx_collective), "peer-memory exchange and NCCL exchange disagree"
         assert int((idx >= 0).sum().item()) > 0
+        if not args.no_early_publish:  # the update kernel's tail publishes the next sample's record
+            shard.enable_early_publish()
 
     def step(i, ev=None):
         if use_mailbox:  # the sampling kernel publishes / awaits the 32-byte records over NVLink itself
@@ -399,6 +403,13 @@ def main():
     # step is kernels only, so world > 1 is captured too)
     if not args.eager and (world == 1 or use_mailbox):
         try:
+            # the graphs run a step as [TD + update of the previous batch, sample, gather]; the warm-up ended with
+            # an update, so draw one batch first (with early publish two updates in a row are refused)
+            if use_mailbox:
+                pn.check(lib.per_sample_sharded(h, None, u_ptrs[0], GB, BETA, glen, a_idx, None, a_w32, sp))
+            else:
+                pn.check(lib.per_sample_indices(h, u_ptrs[0], GB, BETA, a_idx, None, a_w32, sp))
+            pn.check(lib.per_gather(*a_gather))
             side = torch.cuda.Stream()
             side.wait_stream(stream)
             with torch.cuda.stream(side):

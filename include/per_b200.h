@@ -331,7 +331,14 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm"; "update_trace" (0/1, see
  * per_update_trace); "pdl" (default 1: the sample, gather and update kernels are launched with
  * programmatic stream serialization and begin with griddepcontrol.wait, so each one's launch
- * and prologue overlap the tail of the kernel in front of it; 0 = plain launches).
+ * and prologue overlap the tail of the kernel in front of it; 0 = plain launches);
+ * "early_publish" (default 0; needs per_shard_attach_exchange): every priority update ends by
+ * storing the refreshed shard record, tagged with the next exchange epoch, into all ranks'
+ * mailboxes, so the record is on its way over NVLink while the update kernel retires and the next
+ * per_sample_sharded only has to wait for it.  Contract while it is on, on EVERY rank alike:
+ * between an update and the next sample nothing else may modify the tree or the replay length
+ * (per_add_batch, a second update, per_shard_attach_record with another len fail loudly); ingest
+ * goes between a sample and its update, or switch the knob off around it.
  * No reference counterpart. */
 int per_tune(per_buffer *b, const char *key, int64_t value);
 

@@ -140,11 +140,12 @@ def test_sharded_fused_td_update(mods):
         assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
 
 
-@pytest.mark.parametrize("world", [2, 8])
-def test_peer_mailbox_exchange_matches_collective(mods, world):
+@pytest.mark.parametrize("world,early", [(2, False), (8, False), (2, True), (8, True)])
+def test_peer_mailbox_exchange_matches_collective(mods, world, early):
     """The record exchange through mailboxes (per_shard_attach_exchange) must give the same
     indices as the all-gathered records.  Ranks share one GPU here, so every rank publishes with
-    per_shard_publish before any of them samples (on separate GPUs the sampling kernel does both)."""
+    per_shard_publish before any of them samples (on separate GPUs the sampling kernel does both).
+    early: the update kernels publish the next sample's record themselves (per_tune early_publish)."""
     memory, sharded, pn = mods
     size, batch = 6000, 512
     data = make_data(size, (2, 8), 11 + world)
@@ -154,12 +155,16 @@ def test_peer_mailbox_exchange_matches_collective(mods, world):
     for s in shards:
         s.add_batch_device(*data)
     sharded.ShardedReplay.enable_local_exchange(shards)
+    if early:
+        for s in shards:
+            s.enable_early_publish()
     rng = np.random.default_rng(5)
     for step in range(4):  # several epochs: both mailbox parities, flags from earlier epochs left behind
         u = rng.random(batch)
         want = single.sample_device(batch, 0.4, uniforms=u, gather=False)
-        for s in shards:
-            s.publish_record()
+        if not early or step == 0:
+            for s in shards:
+                s.publish_record()
         merged = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
         for s in shards:
             d = s.sample_device(batch, 0.4, u, gather=False)
@@ -172,3 +177,11 @@ def test_peer_mailbox_exchange_matches_collective(mods, world):
         for s in shards:
             own = torch.where((merged // s.tree_capacity_local) == s.rank, merged, torch.full_like(merged, -1))
             s.update_priorities_device(own, newp)
+    if early:  # the contract is enforced: nothing may touch the tree between an update and the next sample
+        s = shards[0]
+        with pytest.raises(Exception, match="early publish"):
+            s.update_priorities_device(own, newp)
+        with pytest.raises(Exception, match="early publish"):
+            s.add_batch_device(*[t[:8].contiguous() for t in data])
+        with pytest.raises(Exception, match="early publish"):
+            s.enable_early_publish(False)
