@@ -47,6 +47,8 @@ struct per_buffer_s {
     int sm_count;
     GatherTune tune;
     int sharded;               // created by per_create_shard: samples leave the owned-strata range on the device
+    u64 *timeline;             // per_tune("timeline", entries): kernel time stamps, read by per_timeline
+    unsigned timeline_cap;
     int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
     bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", 0/1): chain sample / gather / update launches with programmatic dependent launch
@@ -370,6 +372,7 @@ int per_destroy(per_buffer *b) {
     cudaFree(b->t.mnn);
     cudaFree(b->stamps);
     cudaFree(b->scal);
+    cudaFree(b->timeline);
     cudaFree(b->obs);
     cudaFree(b->next);
     cudaFree(b->extra);
@@ -473,6 +476,8 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.out_w64 = d_out_w64;
     a.out_w32 = d_out_w32;
     a.status = b->status();
+    a.tl = b->timeline;
+    a.tl_cap = b->timeline_cap;
     PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, b->pdl != 0, a));
     PER_CUDA(cudaGetLastError());
     b->last_sample_idx = d_out_idx;
@@ -553,6 +558,25 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream) {
     return PER_OK;
 }
 
+int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_count, void *stream) {
+    if (!b || !h_out || !h_count || max_entries < 0) return fail(PER_ERR_ARG, "per_timeline: bad argument");
+    *h_count = 0;
+    if (!b->timeline) return PER_OK;
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    u64 n = 0;
+    PER_CUDA(cudaMemcpyAsync(&n, b->timeline, sizeof(u64), cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaStreamSynchronize(s));
+    n &= 0xffffffffull;
+    if (n > b->timeline_cap) n = b->timeline_cap;
+    if ((int64_t)n > max_entries) n = (u64)max_entries;
+    if (n) PER_CUDA(cudaMemcpyAsync(h_out, b->timeline + 1, sizeof(u64) * n, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemsetAsync(b->timeline, 0, sizeof(u64), s));
+    PER_CUDA(cudaStreamSynchronize(s));
+    *h_count = (int64_t)n;
+    return PER_OK;
+}
+
 int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream) {
     if (!b || !h_out6) return fail(PER_ERR_ARG, "per_update_trace: bad argument");
     DeviceGuard g(b->device);
@@ -597,6 +621,8 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     a.d_epoch = b->xchg_epoch();
     a.d_done = b->xchg_done();
     a.d_range = b->scal + 5;
+    a.tl = b->timeline;
+    a.tl_cap = b->timeline_cap;
     if (!d_records) {  // records travel through the peer-memory mailboxes
         a.use_mailbox = 1;
         a.d_wait_stats = b->scal + 8;
@@ -673,6 +699,8 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
     a.piece = slow.piece = tn.piece;
     a.stages = slow.stages = tn.stages;
+    a.tl = b->timeline;
+    a.tl_cap = b->timeline_cap;
     const int64_t items = batch * per_query;
     if (tn.mode == 0) {
         int64_t grid = (items + tn.warps - 1) / tn.warps;
@@ -742,6 +770,19 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->update_trace = value != 0;
         return PER_OK;
     }
+    if (!strcmp(key, "timeline")) {
+        DeviceGuard g(b->device);
+        PER_CUDA(cudaDeviceSynchronize());
+        cudaFree(b->timeline);
+        b->timeline = nullptr;
+        b->timeline_cap = 0;
+        if (value > 0) {
+            PER_CUDA(cudaMalloc(&b->timeline, sizeof(u64) * (size_t)(value + 1)));
+            PER_CUDA(cudaMemset(b->timeline, 0, sizeof(u64) * (size_t)(value + 1)));
+            b->timeline_cap = (unsigned)value;
+        }
+        return PER_OK;
+    }
     if (!strcmp(key, "early_publish")) {
         if (b->rec_published) return fail(PER_ERR_ARG, "early publish: a published record is pending; sample first");
         b->early_publish = value != 0;
@@ -798,6 +839,8 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
         b->rec_published = true;
     }
     a.trace = b->update_trace ? b->scal + 11 : nullptr;
+    a.tl = b->timeline;
+    a.tl_cap = b->timeline_cap;
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     return run_update(a, td, 0, b->sm_count, s, b->pdl != 0);

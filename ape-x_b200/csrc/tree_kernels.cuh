@@ -28,10 +28,9 @@ namespace perb {
 // starts where the higher bits of `need` end, i.e. node (cap >> b) + (need >> (b+1) << 1).
 // Lane b owns bit b, so all loads go out together; the chain is then folded innermost
 // (lowest bit) first.  Every lane returns the total.  Requires cap <= 2^31.
-__device__ __forceinline__ double warp_prefix_total(const double *v, int64_t cap, int64_t need) {
-    const int lane = threadIdx.x & 31;
-    const bool emit = (need >> lane) & 1;
-    const double term = emit ? __ldcg(v + (cap >> lane) + ((need >> (lane + 1)) << 1)) : 0.0;
+__device__ __forceinline__ int64_t prefix_term_node(int64_t cap, int64_t need, int b) { return (cap >> b) + ((need >> (b + 1)) << 1); }
+// lane b holds the term of bit b (anything where the bit is clear); every lane returns t1 + (t2 + (... + tk))
+__device__ __forceinline__ double warp_prefix_fold(const double term, const int64_t need) {
     double acc = 0.0;
     bool first = true;
 #pragma unroll
@@ -43,6 +42,12 @@ __device__ __forceinline__ double warp_prefix_total(const double *v, int64_t cap
         }
     }
     return acc;
+}
+__device__ __forceinline__ double warp_prefix_total(const double *v, int64_t cap, int64_t need) {
+    const int lane = threadIdx.x & 31;
+    const bool emit = (need >> lane) & 1;
+    const double term = emit ? __ldcg(v + prefix_term_node(cap, need, lane)) : 0.0;
+    return warp_prefix_fold(term, need);
 }
 
 // General [lo, hi] (inclusive) by one thread.  At the node where the range splits the
@@ -138,6 +143,8 @@ struct SampleArgs {
     int use_mailbox;             // 1: exchange through the mailboxes; 0: records come in `recs`
     u64 *d_wait_stats;           // {waits, total ns, max ns} spent by CTA 0 between kernel start and the last record's arrival
     int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
+    u64 *tl;                     // timeline (diagnostics), see tl_stamp
+    unsigned tl_cap;
     int skip_publish;            // 1: this epoch's record is in the mailboxes already (published by the update kernel)
 };
 
@@ -159,21 +166,39 @@ __device__ __forceinline__ void st_release_sys(u64 *p, u64 v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// One warp: computes this shard's record and stores it, then the epoch flag, into the slot
-// [epoch & 1][rank] of every rank's mailbox (lane p -> rank p; plain stores to peer-mapped
-// addresses travel over NVLink).  The flag is a system-scope release store, polled with acquire loads.
-__device__ __forceinline__ void publish_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
-                                               int64_t len_local, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
+// One warp: computes this shard's record once and stores it where asked: into `rec_out` (4 doubles,
+// the all-gather path) and / or, with the epoch flag, into the slot [epoch & 1][rank] of every rank's
+// mailbox (lane p -> rank p; plain stores to peer-mapped addresses travel over NVLink).  The flag is a
+// system-scope release store, polled with acquire loads.
+// The record (one per shard and sample call): the two roots, and the shard-local part of the
+// reference's  sum(0, len-1)  chain (memory.py:244): the prefix over this shard's first `need_local`
+// leaves when the global prefix ends inside this shard.  Nodes are read through L2 (the caller may
+// have just written them).
+__device__ __forceinline__ void emit_record_values(const double rs, const double rm, const double partial, int64_t len_local,
+                                                   double *rec_out, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
     const int lane = threadIdx.x & 31;
-    double partial = 0.0;
-    if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
-    const double rs = __ldcg(sum + 1), rm = __ldcg(mnn + 1);
-    if (lane < n_shards) {
+    if (rec_out && lane == 0) {
+        rec_out[0] = rs;
+        rec_out[1] = rm;
+        rec_out[2] = partial;
+        rec_out[3] = (double)len_local;
+    }
+    if (peer_mailbox && lane < n_shards) {
         double *slot = peer_mailbox[lane] + ((epoch & 1) * n_shards + rank) * MAIL_SLOT;
         reinterpret_cast<double2 *>(slot)[0] = make_double2(rs, rm);
         reinterpret_cast<double2 *>(slot)[1] = make_double2(partial, (double)len_local);
         st_release_sys(reinterpret_cast<u64 *>(slot + SHARD_REC), epoch);  // orders the record in front of the flag
     }
+}
+__device__ __forceinline__ void emit_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
+                                            double *rec_out, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
+    double partial = 0.0;
+    if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
+    emit_record_values(__ldcg(sum + 1), __ldcg(mnn + 1), partial, len_local, rec_out, peer_mailbox, n_shards, rank, epoch);
+}
+__device__ __forceinline__ void publish_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
+                                               int64_t len_local, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
+    emit_record(sum, mnn, cap, need_local, len_local, nullptr, peer_mailbox, n_shards, rank, epoch);
 }
 
 // All lanes of the calling warp return once every rank's slot of this epoch has arrived in the
@@ -201,20 +226,9 @@ __global__ void k_shard_publish(const double *sum, const double *mnn, int64_t ca
     publish_record(sum, mnn, cap, need_local, len_local, peer_mailbox, n_shards, rank, __ldcg(d_epoch) + 1);
 }
 
-// One record per shard and sample call, all-gathered across ranks: the two roots, and the
-// shard-local part of the reference's  sum(0, len-1)  chain (memory.py:244): the prefix over
-// this shard's first `need_local` leaves when the global prefix ends inside this shard.
-// Called by one full warp.  Nodes are read through L2 (the caller may have just written them).
 __device__ __forceinline__ void write_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local,
                                                    int64_t len_local, double *out) {
-    double partial = 0.0;
-    if (need_local > 0 && need_local < cap) partial = warp_prefix_total(sum, cap, need_local);
-    if ((threadIdx.x & 31) == 0) {
-        out[0] = __ldcg(sum + 1);
-        out[1] = __ldcg(mnn + 1);
-        out[2] = partial;
-        out[3] = (double)len_local;
-    }
+    emit_record(sum, mnn, cap, need_local, len_local, out, nullptr, 0, 0, 0);
 }
 
 __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
@@ -280,8 +294,11 @@ __device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int6
 
 // Unsharded: one warp per query.
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
+    const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 1);
     pdl_launch_dependents();
     pdl_wait();  // the tree is written by the kernel in front of this one
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 2);
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= a.batch) return;  // whole warps take the same side
@@ -297,6 +314,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
     }
     descend_and_emit(a, q, lane, mass, left, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 3);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -431,16 +449,24 @@ __device__ __forceinline__ void owned_strata(const SampleArgs &a, const ShardVie
     else hi = first_stratum_search(a, v, a.rank + 1, lane);
 }
 
-constexpr int SAMPLE_THREADS = 128;
+constexpr int SAMPLE_THREADS = 512;  // few, large CTAs: warp 0 of each polls the mailbox flags while the update kernel in front still runs
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
     __shared__ double s_top[32];
     __shared__ double s_scal[3];
     __shared__ int64_t s_range[2];
+    const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 1);
     pdl_launch_dependents();
-    pdl_wait();  // the tree is written by the kernel in front of this one
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const double left = root_block(a, lane);  // needed after the exchange; requested before it
+    // With early publish the records of this sample come from update kernels (this rank's and the peers'), through
+    // release / acquire flags: that part does not depend on the completion of the kernel in front, so warp 0 runs it
+    // BEFORE the programmatic-launch wait, while that kernel (normally this rank's update, which releases its
+    // dependents only after its own wait, i.e. after the previous sample has retired and advanced the epoch) is
+    // still running.  Everything that reads the tree or the caller's inputs comes after the wait.
+    const bool early = a.use_mailbox && a.skip_publish;
+    if (!early) pdl_wait();
+    double left = 0.0;
     if (warp == 0) {
         // only this warp reads the epoch counter, so that it can be advanced as soon as every CTA's warp 0 has it
         const u64 epoch = __ldcg(a.d_epoch) + 1;
@@ -459,6 +485,10 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
             }
         }
         const ShardView v = shard_view(a, epoch, lane);
+        if (tl_on) tl_stamp(a.tl, a.tl_cap, 10);  // records in, view built
+        if (early) pdl_wait();
+        if (tl_on) tl_stamp(a.tl, a.tl_cap, 2);   // the kernel in front has retired
+        left = root_block(a, lane);
         int64_t lo, hi;
         owned_strata(a, v, lane, lo, hi);
         s_top[lane] = v.top;
@@ -473,9 +503,13 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
                 a.d_range[1] = (epoch << 32) | (u64)hi;
             }
         }
+    } else {
+        if (early) pdl_wait();
+        left = root_block(a, lane);  // the same for every query: requested before the range is known
     }
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 11);  // owned strata known
     __syncthreads();
-    if (threadIdx.x == 32 || (blockDim.x == 32 && threadIdx.x == 0)) {
+    if (threadIdx.x == 32) {
         // warp 0 of this CTA has consumed the epoch: the last CTA to say so advances it (nothing in this launch
         // reads it again; the kernels behind this one see the new value)
         if (atomicAdd(a.d_done, 1u) == gridDim.x - 1) {
@@ -502,6 +536,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         shard_owner(a, top, seg, q, mass);  // == a.rank by construction of [lo, hi)
         descend_and_emit(a, q, lane, mass, left, root_sum, root_min, idx_base);
     }
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 3);
 }
 
 }  // namespace perb

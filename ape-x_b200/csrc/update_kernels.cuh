@@ -69,6 +69,8 @@ struct UpdArgs {
     double *const *publish_to; // sharded replay, early publish: the mailboxes of all ranks (null: the next sample publishes)
     int n_shards, shard_rank;  //   this launch's tail stores the refreshed record, tagged with the NEXT exchange epoch
     const u64 *d_epoch;        //   (completed exchange samples + 1), straight into them
+    u64 *tl;                  // timeline (diagnostics), see tl_stamp
+    unsigned tl_cap;
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
 };
@@ -246,8 +248,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             a.trace[slot] = t__;                                             \
         }                                                                    \
     } while (0)
-    pdl_launch_dependents();
+    // Wait first, release second: the sampling kernel behind this one starts its record exchange before its own
+    // wait (tree_kernels.cuh) and relies on every kernel up to the previous sample having retired by then.
+    const bool tl_on = a.tl && rank == 0 && tid == 0;
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 7);
     pdl_wait();  // indices / Q tables / the tree itself come from the kernels in front of this one
+    pdl_launch_dependents();
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 8);
     UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
     owned_range(a.range, a.n, first, last);
@@ -351,6 +358,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         else __syncthreads();
         if (skip_update) return;
     }
+    if (tl_on) tl_stamp(a.tl, a.tl_cap, 12);  // TD arithmetic done
 
     UPD_TRACE(1);
     // phase 1
@@ -421,15 +429,24 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     UPD_TRACE(4);
     // phase 4
     if (rank == 0) {
+        // The shard record (roots + prefix chain) needs nothing from global memory that the dense rebuild writes:
+        // the chain's terms above the dense top are taken from shared memory afterwards, the ones below it are
+        // final since the last cluster barrier and are requested now, so their round trip hides behind the rebuild.
+        const bool want_rec = a.rec_out || a.publish_to;
+        const bool want_partial = want_rec && a.rec_need > 0 && a.rec_need < a.t.cap;
+        const bool emit = want_partial && tid < 32 && ((a.rec_need >> tid) & 1);
+        const int64_t term_node = prefix_term_node(a.t.cap, a.rec_need, tid & 31);
+        const bool term_low = a.t.L - (tid & 31) > top;  // the node lies below the dense top
+        double term = (emit && term_low) ? __ldcg(a.t.sum + term_node) : 0.0;
         dense_lift_block(a.t, 1, top, s_sum, s_min);
         UPD_TRACE(5);
-        if (a.rec_out || a.publish_to) {  // the record's prefix chain reads nodes other threads have just written
-            __threadfence();
-            __syncthreads();
+        if (want_rec && tid < 32) {
+            if (emit && !term_low) term = s_sum[term_node];
+            const double partial = want_partial ? warp_prefix_fold(term, a.rec_need) : 0.0;
+            emit_record_values(s_sum[1], s_min[1], partial, a.rec_len, a.rec_out, a.publish_to, a.n_shards, a.shard_rank,
+                               a.publish_to ? __ldcg(a.d_epoch) + 1 : 0);
         }
-        if (a.rec_out && tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
-        if (a.publish_to && tid < 32)
-            publish_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.publish_to, a.n_shards, a.shard_rank, __ldcg(a.d_epoch) + 1);
+        if (tl_on) tl_stamp(a.tl, a.tl_cap, 9);
     }
 }
 

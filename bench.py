@@ -194,6 +194,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--timeline", action="store_true",
+                    help="diagnostic: after the timed region replay two graph blocks with the kernels' GPU-timer stamps on "
+                         "(per_timeline) and print each rank's median step anatomy to stderr")
     ap.add_argument("--no-early-publish", action="store_true",
                     help="world > 1: the sampling kernel publishes its own record instead of the preceding update kernel")
     ap.add_argument("--eager", action="store_true", help="time plain launches instead of CUDA graphs")
@@ -256,6 +259,8 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
+    if args.timeline:
+        pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"timeline", 8192))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"pdl", int(os.environ["PER_PDL"])))
     use_mailbox = shard is not None and not args.nccl_exchange
@@ -478,6 +483,35 @@ def main():
         st3 = (pn.C.c_int64 * 3)()
         pn.check(lib.per_shard_exchange_stats(h, st3, sp))
         exchange_us = {"mean": st3[1] / max(st3[0], 1) / 1e3, "max": st3[2] / 1e3, "samples": int(st3[0])}
+    if args.timeline and graphs is not None:
+        cap_tl = 8192
+        arr = (pn.C.c_int64 * cap_tl)()
+        cnt = pn.C.c_int64(0)
+        pn.check(lib.per_timeline(h, arr, cap_tl, pn.C.byref(cnt), sp))  # clear
+        barrier()
+        for blk in range(3):
+            graphs[blk % N_GRAPHS].replay()
+        barrier()
+        pn.check(lib.per_timeline(h, arr, cap_tl, pn.C.byref(cnt), sp))
+        ent = sorted(((int(arr[i]) & ((1 << 56) - 1), (int(arr[i]) >> 56) & 0xff) for i in range(cnt.value)))
+        names = {7: "update entered", 8: "update past wait", 12: "TD done", 9: "update CTA0 done", 1: "sample entered",
+                 10: "records in", 2: "sample past wait", 11: "strata known", 3: "sample CTA0 done", 4: "gather entered",
+                 5: "gather past wait", 6: "gather CTA0 done"}
+        steps_tl, cur = [], None
+        for t, tag in ent:  # a step of the graph = [update, sample, gather]; anchor = update past its wait
+            if tag == 8:
+                if cur:
+                    steps_tl.append(cur)
+                cur = {"t0": t}
+            elif cur is not None and tag not in cur:
+                cur[tag] = t - cur["t0"]
+        periods = np.diff([c["t0"] for c in steps_tl]) if len(steps_tl) > 2 else np.array([0])
+        msg = "rank %d timeline (us after 'update past wait', median of %d steps; period %.2f): " % (rank, len(steps_tl), float(np.median(periods)) / 1e3)
+        for tag in (12, 9, 1, 10, 2, 11, 3, 4, 5, 6, 7):
+            vals = [c[tag] for c in steps_tl[2:] if tag in c]
+            if vals:
+                msg += "%s %.2f | " % (names[tag], float(np.median(vals)) / 1e3)
+        sys.stderr.write(msg + "\n")
     value = GB * K / (ms * 1e-3)
     rows_this_rank = int((idx >= 0).sum().item())
     status = pn.C.c_int64(0)
