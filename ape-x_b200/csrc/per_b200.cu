@@ -51,7 +51,8 @@ struct per_buffer_s {
     unsigned timeline_cap;
     int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
     bool rec_published;        //   ... and one has done so since the last sample
-    int pdl;                   // per_tune("pdl", 0/1): chain sample / gather / update launches with programmatic dependent launch
+    int pdl;                   // per_tune("pdl", bits): programmatic dependent launch for 1 sampling, 2 gather, 4 update kernels
+    int sorted_update;         // per_tune("sorted_update", 0/1): updates of the sample just drawn take the sorted fast path
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
     int64_t last_sample_batch;       //   update calls that pass the same buffer visit only the strata this shard owns
@@ -294,7 +295,8 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     per_buffer *b = new per_buffer();
     memset(b, 0, sizeof *b);
     b->device = device;
-    b->pdl = 1;
+    b->pdl = 3;
+    b->sorted_update = 1;
     b->ring_size = ring_size;
     b->alpha = alpha;
     b->obs_bytes = obs_bytes;
@@ -478,7 +480,7 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.status = b->status();
     a.tl = b->timeline;
     a.tl_cap = b->timeline_cap;
-    PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, b->pdl != 0, a));
+    PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
     PER_CUDA(cudaGetLastError());
     b->last_sample_idx = d_out_idx;
     b->last_sample_batch = batch;
@@ -644,7 +646,7 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     int64_t warps = batch / b->n_shards + batch / (4 * b->n_shards) + 4;
     if (warps > batch) warps = batch;
     const int64_t ctas = (warps * 32 + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
-    PER_CUDA(launch_pdl(k_sample_sharded, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, b->pdl != 0, a));
+    PER_CUDA(launch_pdl(k_sample_sharded, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
@@ -707,7 +709,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;  // persistent CTAs
         if (grid < 1) grid = 1;
         const size_t smem = per_query ? (size_t)round_up(tn.warps * tn.stages * 8, 128) + (size_t)tn.warps * tn.stages * tn.piece : 0;
-        PER_CUDA(launch_pdl(k_gather_tma, dim3((unsigned)grid), dim3(tn.warps * 32), smem, s, b->pdl != 0, a, per_query));
+        PER_CUDA(launch_pdl(k_gather_tma, dim3((unsigned)grid), dim3(tn.warps * 32), smem, s, (b->pdl & 2) != 0, a, per_query));
     } else {
         int64_t grid = (items + 7) / 8;
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;
@@ -788,8 +790,12 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->early_publish = value != 0;
         return PER_OK;
     }
-    if (!strcmp(key, "pdl")) {
-        b->pdl = value != 0;
+    if (!strcmp(key, "sorted_update")) {
+        b->sorted_update = value != 0;
+        return PER_OK;
+    }
+    if (!strcmp(key, "pdl")) {  // bit 0: sampling kernels, bit 1: gather, bit 2: update
+        b->pdl = (int)value;
         return PER_OK;
     }
     if (!strcmp(key, "gather_mode")) t.mode = (int)value;
@@ -843,7 +849,8 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.tl_cap = b->timeline_cap;
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
-    return run_update(a, td, 0, b->sm_count, s, b->pdl != 0);
+    a.sorted_fast = b->sorted_update;
+    return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);
 }
 
 int per_update_priorities(per_buffer *b, const int64_t *d_idx, const void *d_prio, int prio_dtype, int64_t n, void *stream) {
@@ -902,7 +909,7 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
         memset(&a, 0, sizeof a);
         a.t = b->t;
         a.n = batch;
-        return run_update(a, &t, 1, b->sm_count, s, b->pdl != 0);
+        return run_update(a, &t, 1, b->sm_count, s, (b->pdl & 4) != 0);
     }
     const int grid = grid_for(batch, 256, b->sm_count);
     k_td_reset<<<1, 1, 0, s>>>(t.red);

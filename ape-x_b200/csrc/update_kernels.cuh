@@ -63,6 +63,7 @@ struct UpdArgs {
     double *rec_out;          // sharded replay: refresh this shard's 4-double record after the update (may be null)
     int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
     int64_t rec_len;          //   local len
+    int sorted_fast;          // sorted_idx: take the per-CTA climb (sorted fast path) instead of the level-synchronous rounds
     int sorted_idx;           // the indices are non-decreasing (they are the stratified sample just drawn): equal
                               // indices are adjacent, so "a later duplicate wins" needs one look at idx[j+1], no atomics
     u64 *trace;               // diagnostics: CTA 0 / thread 0 stores globaltimer ns at phase boundaries (null: off)
@@ -170,13 +171,16 @@ __device__ __forceinline__ void lift8_both(const TreeRef &t, int64_t g, int sub,
 // Dense rebuild, by one CTA, of the k generations above the 2^k contiguous nodes that
 // descend from node `a` (k <= TOP_LEVELS).  smem: 2 * 2^k doubles per tree, addressed as a
 // relative heap (generation j, position t at s[(1<<j) + t]).
-__device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+__device__ __forceinline__ void dense_load(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
     const int n = 1 << k;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         if (t.sum) s_sum[n + i] = ldcg_f64(t.sum + (a << k) + i);
         if (t.mnn) s_min[n + i] = ldcg_f64(t.mnn + (a << k) + i);
     }
-    __syncthreads();
+}
+// Expects the bottom row in s_sum / s_min [n, 2n) and a CTA barrier behind the stores that filled it.
+__device__ __forceinline__ void dense_build_write(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+    const int n = 1 << k;
     // all generations in shared memory first (CTA barriers down to 32 nodes, then one warp) ...
 #pragma unroll 1
     for (int j = k - 1; j >= 5; --j) {
@@ -214,6 +218,46 @@ __device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, in
         if (t.mnn) t.mnn[node] = s_min[p];
     }
 }
+__device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+    dense_load(t, a, k, s_sum, s_min);
+    __syncthreads();
+    dense_build_write(t, a, k, s_sum, s_min);
+}
+
+// ---------------------------------------------------------------------------------------
+// Sorted fast path of the one-launch form.  When the indices are the stratified sample just drawn
+// they ascend, each CTA of the cluster owns a contiguous run of leaves, and an ancestor can only be
+// shared between CTAs along the <= 7 borders between their runs.  So
+//   stage 1  every CTA lifts its own items through all generations below the dense top WITHOUT
+//            meeting the others: one thread per surviving item climbs level by level; the sibling at
+//            each level is either clean (prefetched from global memory for all levels in ONE round
+//            trip) or the neighbouring run of the same CTA (its value comes through shared memory,
+//            a named barrier per level).  Nodes that have a leaf of another CTA below them are left out;
+//   one cluster barrier;
+//   stage 2  one warp of CTA 0 recomputes the left-out nodes, a chain per border from the level where
+//            the two border leaves meet, children prefetched in one round trip beside the loads of
+//            the dense top, whose bottom row is then patched in shared memory.
+// Three level-synchronous phases with five cluster barriers become one barrier and two round trips.
+// Every node is still op(left child, right child) of final children: same bits (memory.py:82-87).
+// ---------------------------------------------------------------------------------------
+constexpr int SORT_SLICE_MAX = 128;  // items per CTA
+constexpr int SORT_CLIMB_MAX = 16;   // generations between the leaves and the dense top
+struct SortSmem {
+    double sib[SORT_CLIMB_MAX][SORT_SLICE_MAX][2];  // sibling (sum, min) of the level-l node above slice item t (by slice position)
+    double v[SORT_SLICE_MAX][2];                    // published value of the node holding survivor i (read where two runs meet)
+    double leaf[SORT_SLICE_MAX];
+    int k[SORT_SLICE_MAX];                          // surviving leaves of this CTA, ascending
+    short fl[SORT_SLICE_MAX][2];                    // published first / last survivor of the run below that node
+    short orig[SORT_SLICE_MAX];                     // slice position of survivor i
+    int warp_cnt[4];
+};
+enum { SRT_KEY_MIN = 0, SRT_KEY_MAX, SRT_NB_LEFT, SRT_NB_RIGHT, SRT_MERGE_MASK, SRT_CHAINS, SRT_WORDS = 8 };
+static_assert(sizeof(SortSmem) <= UPD_STAGE_FLOATS * sizeof(float), "SortSmem must fit the staging buffer");
+constexpr int S2_OFF_DOUBLES = 4 * TOP_NODES;  // stage-2 child staging sits behind the two dense-top buffers
+static_assert((S2_OFF_DOUBLES + UPD_MAX_CTAS * SORT_CLIMB_MAX * 6) * sizeof(double) <= UPD_STAGE_FLOATS * sizeof(float), "stage-2 staging");
+
+// level (generations above the leaves) of the lowest common ancestor of two leaves; equal leaves count as 1
+__device__ __forceinline__ int lca_level(int64_t x, int64_t y) { return x == y ? 1 : 64 - __clzll((long long)(x ^ y)); }
 
 // ---------------------------------------------------------------------------------------
 // One-launch form (n <= UPD_CLUSTER_MAX_ITEMS): a cluster of 1..8 CTAs.
@@ -233,6 +277,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     double *s_tree = reinterpret_cast<double *>(s_raw);
     __shared__ double s_red[34];
     __shared__ float s_clu[2 * UPD_MAX_CTAS];               // CTA 0's copy collects per-CTA max / loss partials
+    __shared__ int s_srt[SRT_WORDS];                        // sorted path: slice key range, neighbouring leaves, levels at which runs meet
+    __shared__ long long s_bound[4 * UPD_MAX_CTAS];         // sorted path, CTA 0's copy: {smallest, largest leaf} per CTA; then {border leaf, level} per border
     double *s_sum = s_tree, *s_min = s_tree + 2 * TOP_NODES;
 
     cg::cluster_group cl = cg::this_cluster();
@@ -240,6 +286,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     const int rank = (int)cl.block_rank();
     const int T = blockDim.x, tid = threadIdx.x;
     const int nwarp = (T + 31) >> 5;
+    if (tid == 0) {
+        s_srt[SRT_KEY_MIN] = INT_MAX;
+        s_srt[SRT_KEY_MAX] = -1;
+        s_srt[SRT_NB_LEFT] = s_srt[SRT_NB_RIGHT] = -1;
+        s_srt[SRT_MERGE_MASK] = 0;
+    }
 #define UPD_TRACE(slot)                                                      \
     do {                                                                     \
         if (a.trace && rank == 0 && tid == 0) {                              \
@@ -248,12 +300,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             a.trace[slot] = t__;                                             \
         }                                                                    \
     } while (0)
-    // Wait first, release second: the sampling kernel behind this one starts its record exchange before its own
-    // wait (tree_kernels.cuh) and relies on every kernel up to the previous sample having retired by then.
+    // With early publish: wait first, release second.  The sampling kernel behind this one then starts its record
+    // exchange before its own wait (tree_kernels.cuh) and relies on every kernel up to the previous sample having
+    // retired by then.  Otherwise the dependents are released at once.
     const bool tl_on = a.tl && rank == 0 && tid == 0;
     if (tl_on) tl_stamp(a.tl, a.tl_cap, 7);
+    if (!a.publish_to) pdl_launch_dependents();  // (early publish: only behind the wait, see above)
     pdl_wait();  // indices / Q tables / the tree itself come from the kernels in front of this one
-    pdl_launch_dependents();
+    if (a.publish_to) pdl_launch_dependents();
     if (tl_on) tl_stamp(a.tl, a.tl_cap, 8);
     UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
@@ -263,6 +317,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     const int lo = first + (rank * per < n ? rank * per : n);
     const int hi = lo + per < last ? lo + per : last;
     const int cnt = hi - lo;
+    const int climb = a.t.L > TOP_LEVELS ? a.t.L - TOP_LEVELS : 0;
+    // uniform over the cluster: `per`, the tree and the flags are the same in every CTA
+    const bool sorted_path = a.sorted_idx && a.sorted_fast && per <= SORT_SLICE_MAX && climb <= SORT_CLIMB_MAX && a.t.sum && a.t.mnn;
+    const int top = sorted_path ? (a.t.L < TOP_LEVELS ? a.t.L : TOP_LEVELS) : top_depth(a.t.L);
+    // sorted path: the index of slice item tid % 128 is requested now, so that the sibling loads behind the TD phase
+    // can go out at once
+    const int64_t early_ki = (sorted_path && (tid & (SORT_SLICE_MAX - 1)) < cnt) ? upd_index(a, lo + (tid & (SORT_SLICE_MAX - 1))) : IDX_SKIP;
 
     if (fused_td) {  // rows of the WHOLE batch (the max is batch-wide), partitioned over the CTAs
         float *f_red = reinterpret_cast<float *>(s_red);
@@ -361,9 +422,170 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     if (tl_on) tl_stamp(a.tl, a.tl_cap, 12);  // TD arithmetic done
 
     UPD_TRACE(1);
+    double my_max = 0.0;
+    if (sorted_path) {
+        SortSmem &S = *reinterpret_cast<SortSmem *>(s_raw);
+        const int lane = tid & 31, warp = tid >> 5;
+        if (!fused_td) __syncthreads();  // s_srt was initialised at kernel entry; the TD phase ends with a barrier of its own
+        // ---- siblings first: they depend on nothing but the indices, so their round trip runs beside the pow() below.
+        // Thread t takes slice item t % 128 at levels t / 128 + 1 and + 9 (everything is loaded; shared or joined
+        // levels are simply not used).
+        {
+            const int it = tid & (SORT_SLICE_MAX - 1), lg = tid / SORT_SLICE_MAX;
+            if (it < cnt) {
+                const int64_t ki = early_ki;
+                if (ki != IDX_SKIP && ki >= 0 && ki < a.len_limit) {
+#pragma unroll
+                    for (int r = 0; r < 2; ++r) {
+                        const int l = lg + 1 + r * (UPD_THREADS / SORT_SLICE_MAX);
+                        if (l <= climb) {
+                            const int64_t sibn = ((a.t.cap + ki) >> (l - 1)) ^ 1;
+                            S.sib[l - 1][it][0] = ldcg_f64(a.t.sum + sibn);
+                            S.sib[l - 1][it][1] = ldcg_f64(a.t.mnn + sibn);
+                        }
+                    }
+                }
+            }
+        }
+        // ---- leaves: one thread per item of the slice (cnt <= 128) ----
+        int kk = -1, kraw = -1;
+        double leaf = 0.0;
+        if (tid < cnt) {
+            const int64_t ki = early_ki;
+            if (ki != IDX_SKIP && ki >= 0 && ki < a.len_limit) kraw = (int)ki;
+            int64_t k;
+            double raw;
+            if (upd_item(a, lo + tid, k, leaf, raw)) {
+                kk = (int)k;
+                my_max = raw;
+                if (lo + tid + 1 < (int)a.n && a.idx[lo + tid + 1] == a.idx[lo + tid]) kk = -1;  // the next item overwrites this one
+            }
+        } else if (tid == SORT_SLICE_MAX) {  // nearest index-valid leaf in front of the slice ...
+            for (int j = lo - 1; j >= first; --j) {
+                const int64_t ki = upd_index(a, j);
+                if (ki != IDX_SKIP && ki >= 0 && ki < a.len_limit) {
+                    s_srt[SRT_NB_LEFT] = (int)ki;
+                    break;
+                }
+            }
+        } else if (tid == SORT_SLICE_MAX + 32) {  // ... and behind it
+            for (int j = hi; j < last; ++j) {
+                const int64_t ki = upd_index(a, j);
+                if (ki != IDX_SKIP && ki >= 0 && ki < a.len_limit) {
+                    s_srt[SRT_NB_RIGHT] = (int)ki;
+                    break;
+                }
+            }
+        }
+        unsigned alive = 0;
+        if (tid < SORT_SLICE_MAX) {
+            // keys ascend: the smallest / largest index-valid leaf of the slice, one shared-memory atomic per warp
+            const int wmin = __reduce_min_sync(0xffffffffu, kraw >= 0 ? kraw : INT_MAX), wmax = __reduce_max_sync(0xffffffffu, kraw);
+            alive = __ballot_sync(0xffffffffu, kk >= 0);
+            if (lane == 0) {
+                S.warp_cnt[warp] = __popc(alive);
+                if (wmax >= 0) {
+                    atomicMin(&s_srt[SRT_KEY_MIN], wmin);
+                    atomicMax(&s_srt[SRT_KEY_MAX], wmax);
+                }
+            }
+            if (a.max_prio) {
+                if (a.src_kind == LEAF_GIVEN) my_max = (tid == 0 && rank == 0) ? a.batch_max : 0.0;
+                for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, lane ^ o));
+                if (lane == 0) s_red[warp] = my_max;
+            }
+        }
+        __syncthreads();
+        int m = 0;  // survivors of this CTA
+        for (int w = 0; w < SORT_SLICE_MAX / 32; ++w) m += S.warp_cnt[w];
+        if (tid < SORT_SLICE_MAX && kk >= 0) {  // compact: surviving leaves, still ascending
+            int pos = __popc(alive & ((1u << lane) - 1u));
+            for (int w = 0; w < warp; ++w) pos += S.warp_cnt[w];
+            S.k[pos] = kk;
+            S.leaf[pos] = leaf;
+            S.orig[pos] = (short)tid;
+            S.v[pos][0] = S.v[pos][1] = leaf;
+            S.fl[pos][0] = S.fl[pos][1] = (short)pos;
+            a.t.sum[a.t.cap + kk] = leaf;
+            a.t.mnn[a.t.cap + kk] = leaf;
+        }
+        if (tid == 0) {  // CTA 0 learns every CTA's key range for the borders of stage 2
+            long long *home = cl.map_shared_rank(s_bound, 0);
+            home[2 * rank] = s_srt[SRT_KEY_MAX] >= 0 ? (long long)s_srt[SRT_KEY_MIN] : -1;
+            home[2 * rank + 1] = (long long)s_srt[SRT_KEY_MAX];
+            if (a.max_prio) {
+                double mx = 0.0;
+                for (int w = 0; w < SORT_SLICE_MAX / 32; ++w) mx = fmax(mx, s_red[w]);
+                if (mx > 0.0) atomic_max_pos_f64(a.max_prio, mx);
+            }
+        }
+        UPD_TRACE(2);
+        __syncthreads();
+        // ---- stage 1 ----
+        if (tid < SORT_SLICE_MAX) {
+            // One thread per survivor keeps, in registers, the value of the node that holds its item and the first /
+            // last survivor of the run of items below that node.  Two runs meet at the level of the lowest common
+            // ancestor of the adjacent leaves between them (mL / mR): only there does a thread need a neighbour's
+            // value, which that neighbour published one level earlier; the four warps meet at a named barrier only
+            // at the levels where some pair of runs of this CTA meets (rare below the dense top for a spread-out sample).
+            const int64_t nbl = s_srt[SRT_NB_LEFT], nbr = s_srt[SRT_NB_RIGHT];
+            const int i = tid;
+            const bool have = i < m;
+            const int ck = have ? (int)a.t.cap + S.k[i] : 0;  // my leaf's node number (cap <= 2^26 on this path)
+            const int org = have ? S.orig[i] : 0;
+            int stop = climb + 1;  // first level whose node another CTA shares
+            if (have && nbl >= 0) stop = min(stop, lca_level(S.k[i], nbl));
+            if (have && nbr >= 0) stop = min(stop, lca_level(S.k[i], nbr));
+            double vs = have ? S.leaf[i] : 0.0, vm = vs;
+            int F = i, Lr = i;
+            int mR = (have && i + 1 < m) ? lca_level(S.k[i], S.k[i + 1]) : 99;  // level where the run behind mine joins
+            int mL = (have && i > 0) ? lca_level(S.k[i - 1], S.k[i]) : 99;      // ... and the run in front of mine
+            unsigned meet = 0;
+            if (mR < stop) meet |= 1u << mR;
+            if (mL < stop) meet |= 1u << mL;
+            meet = __reduce_or_sync(0xffffffffu, meet);
+            if (lane == 0 && meet) atomicOr(reinterpret_cast<unsigned *>(&s_srt[SRT_MERGE_MASK]), meet);
+            asm volatile("bar.sync 1, %0;" ::"n"(SORT_SLICE_MAX) : "memory");
+            meet = (unsigned)s_srt[SRT_MERGE_MASK];
+#pragma unroll 1
+            for (int l = 1; l <= climb; ++l) {
+                const bool act = have && l < stop;
+                const bool sync_here = (meet >> l) & 1u;
+                if (sync_here) asm volatile("bar.sync 1, %0;" ::"n"(SORT_SLICE_MAX) : "memory");  // level l-1 values are published
+                const int c = ck >> (l - 1);
+                if (act) {
+                    double2 o = *reinterpret_cast<const double2 *>(S.sib[l - 1][org]);  // clean sibling unless a run joins
+                    if (mR == l) {  // my node is the left child, the run behind mine fills the right one
+                        const int j = Lr + 1;
+                        o = *reinterpret_cast<const double2 *>(S.v[j]);
+                        Lr = S.fl[j][1];
+                        mR = Lr + 1 < m ? lca_level(S.k[Lr], S.k[Lr + 1]) : 99;
+                    } else if (mL == l) {
+                        const int j = F - 1;
+                        o = *reinterpret_cast<const double2 *>(S.v[j]);
+                        F = S.fl[j][0];
+                        mL = F > 0 ? lca_level(S.k[F - 1], S.k[F]) : 99;
+                    }
+                    vs = (c & 1) ? __dadd_rn(o.x, vs) : __dadd_rn(vs, o.x);  // left operand = left child
+                    vm = fmin(vm, o.y);
+                    if (i == F) {  // one writer per node
+                        a.t.sum[c >> 1] = vs;
+                        a.t.mnn[c >> 1] = vm;
+                    }
+                }
+                if (sync_here) asm volatile("bar.sync 1, %0;" ::"n"(SORT_SLICE_MAX) : "memory");  // everybody has read level l-1
+                if (act && (mR == l + 1 || mL == l + 1)) {  // somebody reads me one level up
+                    *reinterpret_cast<double2 *>(S.v[i]) = make_double2(vs, vm);
+                    *reinterpret_cast<short2 *>(S.fl[i]) = make_short2((short)F, (short)Lr);
+                }
+            }
+        }
+        cl.sync();  // every CTA's leaves and unshared ancestors are in global memory
+        UPD_TRACE(3);
+        UPD_TRACE(4);
+    } else {
     // phase 1
     double *s_leaf = s_sum;
-    double my_max = 0.0;
 #pragma unroll 1
     for (int i = tid; i < cnt; i += T) {
         int64_t k;
@@ -414,7 +636,6 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     cl.sync();
     UPD_TRACE(3);
     // phase 3
-    const int top = top_depth(a.t.L);
     const int sub = tid & (LIFT_LANES - 1);
 #pragma unroll 1
     for (int done = 0; a.t.L - done > top; done += LIFT) {
@@ -427,18 +648,133 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         cl.sync();
     }
     UPD_TRACE(4);
+    }
     // phase 4
     if (rank == 0) {
         // The shard record (roots + prefix chain) needs nothing from global memory that the dense rebuild writes:
         // the chain's terms above the dense top are taken from shared memory afterwards, the ones below it are
-        // final since the last cluster barrier and are requested now, so their round trip hides behind the rebuild.
+        // final since the last cluster barrier (sorted path: unless stage 2 recomputes them, see there) and are
+        // requested now, so their round trip hides behind the rebuild.
         const bool want_rec = a.rec_out || a.publish_to;
         const bool want_partial = want_rec && a.rec_need > 0 && a.rec_need < a.t.cap;
         const bool emit = want_partial && tid < 32 && ((a.rec_need >> tid) & 1);
         const int64_t term_node = prefix_term_node(a.t.cap, a.rec_need, tid & 31);
         const bool term_low = a.t.L - (tid & 31) > top;  // the node lies below the dense top
         double term = (emit && term_low) ? __ldcg(a.t.sum + term_node) : 0.0;
-        dense_lift_block(a.t, 1, top, s_sum, s_min);
+        if (!sorted_path) {
+            dense_lift_block(a.t, 1, top, s_sum, s_min);
+        } else {
+            // ---- stage 2: the nodes shared between CTAs, one chain per border, next to the dense top ----
+            double *s2 = s_tree + S2_OFF_DOUBLES;  // [border][level - 1][sum L, sum R, min L, min R]
+            double *s_chain_v = s2 + UPD_MAX_CTAS * SORT_CLIMB_MAX * 4;                      // [level - 1][border] fresh sums
+            int *s_chain_n = reinterpret_cast<int *>(s_chain_v + SORT_CLIMB_MAX * UPD_MAX_CTAS);  // ... and their nodes
+            int ckR = -1;  // warp 0, lane p: node number of the first leaf behind border p (borders in ascending order)
+            int sh = 0;    // level of the lowest node the border's two leaves share
+            int nbord = 0, l_first = climb + 1;
+            if (tid < 32) {
+                const int my_min = tid < ncta ? (int)s_bound[2 * tid] : -1, my_max_k = tid < ncta ? (int)s_bound[2 * tid + 1] : -1;
+                int kL = __shfl_up_sync(0xffffffffu, my_max_k, 1);  // keys ascend with the CTA rank: the largest leaf in front
+                if (tid == 0) kL = -1;                              // of mine is the maximum over the lanes below me
+                for (int o = 1; o < UPD_MAX_CTAS; o <<= 1) {
+                    const int other = __shfl_up_sync(0xffffffffu, kL, o);
+                    if (tid >= o) kL = max(kL, other);
+                }
+                const bool border = my_min >= 0 && kL >= 0;
+                const int my_sh = border ? lca_level(kL, my_min) : 0;
+                const int my_ck = border ? (int)a.t.cap + my_min : -1;
+                const unsigned mask = __ballot_sync(0xffffffffu, border);
+                nbord = __popc(mask);
+                const unsigned src = __fns(mask, 0, tid + 1);  // lane of the (tid+1)-th border
+                const int g_ck = __shfl_sync(0xffffffffu, my_ck, src & 31), g_sh = __shfl_sync(0xffffffffu, my_sh, src & 31);
+                if (tid < nbord) {
+                    ckR = g_ck;
+                    sh = g_sh;
+                }
+                l_first = __reduce_min_sync(0xffffffffu, tid < nbord ? sh : climb + 1);
+                if (tid < UPD_MAX_CTAS) {
+                    s_bound[2 * UPD_MAX_CTAS + 2 * tid] = ckR;
+                    s_bound[2 * UPD_MAX_CTAS + 2 * tid + 1] = sh;
+                }
+                if (tid == 0) s_srt[SRT_CHAINS] = l_first <= climb;
+            }
+            dense_load(a.t, 1, top, s_sum, s_min);
+            __syncthreads();
+            const bool chains = s_srt[SRT_CHAINS] != 0;  // some node below the dense top is shared between CTAs (a sample that crowds)
+            if (chains) {
+                if (tid < UPD_MAX_CTAS * SORT_CLIMB_MAX) {  // children of every chain node: one round trip
+                    const int b = tid / SORT_CLIMB_MAX, l = tid % SORT_CLIMB_MAX + 1;
+                    const int bck = (int)s_bound[2 * UPD_MAX_CTAS + 2 * b];
+                    const int bsh = (int)s_bound[2 * UPD_MAX_CTAS + 2 * b + 1];
+                    if (bck >= 0 && l >= bsh && l <= climb) {
+                        const int64_t X = bck >> l;
+                        const double2 cs = ldcg_f64x2(a.t.sum + 2 * X), cm = ldcg_f64x2(a.t.mnn + 2 * X);
+                        double *d = s2 + (b * SORT_CLIMB_MAX + (l - 1)) * 4;
+                        d[0] = cs.x;
+                        d[1] = cs.y;
+                        d[2] = cm.x;
+                        d[3] = cm.y;
+                    }
+                }
+                __syncthreads();
+            }
+            if (chains && tid < 32) {
+                // Chains that have reached the same node form a run of adjacent lanes (borders ascend).  Inside a run the
+                // lanes whose border lies in the left child come first, then at most one lane whose border is the split
+                // itself, then the lanes of the right child: if a child is shared at all, the run's first lane holds the
+                // left child's fresh value and its last lane the right child's.
+                int pn = -1;  // my chain's node one level down and its fresh value
+                double pvs = 0.0, pvm = 0.0;
+                for (int t = tid; t < (l_first - 1) * UPD_MAX_CTAS; t += 32) s_chain_n[t] = -1;  // levels no chain reaches
+#pragma unroll 1
+                for (int l = l_first; l <= climb; ++l) {
+                    const bool on = tid < nbord && l >= sh;
+                    const int X = on ? (ckR >> l) : -1;
+                    double ls = 0.0, rs = 0.0, lm = 0.0, rm = 0.0;
+                    if (on) {
+                        const double *d = s2 + (tid * SORT_CLIMB_MAX + (l - 1)) * 4;
+                        ls = d[0];
+                        rs = d[1];
+                        lm = d[2];
+                        rm = d[3];
+                    }
+                    const int Xn = __shfl_down_sync(0xffffffffu, X, 1);
+                    const unsigned ends = __ballot_sync(0xffffffffu, !(on && tid < 31 && Xn == X));  // bit p: a run ends at lane p
+                    const int g1 = tid + __ffs(ends >> tid) - 1;                                     // (bit 31 is always set)
+                    const unsigned before = tid ? (ends & ((1u << tid) - 1u)) : 0u;
+                    const int g0 = before ? 32 - __clz(before) : 0;
+                    const int n0 = __shfl_sync(0xffffffffu, pn, g0), n1 = __shfl_sync(0xffffffffu, pn, g1);
+                    const double s0 = shfl_f64(pvs, g0), m0 = shfl_f64(pvm, g0);
+                    const double s1 = shfl_f64(pvs, g1), m1 = shfl_f64(pvm, g1);
+                    if (on) {
+                        if (n0 == 2 * X) { ls = s0; lm = m0; }
+                        if (n1 == 2 * X + 1) { rs = s1; rm = m1; }
+                    }
+                    const double nvs = __dadd_rn(ls, rs), nvm = fmin(lm, rm);
+                    if (on) {
+                        a.t.sum[X] = nvs;
+                        a.t.mnn[X] = nvm;
+                        if (l == climb) {  // bottom row of the dense top: heap slot == node number
+                            s_sum[X] = nvs;
+                            s_min[X] = nvm;
+                        }
+                    }
+                    if (tid < UPD_MAX_CTAS) {
+                        s_chain_n[(l - 1) * UPD_MAX_CTAS + tid] = X;
+                        s_chain_v[(l - 1) * UPD_MAX_CTAS + tid] = nvs;
+                    }
+                    pn = X;
+                    pvs = nvs;
+                    pvm = nvm;
+                }
+                __syncwarp();
+                if (emit && term_low && tid >= 1 && tid <= climb) {  // a term of the record's chain that stage 2 has just recomputed
+                    for (int c2 = 0; c2 < UPD_MAX_CTAS; ++c2)
+                        if (s_chain_n[(tid - 1) * UPD_MAX_CTAS + c2] == (int)term_node) term = s_chain_v[(tid - 1) * UPD_MAX_CTAS + c2];
+                }
+            }
+            if (chains) __syncthreads();
+            dense_build_write(a.t, 1, top, s_sum, s_min);
+        }
         UPD_TRACE(5);
         if (want_rec && tid < 32) {
             if (emit && !term_low) term = s_sum[term_node];

@@ -261,6 +261,8 @@ def main():
         shard.set_global_len(world * ring, 0)
     if args.timeline:
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"timeline", 8192))
+    if os.environ.get("PER_SORTED_UPDATE") is not None:
+        pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"sorted_update", int(os.environ["PER_SORTED_UPDATE"])))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"pdl", int(os.environ["PER_PDL"])))
     use_mailbox = shard is not None and not args.nccl_exchange

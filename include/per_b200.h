@@ -329,9 +329,12 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies
  * through shared memory, 1 register-staged LDG/STG), "gather_warps", "gather_stages",
  * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm"; "update_trace" (0/1, see
- * per_update_trace); "pdl" (default 1: the sample, gather and update kernels are launched with
- * programmatic stream serialization and begin with griddepcontrol.wait, so each one's launch
- * and prologue overlap the tail of the kernel in front of it; 0 = plain launches);
+ * per_update_trace); "pdl" (bit mask, default 3: 1 = sampling kernels, 2 = gather, 4 = the one-launch
+ * update are launched with programmatic stream serialization and begin with
+ * griddepcontrol.wait, so their launch and prologue overlap the tail of the kernel in front;
+ * measured on B200 the cluster launch of the update loses from it, profiles/r01_notes.md);
+ * "sorted_update" (default 1: an update of exactly the index buffer the last sample wrote takes
+ * the sorted fast path of update_kernels.cuh; 0 = always the level-synchronous rounds);
  * "early_publish" (default 0; needs per_shard_attach_exchange): every priority update ends by
  * storing the refreshed shard record, tagged with the next exchange epoch, into all ranks'
  * mailboxes, so the record is on its way over NVLink while the update kernel retires and the next
