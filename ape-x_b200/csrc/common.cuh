@@ -78,14 +78,16 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 }
 
 // ---- device helpers -------------------------------------------------------------------
-// Timeline (diagnostics, per_tune "timeline"): tl[0] counts entries, entry i = (tag << 56) | globaltimer ns.
-// Stamped by thread 0 of CTA 0 of the sample / gather / update kernels; null = off.
-__device__ __forceinline__ void tl_stamp(unsigned long long *tl, unsigned cap, unsigned tag) {
+// Timeline (diagnostics, per_tune "timeline"): every sample / gather / update launch owns TL_SLOTS consecutive
+// entries of the list (its launch sequence number is a kernel argument, so launches captured in a CUDA graph
+// keep their entries across replays); thread 0 of CTA 0 stores (tag << 56) | globaltimer ns with plain stores —
+// no atomics, nothing on the kernel's critical path waits for the stamp.  tl == null: off.
+constexpr int TL_SLOTS = 6;
+__device__ __forceinline__ void tl_stamp(unsigned long long *tl, unsigned slot, unsigned tag) {
     if (!tl) return;
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    const unsigned slot = atomicAdd(reinterpret_cast<unsigned *>(tl), 1u);
-    if (slot < cap) tl[1 + slot] = ((unsigned long long)tag << 56) | (t & ((1ull << 56) - 1));
+    tl[slot] = ((unsigned long long)tag << 56) | (t & ((1ull << 56) - 1));
 }
 
 // Programmatic dependent launch: let the next kernel of the stream become resident / wait until the

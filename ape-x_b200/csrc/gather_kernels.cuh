@@ -51,8 +51,7 @@ struct GatherArgs {
     int64_t idx_base;  // sharded replay: global index of this shard's row 0
     int skip_foreign;  // sharded replay: idx == -1 = another shard's row, skipped silently
     const u64 *range;  // sharded replay: owned strata of the last sample (see owned_range); null = all queries
-    u64 *tl;           // timeline (diagnostics), see tl_stamp
-    unsigned tl_cap;
+    u64 *tl;           // timeline (diagnostics), see tl_stamp: this launch's first entry
     uint8_t *cast_out[2];  // k_gather_cast: widened obs / next_obs batches (rc[0..1].dst then only define offsets)
 };
 
@@ -166,10 +165,10 @@ __device__ __forceinline__ void gather_scalars(const GatherArgs &a, int64_t firs
 __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs a, int per_query) {
     extern __shared__ __align__(128) uint8_t g_smem[];
     const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 4);
+    if (tl_on) tl_stamp(a.tl, 0, 4);
     pdl_launch_dependents();
     pdl_wait();  // indices and range tags come from the sampling kernel in front of this one
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 5);
+    if (tl_on) tl_stamp(a.tl, 1, 5);
     int64_t first_q, last_q;
     gather_range(a, first_q, last_q);
     gather_scalars(a, first_q, last_q);
@@ -213,7 +212,7 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
         if (++s == NS) { s = 0; parity ^= 1u; }
     }
     bulk_wait_read<0>();
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 6);
+    if (tl_on) tl_stamp(a.tl, 2, 6);
 }
 
 // Register-staged variant: one warp per piece, up to 16 x 16-B loads in flight per lane,

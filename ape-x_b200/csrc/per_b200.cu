@@ -3,6 +3,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <vector>
+
 #include "common.cuh"
 #include "gather_kernels.cuh"
 #include "aql_kernels.cuh"
@@ -48,7 +50,15 @@ struct per_buffer_s {
     GatherTune tune;
     int sharded;               // created by per_create_shard: samples leave the owned-strata range on the device
     u64 *timeline;             // per_tune("timeline", entries): kernel time stamps, read by per_timeline
-    unsigned timeline_cap;
+    unsigned timeline_cap;     //   entries; launch number timeline_seq owns entries [seq * TL_SLOTS, +TL_SLOTS)
+    unsigned timeline_seq;
+    u64 *tl_next() {           //   first entry of the launch being issued, or null
+        if (!timeline) return nullptr;
+        const unsigned launches = timeline_cap / TL_SLOTS;
+        u64 *p = timeline + (size_t)(timeline_seq % launches) * TL_SLOTS;
+        ++timeline_seq;
+        return p;
+    }
     int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
     bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", bits): programmatic dependent launch for 1 sampling, 2 gather, 4 update kernels
@@ -478,8 +488,7 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.out_w64 = d_out_w64;
     a.out_w32 = d_out_w32;
     a.status = b->status();
-    a.tl = b->timeline;
-    a.tl_cap = b->timeline_cap;
+    a.tl = b->tl_next();
     PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
     PER_CUDA(cudaGetLastError());
     b->last_sample_idx = d_out_idx;
@@ -566,16 +575,14 @@ int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_
     if (!b->timeline) return PER_OK;
     DeviceGuard g(b->device);
     cudaStream_t s = (cudaStream_t)stream;
-    u64 n = 0;
-    PER_CUDA(cudaMemcpyAsync(&n, b->timeline, sizeof(u64), cudaMemcpyDeviceToHost, s));
+    std::vector<u64> host(b->timeline_cap);
+    PER_CUDA(cudaMemcpyAsync(host.data(), b->timeline, sizeof(u64) * b->timeline_cap, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaMemsetAsync(b->timeline, 0, sizeof(u64) * b->timeline_cap, s));
     PER_CUDA(cudaStreamSynchronize(s));
-    n &= 0xffffffffull;
-    if (n > b->timeline_cap) n = b->timeline_cap;
-    if ((int64_t)n > max_entries) n = (u64)max_entries;
-    if (n) PER_CUDA(cudaMemcpyAsync(h_out, b->timeline + 1, sizeof(u64) * n, cudaMemcpyDeviceToHost, s));
-    PER_CUDA(cudaMemsetAsync(b->timeline, 0, sizeof(u64), s));
-    PER_CUDA(cudaStreamSynchronize(s));
-    *h_count = (int64_t)n;
+    int64_t n = 0;
+    for (u64 e : host)
+        if (e && n < max_entries) h_out[n++] = (int64_t)e;
+    *h_count = n;
     return PER_OK;
 }
 
@@ -623,8 +630,7 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     a.d_epoch = b->xchg_epoch();
     a.d_done = b->xchg_done();
     a.d_range = b->scal + 5;
-    a.tl = b->timeline;
-    a.tl_cap = b->timeline_cap;
+    a.tl = b->tl_next();
     if (!d_records) {  // records travel through the peer-memory mailboxes
         a.use_mailbox = 1;
         a.d_wait_stats = b->scal + 8;
@@ -701,8 +707,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
     a.piece = slow.piece = tn.piece;
     a.stages = slow.stages = tn.stages;
-    a.tl = b->timeline;
-    a.tl_cap = b->timeline_cap;
+    a.tl = b->tl_next();
     const int64_t items = batch * per_query;
     if (tn.mode == 0) {
         int64_t grid = (items + tn.warps - 1) / tn.warps;
@@ -778,9 +783,10 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         cudaFree(b->timeline);
         b->timeline = nullptr;
         b->timeline_cap = 0;
-        if (value > 0) {
-            PER_CUDA(cudaMalloc(&b->timeline, sizeof(u64) * (size_t)(value + 1)));
-            PER_CUDA(cudaMemset(b->timeline, 0, sizeof(u64) * (size_t)(value + 1)));
+        b->timeline_seq = 0;
+        if (value >= TL_SLOTS) {
+            PER_CUDA(cudaMalloc(&b->timeline, sizeof(u64) * (size_t)value));
+            PER_CUDA(cudaMemset(b->timeline, 0, sizeof(u64) * (size_t)value));
             b->timeline_cap = (unsigned)value;
         }
         return PER_OK;
@@ -845,8 +851,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
         b->rec_published = true;
     }
     a.trace = b->update_trace ? b->scal + 11 : nullptr;
-    a.tl = b->timeline;
-    a.tl_cap = b->timeline_cap;
+    a.tl = b->tl_next();
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     a.sorted_fast = b->sorted_update;

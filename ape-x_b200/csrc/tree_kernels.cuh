@@ -106,11 +106,12 @@ __global__ void k_range_reduce(const double *v, int64_t cap, int64_t lo, int64_t
 // K2 + K3: stratified prefix-sum descent, one warp per query, and importance weights.
 //
 // Descent (memory.py:122-129) reads only LEFT children.  Below node i, the left children
-// of the next 5 generations number 1+2+4+8+16 = 31, so lanes 0..30 fetch them in one
-// round trip (generation j, pair q -> node i*2^j + 2q, lane 2^(j-1)-1+q) and the five
-// compare / subtract steps then run out of registers through shuffles: ceil(L/5)
-// dependent memory round trips per query instead of L.  The subtraction sequence is the
-// reference's, so the index is bit-exact.
+// of the next 7 generations number 1+2+...+64 = 127 (generation j, pair q -> node i*2^j + 2q):
+// the warp fetches them with four independent loads per lane in one round trip and the seven
+// compare / subtract steps then run out of registers through shuffles: ceil(L/7) dependent
+// memory round trips per query instead of L (three for a 2^20-leaf tree, the first of them
+// issued before the query's mass is known).  The subtraction sequence is the reference's, so
+// the index is bit-exact.
 // ---------------------------------------------------------------------------------------
 struct SampleArgs {
     const double *sum;
@@ -143,8 +144,7 @@ struct SampleArgs {
     int use_mailbox;             // 1: exchange through the mailboxes; 0: records come in `recs`
     u64 *d_wait_stats;           // {waits, total ns, max ns} spent by CTA 0 between kernel start and the last record's arrival
     int64_t rec_need, rec_len;   // this shard's part of the global prefix, local len
-    u64 *tl;                     // timeline (diagnostics), see tl_stamp
-    unsigned tl_cap;
+    u64 *tl;                     // timeline (diagnostics), see tl_stamp: this launch's first entry
     int skip_publish;            // 1: this epoch's record is in the mailboxes already (published by the update kernel)
 };
 
@@ -236,52 +236,104 @@ __global__ void k_shard_record(const double *sum, const double *mnn, int64_t cap
     write_shard_record(sum, mnn, cap, need_local, len_local, out);
 }
 
-// Left children of the first five generations below the root, lane layout of the descent
-// (generation j, pair qg -> lane 2^(j-1)-1+qg).  The same for every query, so callers load it
-// before they know the query's mass.
-__device__ __forceinline__ double root_block(const SampleArgs &a, const int lane) {
-    const int j = 32 - __clz(lane + 1);
+// One block of the descent: the LEFT children of the next (up to) seven generations below `node`,
+// 1+2+4+8+16+32+64 = 127 of them, fetched by the warp in one round trip.  Register r0 of lane p holds
+// generations 1..5 in the order (generation j, pair q) -> p = 2^(j-1)-1+q (31 values); r1 holds generation 6
+// (pair q at lane q); r2 / r3 hold generation 7 (pair q at lane q & 31 of register 2 + (q >> 5)).
+struct DescentBlock {
+    double r0, r1, r2, r3;
+};
+constexpr int DESCENT_GENS = 7;
+
+__device__ __forceinline__ DescentBlock load_block(const double *v, const int64_t node, const int s, const int lane) {
+    const int j = 32 - __clz(lane + 1);  // lane -> generation 1..5 (lane 31 unused)
     const int qg = lane + 1 - (1 << (j - 1));
-    const int s = a.L < 5 ? a.L : 5;
-    return (j <= s && lane < 31) ? a.sum[(int64_t(1) << j) + 2 * qg] : 0.0;
+    DescentBlock b;
+    b.r0 = (j <= s && lane < 31) ? v[(node << j) + 2 * qg] : 0.0;
+    b.r1 = s >= 6 ? v[(node << 6) + 2 * lane] : 0.0;
+    b.r2 = s >= 7 ? v[(node << 7) + 2 * lane] : 0.0;
+    b.r3 = s >= 7 ? v[(node << 7) + 2 * (lane + 32)] : 0.0;
+    return b;
+}
+
+// Walks the s generations of one block (memory.py:122-129: left child if its sum exceeds the mass, else subtract
+// and go right); returns the path inside the block.
+__device__ __forceinline__ int walk_block(const DescentBlock &b, const int s, double &mass) {
+    int m = 0;
+#pragma unroll
+    for (int g = 1; g <= DESCENT_GENS; ++g) {
+        if (g <= s) {
+            double lv;
+            if (g <= 5) {
+                lv = shfl_f64(b.r0, (1 << (g - 1)) - 1 + m);
+            } else if (g == 6) {
+                lv = shfl_f64(b.r1, m);
+            } else {
+                const double lo = shfl_f64(b.r2, m & 31), hi = shfl_f64(b.r3, m & 31);
+                lv = (m >> 5) ? hi : lo;
+            }
+            if (lv > mass) {
+                m = 2 * m;
+            } else {
+                mass = __dsub_rn(mass, lv);
+                m = 2 * m + 1;
+            }
+        }
+    }
+    return m;
+}
+
+// The block below the root: the same for every query, so callers load it before they know the query's mass.
+__device__ __forceinline__ DescentBlock root_block(const SampleArgs &a, const int lane) {
+    return load_block(a.sum, 1, a.L < DESCENT_GENS ? a.L : DESCENT_GENS, lane);
+}
+
+// Value of the left child of generation g, pair q, out of a loaded block (every lane asks for the same q).
+__device__ __forceinline__ double block_left(const DescentBlock &b, const int g, const int q) {
+    if (g <= 5) return shfl_f64(b.r0, (1 << (g - 1)) - 1 + q);
+    if (g == 6) return shfl_f64(b.r1, q);
+    const double lo = shfl_f64(b.r2, q & 31), hi = shfl_f64(b.r3, q & 31);
+    return (q >> 5) ? hi : lo;
 }
 
 // The local descent of one query (all 32 lanes) from the root of this tree, then the index and
-// the importance weight.  `mass` is the prefix sum looked for inside this tree, `left` = root_block().
-__device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int64_t q, const int lane, double mass, double left,
+// the importance weight.  `mass` is the prefix sum looked for inside this tree, `blk` = root_block().
+// ceil(L / 7) dependent round trips, the first of them hoisted by the caller; the block that reaches
+// the leaves also brings the RIGHT children of its last generation, so the sampled leaf's value (the
+// weight's numerator) needs no round trip of its own.
+__device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int64_t q, const int lane, double mass, DescentBlock blk,
                                                  const double root_sum, const double root_min, const int64_t idx_base) {
-    // lane -> (generation j in 1..5, pair qg): lane 0 -> 1, lanes 1-2 -> 2, 3-6 -> 3, 7-14 -> 4, 15-30 -> 5
-    const int j = 32 - __clz(lane + 1);
-    const int qg = lane + 1 - (1 << (j - 1));
+    const bool want_w = a.mnn && (a.out_w64 || a.out_w32);
     int64_t node = 1;
     int depth = 0;
+    double leaf_v = 0.0;
 #pragma unroll 1
     while (depth < a.L) {
-        const int s = a.L - depth < 5 ? a.L - depth : 5;
-        if (depth) left = (j <= s && lane < 31) ? a.sum[(node << j) + 2 * qg] : 0.0;
-        int m = 0;  // path inside this 5-generation block
-#pragma unroll
-        for (int g = 1; g <= 5; ++g) {
-            if (g <= s) {
-                double lv = shfl_f64(left, (1 << (g - 1)) - 1 + m);
-                if (lv > mass) {
-                    m = 2 * m;
-                } else {
-                    mass = __dsub_rn(mass, lv);
-                    m = 2 * m + 1;
-                }
-            }
+        const int s = a.L - depth < DESCENT_GENS ? a.L - depth : DESCENT_GENS;
+        const bool last = depth + s == a.L;
+        if (depth) blk = load_block(a.sum, node, s, lane);
+        double rr0 = 0.0, rr1 = 0.0;  // right children of generation s (the leaves' right halves)
+        if (last && want_w) {
+            if (lane < (1 << (s - 1))) rr0 = a.sum[(node << s) + 2 * lane + 1];
+            if (s == 7) rr1 = a.sum[(node << 7) + 2 * (lane + 32) + 1];
+        }
+        const int m = walk_block(blk, s, mass);
+        if (last && want_w) {
+            const int pm = m >> 1;
+            const double lv = block_left(blk, s, pm);
+            const double r_lo = shfl_f64(rr0, pm & 31), r_hi = shfl_f64(rr1, pm & 31);
+            leaf_v = (m & 1) ? ((pm >> 5) ? r_hi : r_lo) : lv;
         }
         node = (node << s) + m;
         depth += s;
     }
     const int64_t k = node - a.cap;
     if (lane == 0) a.out_idx[q] = idx_base + k;
-    if (a.mnn && (a.out_w64 || a.out_w32)) {
+    if (want_w) {
         // memory.py:289-295.  The two pow() evaluations run side by side: lane 0 raises the
         // sampled probability, lane 1 the minimum one (one call site, one pow latency).
         const double n = (double)a.n_rows;
-        const double num = lane == 1 ? root_min : a.sum[a.cap + k];
+        const double num = lane == 1 ? root_min : leaf_v;
         const double r = pow(__dmul_rn(__ddiv_rn(num, root_sum), n), -a.beta);
         const double max_w = shfl_f64(r, 1);
         if (lane == 0) {
@@ -295,14 +347,14 @@ __device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int6
 // Unsharded: one warp per query.
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 1);
+    if (tl_on) tl_stamp(a.tl, 0, 1);
     pdl_launch_dependents();
     pdl_wait();  // the tree is written by the kernel in front of this one
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 2);
+    if (tl_on) tl_stamp(a.tl, 1, 2);
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (q >= a.batch) return;  // whole warps take the same side
-    const double left = root_block(a, lane);  // in flight together with the loads of the prefix total
+    const DescentBlock left = root_block(a, lane);  // in flight together with the loads of the prefix total
     const double root_sum = a.sum[1];
     double mass;
     if (a.direct_mass) {
@@ -314,7 +366,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
     }
     descend_and_emit(a, q, lane, mass, left, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 3);
+    if (tl_on) tl_stamp(a.tl, 2, 3);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -456,7 +508,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
     __shared__ double s_scal[3];
     __shared__ int64_t s_range[2];
     const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 1);
+    if (tl_on) tl_stamp(a.tl, 0, 1);
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // With early publish the records of this sample come from update kernels (this rank's and the peers'), through
@@ -466,7 +518,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
     // still running.  Everything that reads the tree or the caller's inputs comes after the wait.
     const bool early = a.use_mailbox && a.skip_publish;
     if (!early) pdl_wait();
-    double left = 0.0;
+    DescentBlock left;
     if (warp == 0) {
         // only this warp reads the epoch counter, so that it can be advanced as soon as every CTA's warp 0 has it
         const u64 epoch = __ldcg(a.d_epoch) + 1;
@@ -485,9 +537,9 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
             }
         }
         const ShardView v = shard_view(a, epoch, lane);
-        if (tl_on) tl_stamp(a.tl, a.tl_cap, 10);  // records in, view built
+        if (tl_on) tl_stamp(a.tl, 1, 10);  // records in, view built
         if (early) pdl_wait();
-        if (tl_on) tl_stamp(a.tl, a.tl_cap, 2);   // the kernel in front has retired
+        if (tl_on) tl_stamp(a.tl, 2, 2);   // the kernel in front has retired
         left = root_block(a, lane);
         int64_t lo, hi;
         owned_strata(a, v, lane, lo, hi);
@@ -507,7 +559,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         if (early) pdl_wait();
         left = root_block(a, lane);  // the same for every query: requested before the range is known
     }
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 11);  // owned strata known
+    if (tl_on) tl_stamp(a.tl, 3, 11);  // owned strata known
     __syncthreads();
     if (threadIdx.x == 32) {
         // warp 0 of this CTA has consumed the epoch: the last CTA to say so advances it (nothing in this launch
@@ -536,7 +588,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         shard_owner(a, top, seg, q, mass);  // == a.rank by construction of [lo, hi)
         descend_and_emit(a, q, lane, mass, left, root_sum, root_min, idx_base);
     }
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 3);
+    if (tl_on) tl_stamp(a.tl, 4, 3);
 }
 
 }  // namespace perb

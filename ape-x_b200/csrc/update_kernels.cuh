@@ -70,8 +70,7 @@ struct UpdArgs {
     double *const *publish_to; // sharded replay, early publish: the mailboxes of all ranks (null: the next sample publishes)
     int n_shards, shard_rank;  //   this launch's tail stores the refreshed record, tagged with the NEXT exchange epoch
     const u64 *d_epoch;        //   (completed exchange samples + 1), straight into them
-    u64 *tl;                  // timeline (diagnostics), see tl_stamp
-    unsigned tl_cap;
+    u64 *tl;                  // timeline (diagnostics), see tl_stamp: this launch's first entry
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
 };
@@ -304,11 +303,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     // exchange before its own wait (tree_kernels.cuh) and relies on every kernel up to the previous sample having
     // retired by then.  Otherwise the dependents are released at once.
     const bool tl_on = a.tl && rank == 0 && tid == 0;
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 7);
+    if (tl_on) tl_stamp(a.tl, 0, 7);
     if (!a.publish_to) pdl_launch_dependents();  // (early publish: only behind the wait, see above)
     pdl_wait();  // indices / Q tables / the tree itself come from the kernels in front of this one
     if (a.publish_to) pdl_launch_dependents();
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 8);
+    if (tl_on) tl_stamp(a.tl, 1, 8);
     UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
     owned_range(a.range, a.n, first, last);
@@ -348,10 +347,16 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             done_b = td.done[b];
             if (td.out_loss) w_b = td.w[b];
         }
+        // the target network's rows as well when both fit: Q_target(s', argmax) then needs no dependent global load
+        const bool staged_t = staged && (int64_t)2 * cnt * nA <= UPD_STAGE_FLOATS;
         if (staged) {
             const float *src = td.q_next + (int64_t)lo * nA;
+            const float *src_t = td.q_tgt + (int64_t)lo * nA;
 #pragma unroll 1
-            for (int e = tid; e < cnt * nA; e += T) s_q[e] = src[e];
+            for (int e = tid; e < cnt * nA; e += T) {
+                s_q[e] = src[e];
+                if (staged_t) s_q[cnt * nA + e] = src_t[e];
+            }
         }
         if (have) q_a = td.q[b * nA + act_b];
         __syncthreads();
@@ -365,7 +370,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
                 const float x = qn[i];
                 if (x > bv) { bv = x; best = i; }
             }
-            const float boot = td.q_tgt[b * nA + best];
+            const float boot = staged_t ? s_q[cnt * nA + tid * nA + best] : td.q_tgt[b * nA + best];
             const float y = __fadd_rn(rew_b, __fmul_rn(__fmul_rn(td.gamma_n, boot), __fsub_rn(1.0f, done_b)));
             const float x = fabsf(__fsub_rn(y, q_a));
             s_td[tid] = x;
@@ -419,7 +424,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         else __syncthreads();
         if (skip_update) return;
     }
-    if (tl_on) tl_stamp(a.tl, a.tl_cap, 12);  // TD arithmetic done
+    if (tl_on) tl_stamp(a.tl, 2, 12);  // TD arithmetic done
 
     UPD_TRACE(1);
     double my_max = 0.0;
@@ -482,6 +487,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             // keys ascend: the smallest / largest index-valid leaf of the slice, one shared-memory atomic per warp
             const int wmin = __reduce_min_sync(0xffffffffu, kraw >= 0 ? kraw : INT_MAX), wmax = __reduce_max_sync(0xffffffffu, kraw);
             alive = __ballot_sync(0xffffffffu, kk >= 0);
+            // The path relies on ascending indices (they are the sampler's own output).  A caller that scribbled on
+            // the buffer in between is told so: neighbours inside a warp, and the slice against the leaves around it
+            // (checked below), must not descend.
+            const int prev = __shfl_up_sync(0xffffffffu, kraw, 1);
+            if (lane > 0 && kraw >= 0 && prev > kraw) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
             if (lane == 0) {
                 S.warp_cnt[warp] = __popc(alive);
                 if (wmax >= 0) {
@@ -510,6 +520,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             a.t.mnn[a.t.cap + kk] = leaf;
         }
         if (tid == 0) {  // CTA 0 learns every CTA's key range for the borders of stage 2
+            if (s_srt[SRT_KEY_MAX] >= 0 && ((s_srt[SRT_NB_LEFT] > s_srt[SRT_KEY_MIN]) ||
+                                            (s_srt[SRT_NB_RIGHT] >= 0 && s_srt[SRT_NB_RIGHT] < s_srt[SRT_KEY_MAX])))
+                atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending across slices
             long long *home = cl.map_shared_rank(s_bound, 0);
             home[2 * rank] = s_srt[SRT_KEY_MAX] >= 0 ? (long long)s_srt[SRT_KEY_MIN] : -1;
             home[2 * rank + 1] = (long long)s_srt[SRT_KEY_MAX];
@@ -782,7 +795,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             emit_record_values(s_sum[1], s_min[1], partial, a.rec_len, a.rec_out, a.publish_to, a.n_shards, a.shard_rank,
                                a.publish_to ? __ldcg(a.d_epoch) + 1 : 0);
         }
-        if (tl_on) tl_stamp(a.tl, a.tl_cap, 9);
+        if (tl_on) tl_stamp(a.tl, 3, 9);
     }
 }
 

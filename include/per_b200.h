@@ -350,11 +350,13 @@ int per_tune(per_buffer *b, const char *key, int64_t value);
  * sparse rounds done, top rebuilt}; this reads the six stamps of the last launch.  Synchronises. */
 int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream);
 /* Diagnostics: after per_tune(b, "timeline", entries) thread 0 of CTA 0 of every sample / gather /
- * update launch appends (tag << 56) | GPU-global-timer ns stamps (tags: 1 sample entered, 10 shard
+ * update launch stores, into the six entries that launch owns (plain stores, nothing waits for
+ * them; a launch captured in a CUDA graph keeps its entries across replays, so after a run the
+ * list holds the latest execution of each), (tag << 56) | GPU-global-timer ns stamps (tags: 1 sample entered, 10 shard
  * records in, 2 sample past its programmatic-launch wait, 11 owned strata known, 3 sample CTA 0
  * done; 4 gather entered, 5 past its wait, 6 CTA 0 done; 7 update entered, 8 past its wait, 12 TD
- * arithmetic done, 9 CTA 0 done).  Copies up to max_entries of them to h_out, stores the number in
- * h_count and clears the list.  Works inside CUDA-graph replays.  Synchronises `stream`. */
+ * arithmetic done, 9 CTA 0 done).  Copies up to max_entries non-empty entries to h_out (unordered:
+ * sort by time), stores the number in h_count and clears the list.  Works inside CUDA-graph replays.  Synchronises `stream`. */
 int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_count, void *stream);
 
 /* Copies one tree's node array (`_it_sum._value` / `_it_min._value`) to d_out[2*capacity]. */
