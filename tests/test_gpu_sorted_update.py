@@ -117,3 +117,20 @@ def test_sorted_path_fused_td(mods):
         assert torch.equal(pf, ps) and float(lf) == float(ls)
         for which in (pn.TREE_SUM, pn.TREE_MIN):
             assert np.array_equal(bits(fast.tree_values(which))[1:], bits(slow.tree_values(which))[1:])
+
+
+def test_scribbled_index_buffer_is_reported(mods):
+    """The fast path is taken on pointer identity with the last sample's index buffer; if the caller has
+    reordered that buffer in place the kernel cannot recover, but it must say so (BAD_INDEX status)."""
+    memory, pn = mods
+    size, batch = 1 << 14, 512
+    gen = torch.Generator(device="cuda").manual_seed(9)
+    obs = torch.zeros((size, 8), dtype=torch.uint8, device="cuda")
+    z = torch.zeros(size, device="cuda")
+    buf = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    buf.add_batch_device(obs, obs, torch.zeros(size, dtype=torch.int64, device="cuda"), z, z, priorities=priorities("uniform", size, gen))
+    d = buf.sample_device(batch, 0.4, uniforms=np.random.default_rng(0).random(batch), gather=False)
+    d["idx"].copy_(d["idx"].flip(0).clone())
+    buf.update_priorities_device(d["idx"], torch.rand(batch, dtype=torch.float64, device="cuda", generator=gen) + 1e-3)
+    with pytest.raises(AssertionError):
+        buf._raise_status()
