@@ -59,6 +59,19 @@ struct per_buffer_s {
         ++timeline_seq;
         return p;
     }
+    // host-buffer entry points (per_sample_host / per_update_host): device staging for one batch and a pinned
+    // block for the small uploads; grown on demand, reused from call to call
+    struct HostPath {
+        int64_t cap;  // rows
+        double *d_u, *d_w64;
+        int64_t *d_idx, *d_act;
+        float *d_rew, *d_done;
+        uint8_t *d_obs, *d_next, *d_extra;
+        uint8_t *d_upd;   // [cap] int64 indices | [cap] float64 leaves
+        uint8_t *h_pin;   // pinned: [cap] float64 uniforms | [cap] int64 indices | [cap] float64 leaves
+        cudaEvent_t up_done;  // the last upload out of h_pin
+        bool have_event;
+    } hp;
     int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
     bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", bits): programmatic dependent launch for 1 sampling, 2 gather, 4 update kernels
@@ -377,6 +390,41 @@ int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank
     return rc;
 }
 
+
+static void free_host_path(per_buffer *b) {
+    per_buffer::HostPath &h = b->hp;
+    cudaFree(h.d_u); cudaFree(h.d_w64); cudaFree(h.d_idx); cudaFree(h.d_act); cudaFree(h.d_rew); cudaFree(h.d_done);
+    cudaFree(h.d_obs); cudaFree(h.d_next); cudaFree(h.d_extra); cudaFree(h.d_upd);
+    if (h.h_pin) cudaFreeHost(h.h_pin);
+    if (h.have_event) cudaEventDestroy(h.up_done);
+    memset(&h, 0, sizeof h);
+}
+
+// Staging for `rows` rows (device) and the pinned upload block.  Called with the handle's device current.
+static int ensure_host_path(per_buffer *b, int64_t rows, cudaStream_t s) {
+    per_buffer::HostPath &h = b->hp;
+    if (rows <= h.cap) return PER_OK;
+    PER_CUDA(cudaStreamSynchronize(s));
+    free_host_path(b);
+    int64_t cap = 512;
+    while (cap < rows) cap *= 2;
+    PER_CUDA(cudaMalloc(&h.d_u, sizeof(double) * cap));
+    PER_CUDA(cudaMalloc(&h.d_w64, sizeof(double) * cap));
+    PER_CUDA(cudaMalloc(&h.d_idx, sizeof(int64_t) * cap));
+    PER_CUDA(cudaMalloc(&h.d_act, sizeof(int64_t) * cap));
+    PER_CUDA(cudaMalloc(&h.d_rew, sizeof(float) * cap));
+    PER_CUDA(cudaMalloc(&h.d_done, sizeof(float) * cap));
+    PER_CUDA(cudaMalloc(&h.d_obs, (size_t)b->obs_bytes * cap));
+    PER_CUDA(cudaMalloc(&h.d_next, (size_t)b->obs_bytes * cap));
+    if (b->extra_bytes) PER_CUDA(cudaMalloc(&h.d_extra, (size_t)b->extra_bytes * cap));
+    PER_CUDA(cudaMalloc(&h.d_upd, 16 * (size_t)cap));
+    PER_CUDA(cudaHostAlloc(&h.h_pin, 24 * (size_t)cap, cudaHostAllocDefault));
+    PER_CUDA(cudaEventCreateWithFlags(&h.up_done, cudaEventDisableTiming));
+    h.have_event = true;
+    h.cap = cap;
+    return PER_OK;
+}
+
 int per_destroy(per_buffer *b) {
     if (!b) return PER_OK;
     DeviceGuard g(b->device);
@@ -385,6 +433,7 @@ int per_destroy(per_buffer *b) {
     cudaFree(b->stamps);
     cudaFree(b->scal);
     cudaFree(b->timeline);
+    free_host_path(b);
     cudaFree(b->obs);
     cudaFree(b->next);
     cudaFree(b->extra);
@@ -873,6 +922,70 @@ int per_update_leaves(per_buffer *b, const int64_t *d_idx, const double *d_leaf,
     if (n == 0) return PER_OK;
     DeviceGuard g(b->device);
     return update_common(b, d_idx, d_leaf, LEAF_GIVEN, batch_max_priority, n, nullptr, (cudaStream_t)stream);
+}
+
+// ---- host-buffer entry points: what a binding without device pointers calls (memory.py's sample() and
+// update_priorities() go through these; bench.py's e2e number is measured on them) ----
+int per_sample_host(per_buffer *b, const double *h_u, int64_t batch, double beta, void *h_obs, void *h_next, int64_t *h_act,
+                    float *h_rew, float *h_done, void *h_extra, double *h_w64, int64_t *h_idx, void *stream) {
+    if (!b || !h_u || batch <= 0) return fail(PER_ERR_ARG, "per_sample_host: bad argument");
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_host_path(b, batch, s);
+    if (rc) return rc;
+    per_buffer::HostPath &h = b->hp;
+    PER_CUDA(cudaEventSynchronize(h.up_done));  // the pinned block is free again (no-op before the first upload)
+    memcpy(h.h_pin, h_u, sizeof(double) * batch);
+    PER_CUDA(cudaMemcpyAsync(h.d_u, h.h_pin, sizeof(double) * batch, cudaMemcpyHostToDevice, s));
+    PER_CUDA(cudaEventRecord(h.up_done, s));
+    rc = per_sample_indices(b, h.d_u, batch, beta, h.d_idx, h_w64 ? h.d_w64 : nullptr, nullptr, stream);
+    if (rc) return rc;
+    const bool rows = h_obs || h_next || h_act || h_rew || h_done || h_extra;
+    if (rows) {
+        rc = per_gather(b, h.d_idx, batch, h_obs ? h.d_obs : nullptr, h_next ? h.d_next : nullptr, h_act ? h.d_act : nullptr,
+                        h_rew ? h.d_rew : nullptr, h_done ? h.d_done : nullptr, (h_extra && b->extra_bytes) ? h.d_extra : nullptr, stream);
+        if (rc) return rc;
+    }
+    // the two frame batches first: they are the PCIe time, everything else hides behind them
+    if (h_obs) PER_CUDA(cudaMemcpyAsync(h_obs, h.d_obs, (size_t)b->obs_bytes * batch, cudaMemcpyDeviceToHost, s));
+    if (h_next) PER_CUDA(cudaMemcpyAsync(h_next, h.d_next, (size_t)b->obs_bytes * batch, cudaMemcpyDeviceToHost, s));
+    if (h_extra && b->extra_bytes) PER_CUDA(cudaMemcpyAsync(h_extra, h.d_extra, (size_t)b->extra_bytes * batch, cudaMemcpyDeviceToHost, s));
+    if (h_act) PER_CUDA(cudaMemcpyAsync(h_act, h.d_act, sizeof(int64_t) * batch, cudaMemcpyDeviceToHost, s));
+    if (h_rew) PER_CUDA(cudaMemcpyAsync(h_rew, h.d_rew, sizeof(float) * batch, cudaMemcpyDeviceToHost, s));
+    if (h_done) PER_CUDA(cudaMemcpyAsync(h_done, h.d_done, sizeof(float) * batch, cudaMemcpyDeviceToHost, s));
+    if (h_w64) PER_CUDA(cudaMemcpyAsync(h_w64, h.d_w64, sizeof(double) * batch, cudaMemcpyDeviceToHost, s));
+    if (h_idx) PER_CUDA(cudaMemcpyAsync(h_idx, h.d_idx, sizeof(int64_t) * batch, cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaStreamSynchronize(s));
+    return PER_OK;
+}
+
+int per_update_host(per_buffer *b, const int64_t *h_idx, const double *h_prio, int64_t n, double *h_batch_max, void *stream) {
+    if (!b || n < 0 || (n && (!h_idx || !h_prio))) return fail(PER_ERR_ARG, "per_update_host: bad argument");
+    if (h_batch_max) *h_batch_max = 0.0;
+    if (n == 0) return PER_OK;
+    double bmax = 0.0;
+    for (int64_t i = 0; i < n; ++i) {  // the reference asserts pair by pair (memory.py:315-316); here before anything is applied
+        if (!(h_prio[i] > 0)) return fail(PER_ERR_ASSERT, "priority > 0");
+        if (h_idx[i] < 0 || h_idx[i] >= b->len) return fail(PER_ERR_ASSERT, "0 <= idx < len(self._storage)");
+        if (h_prio[i] > bmax) bmax = h_prio[i];
+    }
+    DeviceGuard g(b->device);
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = ensure_host_path(b, n, s);
+    if (rc) return rc;
+    per_buffer::HostPath &h = b->hp;
+    PER_CUDA(cudaEventSynchronize(h.up_done));
+    int64_t *p_idx = reinterpret_cast<int64_t *>(h.h_pin + 8 * (size_t)h.cap);
+    double *p_leaf = reinterpret_cast<double *>(h.h_pin + 16 * (size_t)h.cap);
+    memcpy(p_idx, h_idx, sizeof(int64_t) * n);
+    for (int64_t i = 0; i < n; ++i) p_leaf[i] = pow(h_prio[i], b->alpha);  // libm: the bits CPython produces at memory.py:317
+    int64_t *d_idx = reinterpret_cast<int64_t *>(h.d_upd);
+    double *d_leaf = reinterpret_cast<double *>(h.d_upd + 8 * (size_t)h.cap);
+    PER_CUDA(cudaMemcpyAsync(d_idx, p_idx, sizeof(int64_t) * n, cudaMemcpyHostToDevice, s));
+    PER_CUDA(cudaMemcpyAsync(d_leaf, p_leaf, sizeof(double) * n, cudaMemcpyHostToDevice, s));
+    PER_CUDA(cudaEventRecord(h.up_done, s));
+    if (h_batch_max) *h_batch_max = bmax;
+    return per_update_leaves(b, d_idx, d_leaf, bmax, n, stream);
 }
 
 int per_pow_alpha_host(const double *h_prio, double alpha, double *h_out, int64_t n) {

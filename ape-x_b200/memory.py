@@ -68,6 +68,17 @@ class _HostStage(object):
         ent[1].record()
         return d
 
+    def out_slot(self, name, shape, dtype):
+        """One of RING pinned host tensors for a result the native library writes by itself (per_sample_host)."""
+        key = ("out:" + name, tuple(shape), str(dtype))
+        ent = self.down_bufs.get(key)
+        if ent is None:
+            ent = [[torch.empty(tuple(shape), dtype=dtype, pin_memory=True) for _ in range(self.RING)], 0]
+            self.down_bufs[key] = ent
+        slot = ent[0][ent[1] % self.RING]
+        ent[1] += 1
+        return slot
+
     def down(self, named_tensors):
         """{name: cuda tensor} -> {name: numpy array}; one synchronisation for the lot."""
         outs = {}
@@ -520,32 +531,42 @@ class PrioritizedReplayBuffer(ReplayBuffer):
     _sample_fields = ("obs", "act", "rew", "next_obs", "done")
 
     def sample(self, batch_size, beta):
-        """memory.py:252-298 -> (obs, act, rew, next_obs, done, weights float64[B], idxes list[int])."""
+        """memory.py:252-298 -> (obs, act, rew, next_obs, done, weights float64[B], idxes list[int]).
+        One native call with host buffers (per_sample_host): uniforms up, sampling + gather kernels,
+        results into pinned host arrays (handed out as numpy views, see _HostStage)."""
         assert beta > 0
         assert self._h is not None and len(self) >= 2, "sample() needs at least two stored transitions"
-        d = self.sample_device(batch_size, beta)
-        d.pop("weights")
-        h = self._host.down(d)
-        return tuple([h[k] for k in self._sample_fields] + [h["weights64"], h["idx"].tolist()])
+        self._flush()
+        B = int(batch_size)
+        u = self._draw_uniforms(B)
+        slot = self._host.out_slot
+        odt = getattr(torch, self._obs_dtype.name)
+        h = {"obs": slot("obs", (B,) + tuple(self._obs_shape), odt), "next_obs": slot("next_obs", (B,) + tuple(self._obs_shape), odt),
+             "act": slot("act", (B,), torch.int64), "rew": slot("rew", (B,), torch.float32),
+             "done": slot("done", (B,), torch.float32), "weights64": slot("w64", (B,), torch.float64),
+             "idx": slot("idx", (B,), torch.int64)}
+        if self._extra_shape is not None:
+            h["a_mu"] = slot("a_mu", (B,) + tuple(self._extra_shape), getattr(torch, self._extra_dtype.name))
+        P = lambda t: _n.C.c_void_p(t.data_ptr())
+        _n.check(_n.lib.per_sample_host(self._h, u.ctypes.data, B, float(beta), P(h["obs"]), P(h["next_obs"]), P(h["act"]),
+                                        P(h["rew"]), P(h["done"]), P(h["a_mu"]) if "a_mu" in h else None, P(h["weights64"]),
+                                        P(h["idx"]), _n.stream_ptr()))
+        out = {k: (np.array(v.numpy()) if COPY_SAMPLES else v.numpy()) for k, v in h.items()}
+        return tuple([out[k] for k in self._sample_fields] + [out["weights64"], out["idx"].tolist()])
 
     def update_priorities(self, idxes, priorities):
         """memory.py:300-320.  The reference walks the pairs in order and asserts as it goes;
-        here the same conditions are checked for the whole batch first, then the batch is
-        applied on the GPU with the same last-write-wins result."""
+        here the same conditions are checked for the whole batch first (in per_update_host), then
+        the batch is applied on the GPU with the same last-write-wins result."""
         assert len(idxes) == len(priorities)
         if len(idxes) == 0:
             return
         self._flush()
-        idx = np.asarray(idxes, dtype=np.int64)
-        pr = np.asarray(priorities, dtype=np.float64)
-        assert bool((pr > 0).all())
-        assert bool(((idx >= 0) & (idx < len(self))).all())
-        leaves = _pow_alpha_exact(pr, self._alpha)
-        bmax = float(pr.max())
-        d_idx = self._host.up("upd_idx", idx)  # keep both alive until the launch is enqueued
-        d_leaf = self._host.up("upd_leaf", leaves)
-        _n.check(_n.lib.per_update_leaves(self._h, _n.ptr(d_idx), _n.ptr(d_leaf), bmax, idx.size, _n.stream_ptr()))
-        self._max_priority = max(self._max_priority, bmax)
+        idx = np.ascontiguousarray(idxes, dtype=np.int64)
+        pr = np.ascontiguousarray(priorities, dtype=np.float64)
+        bmax = _n.C.c_double(0.0)
+        _n.check(_n.lib.per_update_host(self._h, idx.ctypes.data, pr.ctypes.data, idx.size, _n.C.byref(bmax), _n.stream_ptr()))
+        self._max_priority = max(self._max_priority, bmax.value)
 
     def update_priorities_device(self, idx, priorities):
         """Extension: idx int64 and priorities float32/float64 CUDA tensors; pow on the device

@@ -47,6 +47,8 @@ SIGNATURES = {
     "aql_set_weights": (C.c_int, [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "aql_trace": (C.c_int, [_p, C.POINTER(_i64), _p]),
     "per_timeline": (C.c_int, [_p, C.POINTER(_i64), _i64, C.POINTER(_i64), _p]),
+    "per_sample_host": (C.c_int, [_p, _p, _i64, C.c_double, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "per_update_host": (C.c_int, [_p, _p, _p, _i64, C.POINTER(C.c_double), _p]),
     "aql_candidate_q": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "nstep_assemble": (C.c_int, [C.c_int, _i64, _p, _p, _p, _p, _p, _p, _i64, C.c_int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "seg_set_noalloc": (C.c_int, [C.c_int, _p, _p, _i64, _p, _p, _i64, _p, _p]),

@@ -243,6 +243,28 @@ int per_update_priorities(per_buffer *b, const int64_t *d_idx, const void *d_pri
 int per_update_leaves(per_buffer *b, const int64_t *d_idx, const double *d_leaf, double batch_max_priority,
                       int64_t n, void *stream);
 
+/* ---- the same path with HOST buffers: what a binding that owns no device memory calls ----
+ * (memory.py's sample() / update_priorities() mirrors go through these two; bench.py's `e2e`
+ * number is measured on them.)
+ *
+ * PrioritizedReplayBuffer.sample (memory.py:252-298) in one call: h_u = `batch` uniforms in [0,1)
+ * drawn by the caller (random.random(), memory.py:247); outputs are host pointers, NULL = not
+ * wanted: frame batches h_obs / h_next (batch x obs_bytes, row-compact), h_act int64, h_rew /
+ * h_done float32, h_extra (batch x extra_bytes), h_w64 float64 importance weights, h_idx int64.
+ * Uploads the uniforms, runs the sampling and gather kernels into staging the handle keeps,
+ * copies the results out (frames first: they are the PCIe time) and synchronises `stream`.
+ * Pinned (page-locked) output buffers get the full PCIe rate; pageable ones work. */
+int per_sample_host(per_buffer *b, const double *h_u, int64_t batch, double beta, void *h_obs,
+                    void *h_next, int64_t *h_act, float *h_rew, float *h_done, void *h_extra,
+                    double *h_w64, int64_t *h_idx, void *stream);
+
+/* PrioritizedReplayBuffer.update_priorities (memory.py:300-320) with host arrays: checks the
+ * reference's two assertions for every pair first (PER_ERR_ASSERT, nothing applied), raises the
+ * priorities to alpha with the C library's pow (bit-identical leaves), uploads and launches the
+ * update; stream-ordered, does not synchronise.  *h_batch_max (may be NULL) = max priority. */
+int per_update_host(per_buffer *b, const int64_t *h_idx, const double *h_prio, int64_t n,
+                    double *h_batch_max, void *stream);
+
 /* Host helper: h_out[j] = pow(h_prio[j], alpha) with the C library's double pow —
  * the function CPython's `priority ** alpha` calls (memory.py:317).  No GPU work. */
 int per_pow_alpha_host(const double *h_prio, double alpha, double *h_out, int64_t n);
