@@ -213,6 +213,11 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_tma(GatherArgs
     }
     bulk_wait_read<0>();
     if (tl_on) tl_stamp(a.tl, 2, 6);
+    if (a.tl) {  // timeline on: the latest finish over all issuing lanes of the grid (diagnostic runs only)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(a.tl + 3, (13ull << 56) | (t & ((1ull << 56) - 1)));
+    }
 }
 
 // Register-staged variant: one warp per piece, up to 16 x 16-B loads in flight per lane,

@@ -259,8 +259,6 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
-    if args.timeline:
-        pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"timeline", 8192))
     if os.environ.get("PER_SORTED_UPDATE") is not None:
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"sorted_update", int(os.environ["PER_SORTED_UPDATE"])))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
@@ -485,20 +483,33 @@ def main():
         st3 = (pn.C.c_int64 * 3)()
         pn.check(lib.per_shard_exchange_stats(h, st3, sp))
         exchange_us = {"mean": st3[1] / max(st3[0], 1) / 1e3, "max": st3[2] / 1e3, "samples": int(st3[0])}
-    if args.timeline and graphs is not None:
+    # ---- step anatomy: the same graph blocks captured once more with the kernels' GPU-timer stamps on ----
+    # (per_timeline: plain stores by CTA 0 of every launch, and for the gather the latest finish over the whole
+    # grid).  Outside the timed region; tells how long each kernel takes INSIDE the chained step, which the
+    # event-bracketed gather above cannot: an event between two kernels breaks their programmatic chaining.
+    anatomy = None
+    if graphs is not None:
         cap_tl = 8192
+        pn.check(lib.per_tune(h, b"timeline", cap_tl))
+        with torch.cuda.stream(side):
+            probe = [capture(lambda j=j: full_block(j * GRAPH_STEPS)) for j in range(3)]
+        stream.wait_stream(side)
         arr = (pn.C.c_int64 * cap_tl)()
         cnt = pn.C.c_int64(0)
+        for g in probe:  # warm
+            g.replay()
+        barrier()
         pn.check(lib.per_timeline(h, arr, cap_tl, pn.C.byref(cnt), sp))  # clear
         barrier()
-        for blk in range(3):
-            graphs[blk % N_GRAPHS].replay()
+        for g in probe:
+            g.replay()
         barrier()
         pn.check(lib.per_timeline(h, arr, cap_tl, pn.C.byref(cnt), sp))
+        pn.check(lib.per_tune(h, b"timeline", 0))
         ent = sorted(((int(arr[i]) & ((1 << 56) - 1), (int(arr[i]) >> 56) & 0xff) for i in range(cnt.value)))
         names = {7: "update entered", 8: "update past wait", 12: "TD done", 9: "update CTA0 done", 1: "sample entered",
                  10: "records in", 2: "sample past wait", 11: "strata known", 3: "sample CTA0 done", 4: "gather entered",
-                 5: "gather past wait", 6: "gather CTA0 done"}
+                 5: "gather past wait", 6: "gather CTA0 done", 13: "gather grid done"}
         steps_tl, cur = [], None
         for t, tag in ent:  # a step of the graph = [update, sample, gather]; anchor = update past its wait
             if tag == 8:
@@ -507,13 +518,21 @@ def main():
                 cur = {"t0": t}
             elif cur is not None and tag not in cur:
                 cur[tag] = t - cur["t0"]
-        periods = np.diff([c["t0"] for c in steps_tl]) if len(steps_tl) > 2 else np.array([0])
-        msg = "rank %d timeline (us after 'update past wait', median of %d steps; period %.2f): " % (rank, len(steps_tl), float(np.median(periods)) / 1e3)
-        for tag in (12, 9, 1, 10, 2, 11, 3, 4, 5, 6, 7):
-            vals = [c[tag] for c in steps_tl[2:] if tag in c]
-            if vals:
-                msg += "%s %.2f | " % (names[tag], float(np.median(vals)) / 1e3)
-        sys.stderr.write(msg + "\n")
+        med = lambda xs: float(np.median(xs)) / 1e3 if len(xs) else None
+        body = steps_tl[2:]
+        periods = np.diff([c["t0"] for c in steps_tl]) if len(steps_tl) > 2 else np.array([])
+        span = lambda a_, b_: med([c[b_] - (c[a_] if a_ != 8 else 0) for c in body if b_ in c and (a_ == 8 or a_ in c)])
+        anatomy = {"steps": len(body), "period": med(periods), "td_arithmetic": span(8, 12), "update": span(8, 9),
+                   "sample": span(2, 3), "gather_cta0": span(5, 6), "gather_grid": span(5, 13),
+                   "how": "GPU global-timer stamps written by the kernels (per_timeline) in 3 replayed graph blocks after "
+                          "the timed region: past the programmatic-launch wait -> done"}
+        if args.timeline:
+            msg = "rank %d timeline (us after 'update past wait', median of %d steps; period %.2f): " % (rank, len(body), anatomy["period"] or 0.0)
+            for tag in (12, 9, 1, 10, 2, 11, 3, 4, 5, 6, 13, 7):
+                vals = [c[tag] for c in body if tag in c]
+                if vals:
+                    msg += "%s %.2f | " % (names[tag], med(vals))
+            sys.stderr.write(msg + "\n")
     value = GB * K / (ms * 1e-3)
     rows_this_rank = int((idx >= 0).sum().item())
     status = pn.C.c_int64(0)
@@ -595,10 +614,17 @@ def main():
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "roofline": {"bound": "hbm", "kernel": "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC if world == 1 else None,
-                         "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3},
+                         "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3,
+                         "in_step": None if not (anatomy and anatomy.get("gather_grid")) else {
+                             "avg_launch_us": anatomy["gather_grid"],
+                             "achieved": launch_bytes / (anatomy["gather_grid"] * 1e-6) / 1e9,
+                             "frac": launch_bytes / (anatomy["gather_grid"] * 1e-6) / 1e9 / peak,
+                             "how": "supplementary: the same launch timed by the kernel's own GPU-timer stamps inside the chained "
+                                    "step (wait passed -> last lane of the grid done); the event-bracketed figure above runs the "
+                                    "kernel unchained from its neighbours"}},
             "cpu_baseline": cpu, "launch": launch_mode, "value_eager_launches": eager_value,
             "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
-            "record_exchange_us": exchange_us,
+            "record_exchange_us": exchange_us, "step_anatomy_us": anatomy,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -376,7 +376,7 @@ int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream);
  * them; a launch captured in a CUDA graph keeps its entries across replays, so after a run the
  * list holds the latest execution of each), (tag << 56) | GPU-global-timer ns stamps (tags: 1 sample entered, 10 shard
  * records in, 2 sample past its programmatic-launch wait, 11 owned strata known, 3 sample CTA 0
- * done; 4 gather entered, 5 past its wait, 6 CTA 0 done; 7 update entered, 8 past its wait, 12 TD
+ * done; 4 gather entered, 5 past its wait, 6 CTA 0 done, 13 last issuing lane of the grid done; 7 update entered, 8 past its wait, 12 TD
  * arithmetic done, 9 CTA 0 done).  Copies up to max_entries non-empty entries to h_out (unordered:
  * sort by time), stores the number in h_count and clears the list.  Works inside CUDA-graph replays.  Synchronises `stream`. */
 int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_count, void *stream);
