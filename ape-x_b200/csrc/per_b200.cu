@@ -75,6 +75,7 @@ struct per_buffer_s {
     int early_publish;         // per_tune("early_publish", 1): updates publish the record of the next sample (see header)
     bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", bits): programmatic dependent launch for 1 sampling, 2 gather, 4 update kernels
+    int upd_cluster_max;       // per_tune("update_cluster_max", items): larger plain updates take the multi-launch form
     int sorted_update;         // per_tune("sorted_update", 0/1): updates of the sample just drawn take the sorted fast path
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
@@ -129,7 +130,7 @@ int grid_for(int64_t n, int threads, int sm_count) {
 int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s, bool pdl = false) {
     TdArgs none;
     memset(&none, 0, sizeof none);
-    if (a.n <= UPD_CLUSTER_MAX_ITEMS) {
+    if (a.n <= (td || a.range || a.cluster_max <= 0 ? UPD_CLUSTER_MAX_ITEMS : a.cluster_max)) {
         // one launch: a cluster of CTAs, 64 items (8 lanes each) per CTA and round
         int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));
         if (ncta < 1) ncta = 1;
@@ -845,6 +846,10 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->early_publish = value != 0;
         return PER_OK;
     }
+    if (!strcmp(key, "update_cluster_max")) {
+        b->upd_cluster_max = (int)value;
+        return PER_OK;
+    }
     if (!strcmp(key, "sorted_update")) {
         b->sorted_update = value != 0;
         return PER_OK;
@@ -904,6 +909,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     // the buffer the last sample wrote its (ascending) indices into: duplicates are adjacent
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     a.sorted_fast = b->sorted_update;
+    a.cluster_max = b->upd_cluster_max;
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);
 }
 

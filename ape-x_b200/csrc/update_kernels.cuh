@@ -63,6 +63,7 @@ struct UpdArgs {
     double *rec_out;          // sharded replay: refresh this shard's 4-double record after the update (may be null)
     int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
     int64_t rec_len;          //   local len
+    int cluster_max;          // host side: plain updates above this many items use the multi-launch form (<= 0: the built-in limit)
     int sorted_fast;          // sorted_idx: take the per-CTA climb (sorted fast path) instead of the level-synchronous rounds
     int sorted_idx;           // the indices are non-decreasing (they are the stratified sample just drawn): equal
                               // indices are adjacent, so "a later duplicate wins" needs one look at idx[j+1], no atomics
