@@ -99,6 +99,8 @@ __global__ void k_fill_f64(double *p, int64_t n, double x) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = x;
 }
 
+constexpr int64_t SAMPLE_WIDE_MIN = 2048;  // per_sample_indices: batches from here on use k_sample_wide
+
 bool is_pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
 
 int ceil_log2(int64_t x) {
@@ -539,7 +541,11 @@ int per_sample_indices(per_buffer *b, const double *d_u, int64_t batch, double b
     a.out_w32 = d_out_w32;
     a.status = b->status();
     a.tl = b->tl_next();
-    PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
+    if (batch >= SAMPLE_WIDE_MIN)  // enough queries to fill the machine: one thread per query
+        PER_CUDA(launch_pdl(k_sample_wide, dim3((unsigned)((batch + SAMPLE_WIDE_THREADS - 1) / SAMPLE_WIDE_THREADS)),
+                            dim3(SAMPLE_WIDE_THREADS), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
+    else
+        PER_CUDA(launch_pdl(k_sample, dim3((unsigned)((batch * 32 + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
     PER_CUDA(cudaGetLastError());
     b->last_sample_idx = d_out_idx;
     b->last_sample_batch = batch;

@@ -369,6 +369,54 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     if (tl_on) tl_stamp(a.tl, 2, 3);
 }
 
+// Unsharded, large batches (thousands of queries): one THREAD per query.  A warp per query spends ~750 warp
+// instructions on a query (shuffle-resolved walk, pow on two lanes); with enough queries to fill the machine the
+// dependent 8-byte loads of a per-thread walk (L of them, the top levels hitting in L1) hide behind each other and
+// the instruction count per query drops 30-fold.  Same arithmetic, same order: same bits.  p_total is computed
+// once per CTA.
+constexpr int SAMPLE_WIDE_THREADS = 256;
+__global__ void __launch_bounds__(SAMPLE_WIDE_THREADS) k_sample_wide(SampleArgs a) {
+    __shared__ double s_seg;
+    pdl_launch_dependents();
+    pdl_wait();
+    if (threadIdx.x < 32 && !a.direct_mass) {
+        const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
+        if (threadIdx.x == 0) s_seg = __ddiv_rn(total, (double)a.batch);     // memory.py:245
+    }
+    __syncthreads();
+    const int64_t q = blockIdx.x * (int64_t)SAMPLE_WIDE_THREADS + threadIdx.x;
+    if (q >= a.batch) return;
+    const double root_sum = a.sum[1];
+    double mass;
+    if (a.direct_mass) {
+        mass = a.u[q];
+        if (!(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
+    } else {
+        const double seg = s_seg;
+        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));  // memory.py:247
+    }
+    int64_t node = 1;
+#pragma unroll 1
+    for (int d = 0; d < a.L; ++d) {  // memory.py:122-129
+        const double lv = a.sum[2 * node];
+        if (lv > mass) {
+            node = 2 * node;
+        } else {
+            mass = __dsub_rn(mass, lv);
+            node = 2 * node + 1;
+        }
+    }
+    const int64_t k = node - a.cap;
+    a.out_idx[q] = k;
+    if (a.mnn && (a.out_w64 || a.out_w32)) {  // memory.py:289-295
+        const double n = (double)a.n_rows;
+        const double max_w = pow(__dmul_rn(__ddiv_rn(a.mnn[1], root_sum), n), -a.beta);
+        const double w = __ddiv_rn(pow(__dmul_rn(__ddiv_rn(a.sum[node], root_sum), n), -a.beta), max_w);
+        if (a.out_w64) a.out_w64[q] = w;
+        if (a.out_w32) a.out_w32[q] = (float)w;
+    }
+}
+
 // ---------------------------------------------------------------------------------------
 // Sharded form.  The view of the virtual tree above the shard roots is built ONCE per CTA (not
 // per query): wait for the records, top tree, p_total, segment width.  Stratum masses grow with
