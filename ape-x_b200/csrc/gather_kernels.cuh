@@ -22,7 +22,9 @@ constexpr int GATHER_SMEM_MAX = 200 * 1024;
 
 // Launch shape of the TMA gather; defaults chosen by the sweep in profiles/ (see DESIGN.md).
 struct GatherTune {
-    int mode = 0;        // 0: TMA bulk copies through shared memory, 1: LDG.128/STG.128 through registers
+    int mode = 1;        // 0: TMA bulk copies through shared memory, 1: LDG.128/STG.128 through registers (see DESIGN.md section 3:
+                         // alone the two run the same 12.3 us; inside the chained step the register-staged one is 2.4 us
+                         // ahead because the TMA variant's 226 KB/SM of dynamic shared memory slows the kernels around it)
     int warps = 4;       // issuing warps per CTA
     int stages = 2;      // pieces in flight per warp
     int piece = 7056;    // bytes per piece (multiple of 16); 7056 = one 84x84 frame
@@ -231,7 +233,16 @@ __device__ __forceinline__ void st_stream(int4 *p, const int4 &v) {
     asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-__global__ void __launch_bounds__(256) k_gather_ldg(GatherArgs a, int per_query) {
+// DEPTH = 16-byte loads in flight per lane.  16 (96 registers, two 256-thread CTAs per SM, a whole 7 056-byte piece in
+// flight per warp) measured better inside the step than 8 (64 registers, four CTAs per SM, 4 KB per warp) at every
+// piece size tried (profiles/r01_notes.md): bytes in flight per warp matter more than the number of warps.
+template <int DEPTH>
+__global__ void __launch_bounds__(256, DEPTH <= 8 ? 4 : 2) k_gather_ldg(GatherArgs a, int per_query) {
+    const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
+    if (tl_on) tl_stamp(a.tl, 0, 4);
+    pdl_launch_dependents();
+    pdl_wait();  // indices and range tags come from the sampling kernel in front of this one
+    if (tl_on) tl_stamp(a.tl, 1, 5);
     int64_t first_q, last_q;
     gather_range(a, first_q, last_q);
     gather_scalars(a, first_q, last_q);
@@ -244,19 +255,25 @@ __global__ void __launch_bounds__(256) k_gather_ldg(GatherArgs a, int per_query)
         const int4 *src = reinterpret_cast<const int4 *>(p.src);
         int4 *dst = reinterpret_cast<int4 *>(p.dst);
         const int nv = (int)(p.bytes >> 4);
-        for (int base = 0; base < nv; base += 32 * 16) {
-            int4 v[16];
+        for (int base = 0; base < nv; base += 32 * DEPTH) {
+            int4 v[DEPTH];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
+            for (int j = 0; j < DEPTH; ++j) {
                 int e = base + j * 32 + lane;
                 if (e < nv) v[j] = ld_stream(src + e);
             }
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
+            for (int j = 0; j < DEPTH; ++j) {
                 int e = base + j * 32 + lane;
                 if (e < nv) st_stream(dst + e, v[j]);
             }
         }
+    }
+    if (tl_on) tl_stamp(a.tl, 2, 6);
+    if (a.tl && lane == 0) {  // timeline on: the latest finish over all warps of the grid (diagnostic runs only)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(a.tl + 3, (13ull << 56) | (t & ((1ull << 56) - 1)));
     }
 }
 

@@ -775,7 +775,7 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
         int64_t grid = (items + 7) / 8;
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;
         if (grid < 1) grid = 1;
-        k_gather_ldg<<<(unsigned)grid, 256, 0, s>>>(a, per_query);
+        PER_CUDA(launch_pdl(k_gather_ldg<16>, dim3((unsigned)grid), dim3(256), 0, s, (b->pdl & 2) != 0, a, per_query));
     }
     if (any_slow) k_gather_bytes<<<grid_for(batch * 3 * 32, 256, b->sm_count), 256, 0, s>>>(slow);
     PER_CUDA(cudaGetLastError());
@@ -873,7 +873,7 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
     const int64_t smem = round_up(t.warps * t.stages * 8, 128) + (int64_t)t.warps * t.stages * t.piece;
     if (t.mode < 0 || t.mode > 1 || t.warps < 1 || t.warps > GATHER_MAX_WARPS || t.stages < 2 || t.stages > 64 ||
         t.piece < 16 || t.piece % 16 || t.ctas_per_sm < 1 || t.ctas_per_sm > 8 || smem > GATHER_SMEM_MAX ||
-        (smem + 1024) * t.ctas_per_sm > 228 * 1024)
+        (t.mode == 0 && (smem + 1024) * t.ctas_per_sm > 228 * 1024))
         return fail(PER_ERR_ARG, "per_tune: %s=%lld gives an invalid launch shape (smem %lld B x %d CTAs/SM)", key,
                     (long long)value, (long long)smem, t.ctas_per_sm);
     b->tune = t;

@@ -43,9 +43,9 @@ UNIT = "transitions/s"
 # per sampled transition the gather reads 2*28224 B of frames + 16 B of
 # scalars and writes the same.
 GATHER_BYTES_PER_ROW = 2 * (2 * OBS_BYTES + 16)
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_gather_tma launch at this workload, from the
-# ncu --set full capture summarised in profiles/ (the 28.9 MB written stay in the 126 MB L2)
-NCU_GATHER_TRAFFIC = 29242368 + 434688
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_gather_ldg<16> launch at this workload, from the
+# ncu --set full capture summarised in profiles/r01e_ncu_summary.csv (the 28.9 MB written stay in the 126 MB L2)
+NCU_GATHER_TRAFFIC = 29224192 + 315392
 
 
 def peaks():
@@ -259,6 +259,12 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
+    if os.environ.get("PER_GATHER_MODE") is not None:  # experiment: 1 = register-staged gather, no shared memory
+        hh = buf._h if world == 1 else shard._h
+        pn.check(pn.lib.per_tune(hh, b"gather_mode", int(os.environ["PER_GATHER_MODE"])))
+        pn.check(pn.lib.per_tune(hh, b"gather_ctas_per_sm", int(os.environ.get("PER_GATHER_CTAS", "2"))))
+        if os.environ.get("PER_GATHER_PIECE"):
+            pn.check(pn.lib.per_tune(hh, b"gather_piece", int(os.environ["PER_GATHER_PIECE"])))
     if os.environ.get("PER_SORTED_UPDATE") is not None:
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"sorted_update", int(os.environ["PER_SORTED_UPDATE"])))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
@@ -307,7 +313,7 @@ def main():
             None, P(o_loss), sp)
     u_ptrs = [pn.C.c_void_p(u_all[i].data_ptr()) for i in range(n_u)]
     a_rec, a_all = P(shard_rec), P(all_rec)
-    # kernels per step: k_sample, k_gather_tma, k_update_cluster (TD fused in front); sharded adds
+    # kernels per step: k_sample, k_gather_ldg, k_update_cluster (TD fused in front); sharded adds
     # k_shard_record (+ NCCL's all-gather kernel, not ours) and B > 2048 uses the multi-launch update
     launches_per_step = 3 if (world == 1 or use_mailbox) else 4
 
@@ -612,7 +618,7 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-            "roofline": {"bound": "hbm", "kernel": "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "k_gather_ldg<16>" if os.environ.get("PER_GATHER_MODE", "1") == "1" else "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC if world == 1 else None,
                          "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3,
                          "in_step": None if not (anatomy and anatomy.get("gather_grid")) else {

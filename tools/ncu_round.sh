@@ -7,7 +7,7 @@
 R=${1:-r01}; STAGE=${2:-list}
 mkdir -p gpurun_out
 ARGS="--steps 48 --warmup 5 --no-cpu-baseline --eager"
-KERNELS='k_sample|k_gather_tma|k_update_cluster'
+KERNELS='k_sample|k_gather_ldg|k_gather_tma|k_update_cluster'
 case $STAGE in
 list)
   python bench.py $ARGS > gpurun_out/plain_$R.log 2>&1 &&
