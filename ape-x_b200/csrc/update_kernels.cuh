@@ -178,9 +178,8 @@ __device__ __forceinline__ void dense_load(const TreeRef &t, int64_t a, int k, d
         if (t.mnn) s_min[n + i] = ldcg_f64(t.mnn + (a << k) + i);
     }
 }
-// Expects the bottom row in s_sum / s_min [n, 2n) and a CTA barrier behind the stores that filled it.
-__device__ __forceinline__ void dense_build_write(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
-    const int n = 1 << k;
+// Expects the bottom row in s_sum / s_min [n, 2n) and a CTA barrier behind the stores that filled it; ends with a barrier.
+__device__ __forceinline__ void dense_build(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
     // all generations in shared memory first (CTA barriers down to 32 nodes, then one warp) ...
 #pragma unroll 1
     for (int j = k - 1; j >= 5; --j) {
@@ -210,13 +209,20 @@ __device__ __forceinline__ void dense_build_write(const TreeRef &t, int64_t a, i
         }
     }
     __syncthreads();
-    // ... then one coalesced pass writes them out: relative heap slot (1<<j)+i  <->  node (a<<j)+i
+}
+// ... then one coalesced pass writes them out: relative heap slot (1<<j)+i  <->  node (a<<j)+i
+__device__ __forceinline__ void dense_write(const TreeRef &t, int64_t a, int k, const double *s_sum, const double *s_min) {
+    const int n = 1 << k;
     for (int p = 1 + threadIdx.x; p < n; p += blockDim.x) {
         const int j = 31 - __clz(p);
         const int64_t node = (a << j) + (p - (1 << j));
         if (t.sum) t.sum[node] = s_sum[p];
         if (t.mnn) t.mnn[node] = s_min[p];
     }
+}
+__device__ __forceinline__ void dense_build_write(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+    dense_build(t, a, k, s_sum, s_min);
+    dense_write(t, a, k, s_sum, s_min);
 }
 __device__ __forceinline__ void dense_lift_block(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
     dense_load(t, a, k, s_sum, s_min);
@@ -676,7 +682,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         const bool term_low = a.t.L - (tid & 31) > top;  // the node lies below the dense top
         double term = (emit && term_low) ? __ldcg(a.t.sum + term_node) : 0.0;
         if (!sorted_path) {
-            dense_lift_block(a.t, 1, top, s_sum, s_min);
+            dense_load(a.t, 1, top, s_sum, s_min);
+            __syncthreads();
         } else {
             // ---- stage 2: the nodes shared between CTAs, one chain per border, next to the dense top ----
             double *s2 = s_tree + S2_OFF_DOUBLES;  // [border][level - 1][sum L, sum R, min L, min R]
@@ -787,8 +794,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
                 }
             }
             if (chains) __syncthreads();
-            dense_build_write(a.t, 1, top, s_sum, s_min);
         }
+        // the top in shared memory; the record leaves BEFORE the write-out, so that its system-scope release does not
+        // have to wait for the two thousand node stores to be acknowledged (the record's readers need none of them,
+        // and this rank's own next sample waits for this kernel to retire anyway)
+        dense_build(a.t, 1, top, s_sum, s_min);
         UPD_TRACE(5);
         if (want_rec && tid < 32) {
             if (emit && !term_low) term = s_sum[term_node];
@@ -796,6 +806,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             emit_record_values(s_sum[1], s_min[1], partial, a.rec_len, a.rec_out, a.publish_to, a.n_shards, a.shard_rank,
                                a.publish_to ? __ldcg(a.d_epoch) + 1 : 0);
         }
+        dense_write(a.t, 1, top, s_sum, s_min);
         if (tl_on) tl_stamp(a.tl, 3, 9);
     }
 }
