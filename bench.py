@@ -392,7 +392,7 @@ def main():
     # blocks of GRAPH_STEPS whole steps replayed as ONE CUDA graph, each block followed by one
     # instrumented step whose gather is launched by hand between two timing events (the
     # roofline's per-launch duration comes from those).  Falls back to eager launches if capture fails.
-    GRAPH_STEPS, N_GRAPHS = 15, 4
+    GRAPH_STEPS, N_GRAPHS = 31, 4  # one instrumented step in 32: 62 gather timings in the default 2000 steps
     graphs, head_graphs, launch_mode = None, None, "eager launches"
 
     def capture(body):
