@@ -177,7 +177,7 @@ def reference_arm(args, rank):
 
 def workload_config(n_gpus):
     return {"workload": "Ape-X learner replay step, configs[1]: ring 2^20 Atari transitions per GPU (59.2 GB HBM), "
-                        "batch 512 per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions",
+                        "batch %d per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions" % BATCH,
             "ring_per_gpu": RING, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
             "sharding": "none" if n_gpus == 1 else "one replay of %d x 2^20 transitions cut into %d contiguous slices; "
                         "per step one exchange of a 32-byte record per rank (peer-memory mailboxes written by the sampling kernel over "
@@ -194,6 +194,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling: fix the GLOBAL stratified batch (e.g. 4096) and give every GPU global/N strata "
+                         "(default: 512 strata per GPU, weak scaling, the contract's configuration)")
     ap.add_argument("--timeline", action="store_true",
                     help="diagnostic: after the timed region replay two graph blocks with the kernels' GPU-timer stamps on "
                          "(per_timeline) and print each rank's median step anatomy to stderr")
@@ -229,6 +232,10 @@ def main():
     ring = args.ring
     W = max(args.warmup, 3)
     K = args.steps
+    global BATCH
+    if args.global_batch:
+        assert args.global_batch % world == 0
+        BATCH = args.global_batch // world
     GB = BATCH * world  # global batch: 512 strata per GPU
 
     # ---- build + fill this rank's slice ----------------------------------------------------
@@ -615,7 +622,7 @@ def main():
         achieved = launch_bytes / (gather_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
             "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "roofline": {"bound": "hbm", "kernel": "k_gather_ldg<16>" if os.environ.get("PER_GATHER_MODE", "1") == "1" else "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
