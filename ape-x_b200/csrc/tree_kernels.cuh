@@ -9,7 +9,9 @@
 // arithmetic is IEEE float64 round-to-nearest with explicit __dadd_rn/__dmul_rn so that
 // nvcc cannot contract a*b+c*d into an FMA (memory.py:247 is two products and a sum).
 //
-// This file: range reductions and the stratified descent (K2+K3).  The batched update (K1)
+// This file: range reductions and the stratified descent (K2+K3) in three forms — k_sample (one warp per
+// query, small batches), k_sample_wide (one thread per query, batches >= 2048), k_sample_sharded (one slice of a
+// replay cut over several GPUs, with the record exchange through peer-memory mailboxes).  The batched update (K1)
 // lives in update_kernels.cuh.  Both are latency-bound (a batch of 512 touches ~0.4 MB), so
 // they are written for a short dependent chain and a small instruction footprint (rolled
 // loops, one pow() call site per kernel).

@@ -11,6 +11,10 @@
 //   * lets 16 adjacent lanes share one item: each lane loads 16 B of the two 128-B lines below the item
 //     (one wavefront per 4 items instead of 8 per item) and the 4 generations are reduced
 //     with shuffles, left operand always the lower-numbered child.
+//
+// The update of exactly the sample just drawn (ascending indices, <= 128 items per CTA) takes the SORTED FAST
+// PATH further down instead of the level-synchronous rounds: per-CTA register climb over prefetched siblings,
+// one cluster barrier, border chains in CTA 0 (see the comment in front of SortSmem).
 #pragma once
 #include <cooperative_groups.h>
 
