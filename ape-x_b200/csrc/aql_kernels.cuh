@@ -305,6 +305,13 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
         // ---- CUDA-core side: 256 threads ---------------------------------------------------------
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);  // this warp's 32 TMEM lanes, column 0
         uint32_t it = 0;
+        float act_next[A];  // continuous actions of this thread's row in the tile about to be processed
+        if (CONT) {
+            const int64_t c0 = (int64_t)blockIdx.x * AQL_TILE + r;
+            const float *ap0 = static_cast<const float *>(a.a_mu) + (c0 < a.total ? c0 : a.total - 1) * A;
+#pragma unroll
+            for (int j = 0; j < A; ++j) act_next[j] = ap0[j];
+        }
         if (a.trace && blockIdx.x == 0 && tid == 0) a.trace[6] += (unsigned long long)(clock64() - t_entry);
         for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
             const uint32_t tp = it & 1u;
@@ -325,9 +332,15 @@ __global__ void __launch_bounds__(AQL_THREADS, AQL_CTAS_PER_SM) k_aql_q(const Aq
                 // layer 1 on CUDA cores (K = A): h1 = relu(Wa1 . a + ba1), one 32-column K-atom at a time (16 columns per
                 // thread) into ring slot kb & 1; the issuer starts on an atom as soon as all 256 threads have stored it
                 float act[A];
-                const float *ap = static_cast<const float *>(a.a_mu) + ci * A;
 #pragma unroll
-                for (int j = 0; j < A; ++j) act[j] = ap[j];
+                for (int j = 0; j < A; ++j) act[j] = act_next[j];  // requested one tile ago
+                {   // this row's action of the NEXT tile: its round trip hides behind this tile's three layers
+                    const int64_t cn = (tile + gridDim.x) * AQL_TILE + r;
+                    const int64_t cin = cn < a.total ? cn : a.total - 1;
+                    const float *apn = static_cast<const float *>(a.a_mu) + cin * A;
+#pragma unroll
+                    for (int j = 0; j < A; ++j) act_next[j] = apn[j];
+                }
 #pragma unroll
                 for (int kb = 0; kb < 4; ++kb) {
 #pragma unroll
