@@ -227,7 +227,8 @@ class ShardedReplay(object):
         tensors obs / next_obs / act / rew / done to gather into."""
         assert beta > 0
         u = uniforms if torch.is_tensor(uniforms) else torch.as_tensor(np.asarray(uniforms, dtype=np.float64))
-        u = u.to(self.device, dtype=torch.float64)
+        if u.device != self.device or u.dtype != torch.float64:
+            u = u.to(self.device, dtype=torch.float64)
         sp = _n.stream_ptr()
         if self._peer_exchange:
             recs = None  # the sampling kernel publishes / awaits the records through the mailboxes
@@ -235,9 +236,10 @@ class ShardedReplay(object):
             if not self._rec_fresh:  # inserts since the last update: recompute; otherwise the update left it current
                 _n.check(_n.lib.per_shard_record(self._h, self._len, _n.ptr(self._rec), sp))
             recs = self._exchange(self._rec)
-        idx = torch.empty(batch, dtype=torch.int64, device=self.device)
-        w32 = torch.empty(batch, dtype=torch.float32, device=self.device)
-        w64 = torch.empty(batch, dtype=torch.float64, device=self.device)
+        pre = out or {}  # `out` may also carry preallocated idx / weights / weights64 (a loop that reuses its buffers)
+        idx = pre["idx"] if "idx" in pre else torch.empty(batch, dtype=torch.int64, device=self.device)
+        w32 = pre["weights"] if "weights" in pre else torch.empty(batch, dtype=torch.float32, device=self.device)
+        w64 = pre["weights64"] if "weights64" in pre else torch.empty(batch, dtype=torch.float64, device=self.device)
         _n.check(_n.lib.per_sample_sharded(self._h, _n.ptr(recs), _n.ptr(u), batch, float(beta), self._len, _n.ptr(idx),
                                            _n.ptr(w64), _n.ptr(w32), sp))
         res = {"idx": idx, "weights": w32, "weights64": w64, "records": recs}
@@ -273,12 +275,13 @@ class ShardedReplay(object):
                                           _n.stream_ptr()))
         self._rec_fresh = True
 
-    def td_priority_update(self, q, q_next, q_tgt, actions, rewards, dones, weights, n_steps, gamma, idx):
+    def td_priority_update(self, q, q_next, q_tgt, actions, rewards, dones, weights, n_steps, gamma, idx, out_prio=None,
+                           out_loss=None):
         """utils.py:71-80 over the FULL batch (the 0.9*max term is batch-wide) + the tree update
         of this rank's strata.  All ranks pass the same full-batch tensors."""
         b = int(actions.numel())
-        prio = torch.empty(b, dtype=torch.float32, device=self.device)
-        loss = torch.empty(1, dtype=torch.float32, device=self.device)
+        prio = out_prio if out_prio is not None else torch.empty(b, dtype=torch.float32, device=self.device)
+        loss = out_loss if out_loss is not None else torch.empty(1, dtype=torch.float32, device=self.device)
         gamma_n = float(np.float32(gamma ** n_steps))
         _n.check(_n.lib.per_td_priority_update(self._h, _n.ptr(q), _n.ptr(q_next), _n.ptr(q_tgt), int(q.shape[1]),
                                                _n.ptr(actions), _n.ptr(rewards), _n.ptr(dones), _n.ptr(weights), gamma_n,

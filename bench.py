@@ -583,14 +583,17 @@ def main():
         # them, the step's result (loss + the batch's new priorities) is read back to the host
         u_host = [torch.rand(GB, dtype=torch.float64, generator=torch.Generator().manual_seed(i)).pin_memory() for i in range(8)]
         res_host = torch.empty(GB + 1, dtype=torch.float32).pin_memory()
-        outbuf = {"obs": o_obs, "next_obs": o_nxt, "act": o_act, "rew": o_rew, "done": o_done}
+        outbuf = {"obs": o_obs, "next_obs": o_nxt, "act": o_act, "rew": o_rew, "done": o_done,
+                  "idx": idx, "weights": w32, "weights64": torch.empty(GB, dtype=torch.float64, device=dev)}
+        u_dev = torch.empty(GB, dtype=torch.float64, device=dev)
+        o_res = torch.empty(GB + 1, dtype=torch.float32, device=dev)  # priorities | loss: one read-back per step
 
         def e2e_step(i):
-            u_dev = u_host[i % 8].to(dev, non_blocking=True)
+            u_dev.copy_(u_host[i % 8], non_blocking=True)
             d = shard.sample_device(GB, BETA, u_dev, gather=True, out=outbuf)
-            loss, prio = shard.td_priority_update(q, qn, qt, t_act, t_rew, t_done, t_w, N_STEP, GAMMA, d["idx"])
-            res_host[:GB].copy_(prio, non_blocking=True)
-            res_host[GB:].copy_(loss, non_blocking=True)
+            loss, prio = shard.td_priority_update(q, qn, qt, t_act, t_rew, t_done, t_w, N_STEP, GAMMA, d["idx"],
+                                                  out_prio=o_res[:GB], out_loss=o_res[GB:])
+            res_host.copy_(o_res, non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
         for i in range(3):
