@@ -24,15 +24,19 @@ namespace perb {
 constexpr int GATHER_MAX_WARPS = 16;    // independent copy engines per CTA (upper bound)
 constexpr int GATHER_SMEM_MAX = 200 * 1024;
 
-// Launch shape of the TMA gather; defaults chosen by the sweep in profiles/ (see DESIGN.md).
+// Launch shape of the gather; defaults chosen by the sweeps in profiles/ (see DESIGN.md section 3).
 struct GatherTune {
-    int mode = 1;        // 0: TMA bulk copies through shared memory, 1: LDG.128/STG.128 through registers (see DESIGN.md section 3:
-                         // alone the two run the same 12.3 us; inside the chained step the register-staged one is 2.4 us
-                         // ahead because the TMA variant's 226 KB/SM of dynamic shared memory slows the kernels around it)
-    int warps = 4;       // issuing warps per CTA
-    int stages = 2;      // pieces in flight per warp
-    int piece = 7056;    // bytes per piece (multiple of 16); 7056 = one 84x84 frame
-    int ctas_per_sm = 4; // 4 x (4 x 2 x 7056 B) = 226 KB of shared memory per SM
+    int mode = 2;        // 0: TMA bulk copies through shared memory (k_gather_tma), 1: one piece per warp through registers
+                         // (k_gather_ldg), 2: balanced shares through registers (k_gather_bal; profiles/r02_gather_sweep.txt)
+    int warps = 4;       // mode 0: issuing warps per CTA
+    int stages = 2;      // mode 0: pieces in flight per warp
+    int piece = 7056;    // modes 0/1: bytes per piece (multiple of 16); 7056 = one 84x84 frame
+    int ctas_per_sm = 4; // CTAs per SM at most (mode 0: 4 x (4 x 2 x 7056 B) = 226 KB of shared memory per SM; mode 2: the
+                         // kernel's own occupancy caps it, 3 at depth 8)
+    int depth = 8;       // mode 2: vectors per lane and stage
+    int pipe = 0;        // mode 2: 1 = the next stage's loads go out before this stage's stores (costs registers, hence CTAs per SM:
+                         // measured slower at every depth)
+    int vbytes = 16;     // mode 2: bytes per vector (16: LDG.128, 32: LDG.256 with L2 eviction hints)
 };
 
 struct RowClass {
@@ -270,6 +274,142 @@ __global__ void __launch_bounds__(256, DEPTH <= 8 ? 4 : 2) k_gather_ldg(GatherAr
             for (int j = 0; j < DEPTH; ++j) {
                 int e = base + j * 32 + lane;
                 if (e < nv) st_stream(dst + e, v[j]);
+            }
+        }
+    }
+    if (tl_on) tl_stamp(a.tl, 2, 6);
+    if (a.tl && lane == 0) {  // timeline on: the latest finish over all warps of the grid (diagnostic runs only)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicMax(a.tl + 3, (13ull << 56) | (t & ((1ull << 56) - 1)));
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Balanced register-staged mover (gather_mode 2).  The batch is one linear space of VB-byte vectors
+// (query-major: obs row, next_obs row, extra row) that is cut into equal contiguous shares, one per warp
+// of a grid sized to exactly the resident CTA slots (ctas_per_sm x SMs): no wave tail — with one 7 056-byte
+// piece per warp the 4 096 pieces of a 512-row batch make 1.73 waves of the 296 slots — and every warp
+// finishes together.  A warp walks its share in stages of 32 x DEPTH vectors; with PIPE the loads of stage
+// s+1 are issued before the stores of stage s, so a warp always has loads in flight.
+// VB = 16: LDG.128 / STG.128.  VB = 32: LDG.256 / STG.256 (sm_100), which is also the only form that takes the
+// L2 eviction-priority hints: rows are read once (evict_first), the batch is re-read by the learner (evict_last).
+// ---------------------------------------------------------------------------------------
+template <int VB> struct GVec;
+template <> struct GVec<16> { int4 a; };
+template <> struct GVec<32> { int4 a, b; };
+
+__device__ __forceinline__ void gv_load(GVec<16> &v, const uint8_t *p) { v.a = ld_stream(reinterpret_cast<const int4 *>(p)); }
+__device__ __forceinline__ void gv_store(uint8_t *p, const GVec<16> &v) { st_stream(reinterpret_cast<int4 *>(p), v.a); }
+__device__ __forceinline__ void gv_load(GVec<32> &v, const uint8_t *p) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v.a.x), "=r"(v.a.y), "=r"(v.a.z), "=r"(v.a.w), "=r"(v.b.x), "=r"(v.b.y), "=r"(v.b.z), "=r"(v.b.w)
+                 : "l"(p));
+}
+__device__ __forceinline__ void gv_store(uint8_t *p, const GVec<32> &v) {
+    asm volatile("st.global.L1::no_allocate.L2::evict_last.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(v.a.x),
+                 "r"(v.a.y), "r"(v.a.z), "r"(v.a.w), "r"(v.b.x), "r"(v.b.y), "r"(v.b.z), "r"(v.b.w)
+                 : "memory");
+}
+
+// Position of one lane inside the linear vector space: query q, vector r of the query's V vectors, and the
+// ring row k of that query (-1: not this shard's row, nothing to move).
+struct VecCursor {
+    int64_t q;
+    int r;
+    int64_t k;
+};
+__device__ __forceinline__ int64_t gather_row_of(const GatherArgs &a, int64_t q) {
+    int64_t k = a.idx[q];
+    if (a.skip_foreign && k == -1) return -1;
+    k -= a.idx_base;
+    return (k < 0 || k >= a.n_rows) ? 0 : k;  // flagged by the scalar pass; keep the copy in bounds
+}
+
+template <int VB, int DEPTH>
+struct GatherStage {
+    GVec<VB> v[DEPTH];
+    uint8_t *dst[DEPTH];  // null: nothing to store
+};
+
+// Loads the next DEPTH vectors of this lane (vectors g, g + 32, ...), advancing the cursor.
+template <int VB, int DEPTH>
+__device__ __forceinline__ void gather_stage_load(const GatherArgs &a, GatherStage<VB, DEPTH> &st, VecCursor &c, int64_t &g,
+                                                  const int64_t end, const int64_t last_q, const int v0, const int v01, const int V) {
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j) {
+        st.dst[j] = nullptr;
+        if (g < end) {
+            if (c.k >= 0) {
+                const int cls = c.r < v0 ? 0 : (c.r < v01 ? 1 : 2);
+                const int o = c.r - (cls == 0 ? 0 : (cls == 1 ? v0 : v01));
+                const RowClass &rc = a.rc[cls];
+                gv_load(st.v[j], rc.src + c.k * rc.src_stride + (int64_t)o * VB);
+                st.dst[j] = rc.dst + c.q * rc.dst_stride + (int64_t)o * VB;
+            }
+            g += 32;
+            c.r += 32;
+            if (c.r >= V) {
+                do {
+                    c.r -= V;
+                    ++c.q;
+                } while (c.r >= V);
+                c.k = c.q < last_q ? gather_row_of(a, c.q) : -1;
+            }
+        }
+    }
+}
+template <int VB, int DEPTH>
+__device__ __forceinline__ void gather_stage_store(const GatherStage<VB, DEPTH> &st) {
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j)
+        if (st.dst[j]) gv_store(st.dst[j], st.v[j]);
+}
+
+template <int VB, int DEPTH, bool PIPE>
+__global__ void __launch_bounds__(256) k_gather_bal(GatherArgs a, int v0, int v1, int v2) {
+    const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
+    if (tl_on) tl_stamp(a.tl, 0, 4);
+    pdl_launch_dependents();
+    pdl_wait();  // indices and range tags come from the sampling kernel in front of this one
+    if (tl_on) tl_stamp(a.tl, 1, 5);
+    int64_t first_q, last_q;
+    gather_range(a, first_q, last_q);
+    gather_scalars(a, first_q, last_q);
+    const int V = v0 + v1 + v2, v01 = v0 + v1;
+    if (V == 0) return;
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t w = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t total = (last_q - first_q) * V;
+    const int64_t share = (((total + warps - 1) / warps) + 31) & ~int64_t(31);  // whole warp-rows of 32 vectors
+    const int64_t start = w * share;
+    const int64_t end = start + share < total ? start + share : total;
+    int64_t g = start + lane;
+    if (start < end) {
+        VecCursor c;
+        c.q = g / V;
+        c.r = (int)(g - c.q * V);
+        c.q += first_q;
+        c.k = (g < end) ? gather_row_of(a, c.q) : -1;
+        if (PIPE) {
+            GatherStage<VB, DEPTH> s0, s1;
+            gather_stage_load(a, s0, c, g, end, last_q, v0, v01, V);
+            while (true) {
+                const bool more1 = __any_sync(0xffffffffu, g < end);
+                if (more1) gather_stage_load(a, s1, c, g, end, last_q, v0, v01, V);
+                gather_stage_store(s0);
+                if (!more1) break;
+                const bool more0 = __any_sync(0xffffffffu, g < end);
+                if (more0) gather_stage_load(a, s0, c, g, end, last_q, v0, v01, V);
+                gather_stage_store(s1);
+                if (!more0) break;
+            }
+        } else {
+            while (__any_sync(0xffffffffu, g < end)) {
+                GatherStage<VB, DEPTH> s0;
+                gather_stage_load(a, s0, c, g, end, last_q, v0, v01, V);
+                gather_stage_store(s0);
             }
         }
     }

@@ -765,7 +765,44 @@ int per_gather(per_buffer *b, const int64_t *d_idx, int64_t batch, void *d_out_o
     a.stages = slow.stages = tn.stages;
     a.tl = b->tl_next();
     const int64_t items = batch * per_query;
-    if (tn.mode == 0) {
+    if (tn.mode == 2) {
+        // balanced mover: vectors of VB bytes per class (classes that cannot be cut into them stay with the slow mover)
+        int vb = tn.vbytes;
+        for (int c = 0; c < 3; ++c)
+            if (a.rc[c].dst && (rb[c] % 32 || ss[c] % 32 || ((uintptr_t)a.rc[c].dst) % 32 || ((uintptr_t)a.rc[c].src) % 32)) vb = 16;
+        int v[3];
+        for (int c = 0; c < 3; ++c) v[c] = a.rc[c].dst ? (int)(rb[c] / vb) : 0;
+        const int64_t vecs = batch * ((int64_t)v[0] + v[1] + v[2]);
+        int64_t grid = (int64_t)b->sm_count * tn.ctas_per_sm;
+        const int64_t enough = (vecs + 8 * 32 * 4 - 1) / (8 * 32 * 4);  // at least four vectors per lane
+        if (grid > enough) grid = enough;
+        if (grid < 1) grid = 1;
+        const bool pdl = (b->pdl & 2) != 0;
+        // the grid is exactly the CTA slots this instantiation gets (its register count decides; asked once per shape)
+#define BAL_LAUNCH(VB, D, P)                                                                                              \
+    do {                                                                                                                 \
+        static int occ = 0;                                                                                              \
+        if (!occ) PER_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_gather_bal<VB, D, P>, 256, 0));         \
+        const int64_t slots = (int64_t)b->sm_count * (occ < tn.ctas_per_sm ? occ : tn.ctas_per_sm);                      \
+        if (grid > slots) grid = slots;                                                                                  \
+        PER_CUDA(launch_pdl(k_gather_bal<VB, D, P>, dim3((unsigned)grid), dim3(256), 0, s, pdl, a, v[0], v[1], v[2]));   \
+    } while (0)
+#define BAL_DEPTHS(VB, D0, D1, D2, D3)                                                   \
+    do {                                                                                 \
+        const int d = tn.depth;                                                          \
+        if (tn.pipe) {                                                                   \
+            if (d <= D0) BAL_LAUNCH(VB, D0, true); else if (d <= D1) BAL_LAUNCH(VB, D1, true); \
+            else if (d <= D2) BAL_LAUNCH(VB, D2, true); else BAL_LAUNCH(VB, D3, true);   \
+        } else {                                                                         \
+            if (d <= D0) BAL_LAUNCH(VB, D0, false); else if (d <= D1) BAL_LAUNCH(VB, D1, false); \
+            else if (d <= D2) BAL_LAUNCH(VB, D2, false); else BAL_LAUNCH(VB, D3, false); \
+        }                                                                                \
+    } while (0)
+        if (vb == 32) BAL_DEPTHS(32, 2, 4, 6, 8);
+        else BAL_DEPTHS(16, 4, 8, 12, 16);
+#undef BAL_DEPTHS
+#undef BAL_LAUNCH
+    } else if (tn.mode == 0) {
         int64_t grid = (items + tn.warps - 1) / tn.warps;
         if (grid > (int64_t)b->sm_count * tn.ctas_per_sm) grid = (int64_t)b->sm_count * tn.ctas_per_sm;  // persistent CTAs
         if (grid < 1) grid = 1;
@@ -865,13 +902,16 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         return PER_OK;
     }
     if (!strcmp(key, "gather_mode")) t.mode = (int)value;
+    else if (!strcmp(key, "gather_depth")) t.depth = (int)value;
+    else if (!strcmp(key, "gather_pipe")) t.pipe = value != 0;
+    else if (!strcmp(key, "gather_vbytes")) t.vbytes = (int)value;
     else if (!strcmp(key, "gather_warps")) t.warps = (int)value;
     else if (!strcmp(key, "gather_stages")) t.stages = (int)value;
     else if (!strcmp(key, "gather_piece")) t.piece = (int)value;
     else if (!strcmp(key, "gather_ctas_per_sm")) t.ctas_per_sm = (int)value;
     else return fail(PER_ERR_ARG, "per_tune: unknown key %s", key);
     const int64_t smem = round_up(t.warps * t.stages * 8, 128) + (int64_t)t.warps * t.stages * t.piece;
-    if (t.mode < 0 || t.mode > 1 || t.warps < 1 || t.warps > GATHER_MAX_WARPS || t.stages < 2 || t.stages > 64 ||
+    if (t.mode < 0 || t.mode > 2 || t.depth < 1 || t.depth > 16 || (t.vbytes != 16 && t.vbytes != 32) || t.warps < 1 || t.warps > GATHER_MAX_WARPS || t.stages < 2 || t.stages > 64 ||
         t.piece < 16 || t.piece % 16 || t.ctas_per_sm < 1 || t.ctas_per_sm > 8 || smem > GATHER_SMEM_MAX ||
         (t.mode == 0 && (smem + 1024) * t.ctas_per_sm > 228 * 1024))
         return fail(PER_ERR_ARG, "per_tune: %s=%lld gives an invalid launch shape (smem %lld B x %d CTAs/SM)", key,

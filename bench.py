@@ -7,8 +7,11 @@ weights + frame gather) -> TD-error -> priority -> tree update, per batch.
 Prints ONE JSON line (rank 0).  `value` = transitions sampled+updated per second over all
 ranks with every input resident in HBM; `e2e` = the same loop through the reference-facing
 Python API (memory.py: sample() -> host numpy, update_priorities(host arrays)), host<->device
-copies inside the timed region; `roofline` = the frame-gather kernel (the HBM-bound one)
-timed with CUDA events around each of its launches inside the timed region;
+copies inside the timed region; `roofline` = the frame-gather kernel (the HBM-bound one): one
+CUDA-event pair around a graph of 16 of its launches, each on its own freshly sampled index set,
+run right after the timed region (an event between two kernels of the step would break their
+chaining, so the timed region itself carries none); `roofline_tree`, `aql`, `learner_updates_per_s`:
+the other measurement rows of SURVEY.md section 8(d);
 `cpu_baseline` = the oracle port of the reference's Python path on this box's host cores.
 
 Workload (BASELINE.json configs[1], SURVEY.md §8d "C2"): ring of 2^20 Atari transitions
@@ -38,14 +41,24 @@ OBS_SHAPE = (4, 84, 84)
 OBS_BYTES = 4 * 84 * 84
 N_ACTIONS = 18
 ALPHA, BETA, N_STEP, GAMMA = 0.6, 0.4, 3, 0.99
+DEFAULT_GATHER_MODE = 2  # per_tune "gather_mode" the library ships with (csrc/gather_kernels.cuh GatherTune)
 METRIC = "PER sample+update transitions/s"
 UNIT = "transitions/s"
 # per sampled transition the gather reads 2*28224 B of frames + 16 B of
 # scalars and writes the same.
 GATHER_BYTES_PER_ROW = 2 * (2 * OBS_BYTES + 16)
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_gather_ldg<16> launch at this workload, from the
-# ncu --set full capture summarised in profiles/r01e_ncu_summary.csv (the 28.9 MB written stay in the 126 MB L2)
-NCU_GATHER_TRAFFIC = 29224192 + 315392
+
+
+def ncu_gather_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one gather launch at this workload, from the newest
+    profiles/r*_gather_traffic.json (written by tools/summarize_ncu.py from an `ncu --set full` capture of
+    this very command); None when no capture of the current kernel is on file."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_gather_traffic.json")))
+    if not files:
+        return None, None
+    d = json.load(open(files[-1]))
+    return d.get("dram_bytes_per_launch"), d.get("kernel")
 
 
 def peaks():
@@ -116,6 +129,7 @@ def build_cpu_port(ring, seed=0):
     from oracle import per_oracle as po
     rng = np.random.default_rng(seed)
     buf = po.ReplayOracle(ring, ALPHA, "apex")
+    buf.lists_like_reference = True  # CustomPrioritizedReplayBuffer._encode_sample (memory.py:348-362): lists of references, no frame copy
     pool = rng.integers(0, 256, size=(256,) + OBS_SHAPE, dtype=np.uint8)
     prio = np.abs(rng.standard_normal(ring)) + 1e-6
     leaves = prio ** ALPHA
@@ -130,28 +144,32 @@ def build_cpu_port(ring, seed=0):
     return buf
 
 
-def cpu_step(buf, rng):
+def cpu_step(buf, rng, batch=None):
     """One reference learner-side replay step: sample(B, beta) then update_priorities."""
-    u = rng.random(BATCH)
-    out = buf.sample(BATCH, BETA, u)
-    pr = np.abs(rng.standard_normal(BATCH)) + 1e-6
+    batch = batch or BATCH
+    u = rng.random(batch)
+    out = buf.sample(batch, BETA, u)
+    pr = np.abs(rng.standard_normal(batch)) + 1e-6
     buf.update_priorities(out[-1], [float(p) for p in pr])
 
 
-def run_cpu_baseline(steps, warmup, budget_s=None):
-    buf = build_cpu_port(RING)
+def run_cpu_baseline(steps, warmup, budget_s=None, n_gpus=1):
+    """The reference's single tree and single process hold the WHOLE replay of the n_gpus configuration:
+    n_gpus x 2^20 transitions, global batch n_gpus x 512."""
+    buf = build_cpu_port(RING * n_gpus)
+    batch = BATCH * n_gpus
     rng = np.random.default_rng(1)
     for _ in range(warmup):
-        cpu_step(buf, rng)
+        cpu_step(buf, rng, batch)
     t0 = time.perf_counter()
     done = 0
     for _ in range(steps):
-        cpu_step(buf, rng)
+        cpu_step(buf, rng, batch)
         done += 1
         if budget_s is not None and time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
-    return done * BATCH / dt, done, dt
+    return done * batch / dt, done, dt
 
 
 def reference_arm(args, rank):
@@ -159,17 +177,20 @@ def reference_arm(args, rank):
     Python lists, like memory.py — it is serial, so 1 core) on the same config and metric."""
     if rank != 0:
         return
-    steps = min(args.steps, 400)  # ~25 ms per step; keeps the run within minutes
-    value, done, dt = run_cpu_baseline(steps, min(args.warmup, 5))
+    n = max(1, args.gpus)
+    steps = min(args.steps, 400)  # ~10-70 ms per step; keeps the run within minutes
+    value, done, dt = run_cpu_baseline(steps, min(args.warmup, 5), budget_s=120.0, n_gpus=n)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
         "steps": done, "warmup": min(args.warmup, 5), "ms_per_step": 1e3 * dt / max(done, 1),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(1),
+        "config": workload_config(n),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
-                         "sample": "%d steps of sample(512)+update_priorities(512) on a 2^20-leaf tree, "
-                                   "oracle/per_oracle.py ReplayOracle (pure Python like memory.py), "
-                                   "host has %d cores" % (done, os.cpu_count())},
+                         "sample": "%d steps of sample(%d)+update_priorities(%d) on one 2^%d-leaf tree pair (the reference "
+                                   "keeps the whole replay in one process), oracle/per_oracle.py ReplayOracle with "
+                                   "CustomPrioritizedReplayBuffer semantics (pure Python like memory.py; observations returned "
+                                   "as lists of references, memory.py:348-362), host has %d cores"
+                                   % (done, BATCH * n, BATCH * n, int(np.log2(RING * n)), os.cpu_count())},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -185,6 +206,136 @@ def workload_config(n_gpus):
             "l2": "inputs (59 GB ring) larger than L2; no flush", "parallelism": "shard%d" % n_gpus}
 
 
+# ------------------------------------------------------------- extra rows of SURVEY 8(d), N = 1
+def _event_us(torch, fn, iters):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / iters
+
+
+def aql_row(dev):
+    """BASELINE configs[2] (C3): AQL candidate-Q + argmax at B=256, K=1000, one continuous action dim —
+    the fused tcgen05 kernel (aql.CandidateQ) against the stock PyTorch float32 ops the reference runs for
+    the same arithmetic (model.py:294-335: action MLP, repeat + concat, 128->64->1, argmax) on this GPU."""
+    import torch
+    import torch.nn.functional as F
+
+    import aql
+    B, K, A, OBS = 256, 1000, 1, 24
+    g = torch.Generator(device=dev).manual_seed(7)
+    r = lambda *shape: torch.randn(*shape, device=dev, generator=g)
+    wa1, ba1, wa2, ba2 = r(128, A) * 0.5, r(128) * 0.1, r(64, 128) * 0.09, r(64) * 0.1
+    wadv1, badv1, wadv2, badv2 = r(64, 128) * 0.09, r(64) * 0.1, r(1, 64) * 0.12, r(1) * 0.1
+    f = torch.relu(r(B, 64))
+    a_mu = torch.rand(B, K, A, device=dev, generator=g) * 2 - 1
+    was_tf32 = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+    def stock():
+        a_out = F.relu(F.linear(F.relu(F.linear(a_mu.reshape(-1, A), wa1, ba1)), wa2, ba2)).reshape(-1, K, 64)
+        q_f = f.repeat(1, K).reshape(-1, K, 64)
+        x = F.relu(torch.cat([a_out, q_f], dim=2)).reshape(-1, 128)
+        q = F.linear(F.relu(F.linear(x, wadv1, badv1)), wadv2, badv2).reshape(B, K)
+        return q, q.argmax(1)
+
+    cq = aql.CandidateQ(True, A)
+    cq.set_weights(wa1, ba1, wa2, ba2, wadv1, badv1, wadv2, badv2)
+    with torch.no_grad():
+        q_ref, am_ref = stock()
+        q_got, am_got = cq.forward(f, a_mu)
+        err = float((q_got - q_ref).abs().max()) / max(float(q_ref.abs().max()), 1.0)
+        t_stock = _event_us(torch, stock, 20)
+        t_ours = _event_us(torch, lambda: cq.forward(f, a_mu), 50)
+    torch.backends.cuda.matmul.allow_tf32 = was_tf32
+    flop = 2 * B * K * (A * 128 + 128 * 64 + 64 * 64 + 64) + 2 * B * 64 * 64
+    pipe = None
+    try:
+        import glob
+        files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_aql_tensor_pipe.json")))
+        if files:
+            pipe = json.load(open(files[-1]))
+    except Exception:
+        pass
+    return {"workload": "AQL candidate-Q + argmax, B=256, K=1000, A=1 (BASELINE configs[2])", "fused_us": t_ours,
+            "stock_pytorch_fp32_us": t_stock, "speedup": t_stock / t_ours, "gflop_per_forward": flop / 1e9,
+            "tflops_fp32_equivalent": flop / t_ours / 1e6, "max_rel_err_vs_stock": err,
+            "argmax_agree": float((am_got == am_ref).float().mean()),
+            "tensor_pipe_from_ncu": pipe, "timing": "CUDA events around 50 forwards (3 chained launches each), plain launches"}
+
+
+def learner_row(buf, dev):
+    """BASELINE's second metric, Ape-X learner updates/s (ApeX.py:43-82) at configs[1]: the reference's dueling
+    Nature-CNN DQN as plain PyTorch fp32 (out of scope), batch 512, n-step 3, double-Q, RMSprop,
+    fed by this replay without leaving the GPU: sample_device (gather fused with the uint8 -> float32 widening) ->
+    3 forwards + backward + optimiser step -> td_priority_update."""
+    import torch
+    import torch.nn as nn
+
+    class Dueling(nn.Module):  # model.py:14-66
+        def __init__(self):
+            super().__init__()
+            self.features = nn.Sequential(nn.Conv2d(4, 32, 8, 4), nn.ReLU(), nn.Conv2d(32, 64, 4, 2), nn.ReLU(),
+                                          nn.Conv2d(64, 64, 3, 1), nn.ReLU(), nn.Flatten())
+            self.advantage = nn.Sequential(nn.Linear(3136, 128), nn.ReLU(), nn.Linear(128, N_ACTIONS))
+            self.value = nn.Sequential(nn.Linear(3136, 128), nn.ReLU(), nn.Linear(128, 1))
+
+        def forward(self, x):
+            f = self.features(x)
+            a = self.advantage(f)
+            return self.value(f) + a - a.mean(1, keepdim=True)
+
+    torch.manual_seed(0)
+    model, tgt = Dueling().to(dev), Dueling().to(dev)
+    tgt.load_state_dict(model.state_dict())
+    opt = torch.optim.RMSprop(model.parameters(), 6.25e-5, alpha=0.95, eps=1.5e-7, centered=True)
+    B = 512
+
+    def net(d):
+        q, qn = model(d["obs"]), model(d["next_obs"])
+        with torch.no_grad():
+            qt = tgt(d["next_obs"])
+        q_a = q.gather(1, d["act"].unsqueeze(1)).squeeze(1)
+        nxt = qt.gather(1, qn.max(1)[1].unsqueeze(1)).squeeze(1)
+        td = torch.abs((d["rew"] + (GAMMA ** N_STEP) * nxt * (1 - d["done"])).detach() - q_a)
+        loss = (torch.where(td < 1, 0.5 * td ** 2, td - 0.5) * d["weights"]).mean()
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 40)
+        opt.step()
+        return q.detach(), qn.detach(), qt
+
+    def step():
+        d = buf.sample_device(B, BETA, obs_dtype=torch.float32)
+        q, qn, qt = net(d)
+        buf.td_priority_update(q, qn, qt, d["act"], d["rew"], d["done"], d["weights"], N_STEP, GAMMA, idx=d["idx"], want_loss=False)
+
+    def wall(fn, n):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn()
+        torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / n
+
+    t_step = wall(step, 20)
+    d0 = buf.sample_device(B, BETA, obs_dtype=torch.float32)
+    t_net = wall(lambda: net(d0), 20)
+    return {"value": 1.0 / t_step, "unit": "learner updates/s", "ms_per_update": t_step * 1e3,
+            "network_alone_ms": t_net * 1e3, "replay_share": max(0.0, 1.0 - t_net / t_step),
+            "workload": "ApeX.py:43-82 at configs[1]: dueling Nature-CNN DQN (PyTorch fp32), batch 512, n-step 3, "
+                        "double-Q, RMSprop; replay on the device path (sample_device + td_priority_update)",
+            "timing": "wall clock over 20 learner steps, synchronised"}
+
+
 # ------------------------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -194,6 +345,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the AQL and whole-learner-step rows (N=1)")
     ap.add_argument("--global-batch", type=int, default=0,
                     help="strong scaling: fix the GLOBAL stratified batch (e.g. 4096) and give every GPU global/N strata "
                          "(default: 512 strata per GPU, weak scaling, the contract's configuration)")
@@ -266,12 +418,14 @@ def main():
     del obs, nxt
     if shard is not None:
         shard.set_global_len(world * ring, 0)
-    if os.environ.get("PER_GATHER_MODE") is not None:  # experiment: 1 = register-staged gather, no shared memory
+    if os.environ.get("PER_GATHER_MODE") is not None:  # experiments: 0 TMA rings, 1 one piece per warp, 2 balanced shares
         hh = buf._h if world == 1 else shard._h
         pn.check(pn.lib.per_tune(hh, b"gather_mode", int(os.environ["PER_GATHER_MODE"])))
-        pn.check(pn.lib.per_tune(hh, b"gather_ctas_per_sm", int(os.environ.get("PER_GATHER_CTAS", "2"))))
-        if os.environ.get("PER_GATHER_PIECE"):
-            pn.check(pn.lib.per_tune(hh, b"gather_piece", int(os.environ["PER_GATHER_PIECE"])))
+        for env, key in (("PER_GATHER_CTAS", b"gather_ctas_per_sm"), ("PER_GATHER_PIECE", b"gather_piece"),
+                         ("PER_GATHER_DEPTH", b"gather_depth"), ("PER_GATHER_PIPE", b"gather_pipe"),
+                         ("PER_GATHER_VBYTES", b"gather_vbytes")):
+            if os.environ.get(env):
+                pn.check(pn.lib.per_tune(hh, key, int(os.environ[env])))
     if os.environ.get("PER_SORTED_UPDATE") is not None:
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"sorted_update", int(os.environ["PER_SORTED_UPDATE"])))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)
@@ -395,12 +549,13 @@ def main():
                          % (rank, tr[0], tr[1], tr[2], int((idx >= 0).sum().item())))
 
     # ---- CUDA graphs for the launch-bound loop ----------------------------------------------
-    # The step is four small launches, so plain Python launches are CPU-bound.  Timed region =
-    # blocks of GRAPH_STEPS whole steps replayed as ONE CUDA graph, each block followed by one
-    # instrumented step whose gather is launched by hand between two timing events (the
-    # roofline's per-launch duration comes from those).  Falls back to eager launches if capture fails.
-    GRAPH_STEPS, N_GRAPHS = 31, 4  # one instrumented step in 32: 62 gather timings in the default 2000 steps
-    graphs, head_graphs, launch_mode = None, None, "eager launches"
+    # The step is three small launches, so plain Python launches are CPU-bound.  Timed region = the K steps
+    # replayed as CUDA graphs of G = min(31, K) whole steps each (plus one graph with the K mod G left-over
+    # steps): exactly K steps, 3 K launches, nothing else on the stream.  Falls back to eager launches if capture fails.
+    GRAPH_STEPS_MAX, N_GRAPHS = 31, 4
+    G = max(1, min(GRAPH_STEPS_MAX, K))
+    n_full, rem = K // G, K % G
+    graphs, tail_graph, launch_mode = None, None, "eager launches (one Python call per kernel)"
 
     def capture(body):
         g = torch.cuda.CUDAGraph()
@@ -417,95 +572,142 @@ def main():
         if rc:
             pn.check(rc)
 
+    def full_block(base, n, sps):
+        for t in range(n):
+            enqueue_head(base + t, sps)
+            rc = lib.per_gather(*(a_gather[:-1] + (sps,)))
+            if rc:
+                pn.check(rc)
+
+    def draw_batch():  # the graphs run a step as [TD + update of the previous batch, sample, gather]
+        if use_mailbox:
+            pn.check(lib.per_sample_sharded(h, None, u_ptrs[0], GB, BETA, glen, a_idx, None, a_w32, sp))
+        else:
+            pn.check(lib.per_sample_indices(h, u_ptrs[0], GB, BETA, a_idx, None, a_w32, sp))
+        pn.check(lib.per_gather(*a_gather))
+
     # (capturing torch's NCCL all-gather inside a graph hung on 2 GPUs in round 1; with the mailbox exchange the
     # step is kernels only, so world > 1 is captured too)
+    side = torch.cuda.Stream()
     if not args.eager and (world == 1 or use_mailbox):
         try:
-            # the graphs run a step as [TD + update of the previous batch, sample, gather]; the warm-up ended with
-            # an update, so draw one batch first (with early publish two updates in a row are refused)
-            if use_mailbox:
-                pn.check(lib.per_sample_sharded(h, None, u_ptrs[0], GB, BETA, glen, a_idx, None, a_w32, sp))
-            else:
-                pn.check(lib.per_sample_indices(h, u_ptrs[0], GB, BETA, a_idx, None, a_w32, sp))
-            pn.check(lib.per_gather(*a_gather))
-            side = torch.cuda.Stream()
+            # the warm-up ended with an update, so draw one batch first (with early publish two updates in a row are refused)
+            draw_batch()
             side.wait_stream(stream)
             with torch.cuda.stream(side):
                 sp_side = pn.stream_ptr(side)
-
-                def full_block(base):
-                    for t in range(GRAPH_STEPS):
-                        enqueue_head(base + t, sp_side)
-                        rc = lib.per_gather(*(a_gather[:-1] + (sp_side,)))
-                        if rc:
-                            pn.check(rc)
-
-                built = [capture(lambda j=j: full_block(j * GRAPH_STEPS)) for j in range(N_GRAPHS)]
-                heads = [capture(lambda j=j: enqueue_head(N_GRAPHS * GRAPH_STEPS + j, sp_side)) for j in range(N_GRAPHS)]
+                built = [capture(lambda j=j: full_block(j * G, G, sp_side)) for j in range(min(N_GRAPHS, n_full))]
+                tail = capture(lambda: full_block(N_GRAPHS * G, rem, sp_side)) if rem else None
             stream.wait_stream(side)
             torch.cuda.synchronize()
-            graphs, head_graphs = built, heads
-            launch_mode = ("cuda graphs: blocks of %d whole steps per graph + 1 instrumented step "
-                           "(gather launched between timing events)" % GRAPH_STEPS)
+            graphs, tail_graph = built, tail
+            launch_mode = ("cuda graphs: %d replay(s) of a %d-step graph%s; a step = TD+update of the previous batch, sample, "
+                           "gather (3 launches)" % (n_full, G, (" + one %d-step graph" % rem) if rem else ""))
         except Exception as exc:
             sys.stderr.write("graph capture failed, timing eager launches: %s\n" % str(exc)[:300])
             graphs = None
 
     def timed(n_steps, use_graphs):
-        """Runs exactly n_steps steps; returns (ms over all ranks, mean ms of the instrumented gather launches)."""
-        evs = []
+        """Runs exactly n_steps steps; returns ms (max over ranks)."""
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         t0.record(stream)
         if use_graphs:
-            done, blk = 0, 0
-            while done < n_steps:
-                if n_steps - done > GRAPH_STEPS:
-                    graphs[blk % N_GRAPHS].replay()
-                    done += GRAPH_STEPS
-                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-                head_graphs[blk % N_GRAPHS].replay()
-                ev[0].record(stream)
-                rc = lib.per_gather(*a_gather)
-                ev[1].record(stream)
-                if rc:
-                    pn.check(rc)
-                evs.append(ev)
-                done += 1
-                blk += 1
+            assert n_steps == K
+            for b_ in range(n_full):
+                graphs[b_ % len(graphs)].replay()
+            if tail_graph is not None:
+                tail_graph.replay()
         else:
             for i in range(n_steps):
-                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-                step(W + i, ev)
-                evs.append(ev)
+                step(W + i)
         t1.record(stream)
         barrier()
-        return max_over_ranks(t0.elapsed_time(t1)), float(np.mean([x.elapsed_time(y) for x, y in evs]))
+        return max_over_ranks(t0.elapsed_time(t1))
 
-    if graphs is not None:
-        timed(min(K, 64), True)  # warm the graphs
-    # ---- timed region: K steps, CUDA events on the launching stream --------------------------
-    sampler = ClockSampler(local_rank)
+    # clocks / throttle reasons are sampled from the graph warm-up to the end of the roofline pass (the timed region
+    # itself can be shorter than one NVML sample at small K)
+    sampler = ClockSampler(local_rank, period=0.005)
     sampler.start()
+    if graphs is not None:
+        timed(K, True)  # warm the graphs (untimed)
+    # ---- timed region: K steps, CUDA events on the launching stream --------------------------
     if use_mailbox:
         pn.check(lib.per_shard_exchange_stats(h, (pn.C.c_int64 * 3)(), sp))  # clear
-    ms, gather_ms = timed(K, graphs is not None)
-    clocks = sampler.stop()
+    ms = timed(K, graphs is not None)
     exchange_us = None
     if use_mailbox:
         st3 = (pn.C.c_int64 * 3)()
         pn.check(lib.per_shard_exchange_stats(h, st3, sp))
         exchange_us = {"mean": st3[1] / max(st3[0], 1) / 1e3, "max": st3[2] / 1e3, "samples": int(st3[0])}
+
+    # the graphs end with a sample + gather; close the step so that the passes below start from a clean state
+    def close_step():
+        rc = lib.per_td_priority_update(*a_td)
+        if rc:
+            pn.check(rc)
+
+    # ---- roofline pass: the gather kernel by itself --------------------------------------------------
+    # M launches, each on its own freshly sampled index set (M x 29 MB of distinct rows: nothing is re-read
+    # from L2), captured as one graph without programmatic chaining so that the launches run one after the
+    # other, one CUDA-event pair around each replay.  average launch duration = elapsed / M.
+    M_SETS, REPS = 16, 8
+    close_step()
+    idx_sets = [torch.empty(GB, dtype=torch.int64, device=dev) for _ in range(M_SETS)]
+    for i in range(M_SETS):
+        if use_mailbox:
+            pn.check(lib.per_sample_sharded(h, None, u_ptrs[(7 * i + 3) % n_u], GB, BETA, glen, P(idx_sets[i]), None, a_w32, sp))
+        elif world > 1:
+            pn.check(lib.per_shard_record(h, glen, a_rec, sp))
+            dist.all_gather_into_tensor(all_rec, shard_rec)
+            pn.check(lib.per_sample_sharded(h, a_all, u_ptrs[(7 * i + 3) % n_u], GB, BETA, glen, P(idx_sets[i]), None, a_w32, sp))
+        else:
+            pn.check(lib.per_sample_indices(h, u_ptrs[(7 * i + 3) % n_u], GB, BETA, P(idx_sets[i]), None, a_w32, sp))
+    torch.cuda.synchronize()
+    rows_per_set = [int((t >= 0).sum().item()) for t in idx_sets]
+    pdl_default = 3
+    pn.check(lib.per_tune(h, b"pdl", 0))
+    gather_ms = None
+    try:
+        side.wait_stream(stream)
+        with torch.cuda.stream(side):
+            sp_side = pn.stream_ptr(side)
+
+            def gather_block():
+                for i in range(M_SETS):
+                    rc = lib.per_gather(h, P(idx_sets[i]), GB, P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp_side)
+                    if rc:
+                        pn.check(rc)
+            gather_block()
+            g_gather = capture(gather_block)
+        stream.wait_stream(side)
+        g_gather.replay()
+        torch.cuda.synchronize()
+        times = []
+        for _ in range(REPS):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            g_gather.replay()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            times.append(e0.elapsed_time(e1) / M_SETS)
+        gather_ms = float(np.mean(times))
+    finally:
+        pn.check(lib.per_tune(h, b"pdl", int(os.environ.get("PER_PDL", pdl_default))))
+    clocks = sampler.stop()
+    # back to the loop's own buffers: one sample + gather into idx / o_*
+    draw_batch()
+
     # ---- step anatomy: the same graph blocks captured once more with the kernels' GPU-timer stamps on ----
     # (per_timeline: plain stores by CTA 0 of every launch, and for the gather the latest finish over the whole
-    # grid).  Outside the timed region; tells how long each kernel takes INSIDE the chained step, which the
-    # event-bracketed gather above cannot: an event between two kernels breaks their programmatic chaining.
+    # grid).  Outside the timed region; tells how long each kernel takes INSIDE the chained step.
     anatomy = None
     if graphs is not None:
         cap_tl = 8192
         pn.check(lib.per_tune(h, b"timeline", cap_tl))
         with torch.cuda.stream(side):
-            probe = [capture(lambda j=j: full_block(j * GRAPH_STEPS)) for j in range(3)]
+            sp_side = pn.stream_ptr(side)
+            probe = [capture(lambda j=j: full_block(j * GRAPH_STEPS_MAX, GRAPH_STEPS_MAX, sp_side)) for j in range(3)]
         stream.wait_stream(side)
         arr = (pn.C.c_int64 * cap_tl)()
         cnt = pn.C.c_int64(0)
@@ -537,7 +739,7 @@ def main():
         span = lambda a_, b_: med([c[b_] - (c[a_] if a_ != 8 else 0) for c in body if b_ in c and (a_ == 8 or a_ in c)])
         anatomy = {"steps": len(body), "period": med(periods), "td_arithmetic": span(8, 12), "update": span(8, 9),
                    "sample": span(2, 3), "gather_cta0": span(5, 6), "gather_grid": span(5, 13),
-                   "how": "GPU global-timer stamps written by the kernels (per_timeline) in 3 replayed graph blocks after "
+                   "how": "GPU global-timer stamps written by the kernels (per_timeline) in 3 replayed 31-step graph blocks after "
                           "the timed region: past the programmatic-launch wait -> done"}
         if args.timeline:
             msg = "rank %d timeline (us after 'update past wait', median of %d steps; period %.2f): " % (rank, len(body), anatomy["period"] or 0.0)
@@ -555,7 +757,7 @@ def main():
     eager_value = None
     if graphs is not None:
         k2 = min(K, 300)
-        ms2, _ = timed(k2, False)
+        ms2 = timed(k2, False)
         eager_value = GB * k2 / (ms2 * 1e-3)
 
     # ---- e2e: the public API with host buffers ---------------------------------------------
@@ -610,37 +812,75 @@ def main():
     e2e = {"value": GB * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "steps": e2e_steps, "api": api}
 
+    # ---- the other measurement rows of SURVEY section 8(d), N = 1 only -------------------------------
+    aql_block = learner = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        try:
+            aql_block = aql_row(dev)
+        except Exception as exc:  # an extra row must never cost the headline line
+            aql_block = {"error": str(exc)[:200]}
+        try:
+            learner = learner_row(buf, dev)
+        except Exception as exc:
+            learner = {"error": str(exc)[:200]}
+
     # ---- CPU baseline on this box (rank 0, N=1 only) -----------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, done_steps, dt = run_cpu_baseline(10 ** 6, 3, budget_s=15.0)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
                "sample": "%d steps (%.1f s) of sample(512)+update_priorities(512) on a 2^20-leaf tree with the "
-                         "oracle's pure-Python port of memory.py; host has %d cores, the reference path is serial"
-                         % (done_steps, dt, os.cpu_count())}
+                         "oracle's pure-Python port of memory.py's CustomPrioritizedReplayBuffer (the class ApeX.py uses: "
+                         "observations come back as lists of references, memory.py:348-362, no frame copy); host has %d "
+                         "cores, the reference path is serial Python" % (done_steps, dt, os.cpu_count())}
 
     if rank == 0:
         peak, peak_src = peaks()
-        launch_bytes = GATHER_BYTES_PER_ROW * rows_this_rank  # rows this rank's gather actually moved (last step)
+        mean_rows = float(np.mean(rows_per_set))
+        launch_bytes = GATHER_BYTES_PER_ROW * mean_rows  # rows one gather launch of the roofline pass moved on this rank
         achieved = launch_bytes / (gather_ms * 1e-3) / 1e9
+        traffic, traffic_kernel = ncu_gather_traffic()
+        mode = int(os.environ.get("PER_GATHER_MODE", DEFAULT_GATHER_MODE))
+        kernel_name = {0: "k_gather_tma", 1: "k_gather_ldg<16>", 2: "k_gather_bal"}[mode]
+        L_tree = int(np.log2(ring))
+        tree_bytes_sample = BATCH * (8 * L_tree + 20)
+        tree_bytes_update = 2 * (8 * BATCH + 24 * sum(min(BATCH, 2 ** l) for l in range(L_tree)))
+        roofline_tree = None
+        if anatomy and anatomy.get("sample") and anatomy.get("update"):
+            upd_us = anatomy["update"] - (anatomy.get("td_arithmetic") or 0.0)
+            roofline_tree = {
+                "bound": "latency (L2-resident trees; SURVEY 8(d) names HBM)", "peak": peak, "unit": "GB/s",
+                "sample": {"kernel": "k_sample" if world == 1 else "k_sample_sharded", "bytes_per_launch": tree_bytes_sample,
+                           "in_step_us": anatomy["sample"], "achieved": tree_bytes_sample / anatomy["sample"] / 1e3,
+                           "frac": tree_bytes_sample / anatomy["sample"] / 1e3 / peak},
+                "update": {"kernel": "k_update_cluster (tree part, TD prologue excluded)", "bytes_per_launch": tree_bytes_update,
+                           "in_step_us": upd_us, "achieved": tree_bytes_update / upd_us / 1e3,
+                           "frac": tree_bytes_update / upd_us / 1e3 / peak},
+                "how": "SURVEY 8(d) algorithmic bytes / the kernel's in-step duration (step_anatomy_us); both kernels are chains of "
+                       "dependent L2 round trips at batch 512 (0.4 MB per step), see profiles/ for the large-batch sweep where the "
+                       "same kernels are bandwidth-bound",
+            }
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
             "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-            "roofline": {"bound": "hbm", "kernel": "k_gather_ldg<16>" if os.environ.get("PER_GATHER_MODE", "1") == "1" else "k_gather_tma", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": NCU_GATHER_TRAFFIC if world == 1 else None,
+            "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic if (world == 1 and traffic_kernel == kernel_name) else None,
                          "peak_source": peak_src, "bytes_per_launch": launch_bytes, "avg_launch_us": gather_ms * 1e3,
+                         "how": "one CUDA-event pair around a graph of %d back-to-back launches (no programmatic chaining), each on "
+                                "its own sampled index set; mean of %d replays, right after the timed region" % (M_SETS, REPS),
                          "in_step": None if not (anatomy and anatomy.get("gather_grid")) else {
                              "avg_launch_us": anatomy["gather_grid"],
-                             "achieved": launch_bytes / (anatomy["gather_grid"] * 1e-6) / 1e9,
-                             "frac": launch_bytes / (anatomy["gather_grid"] * 1e-6) / 1e9 / peak,
-                             "how": "supplementary: the same launch timed by the kernel's own GPU-timer stamps inside the chained "
-                                    "step (wait passed -> last lane of the grid done); the event-bracketed figure above runs the "
-                                    "kernel unchained from its neighbours"}},
+                             "achieved": GATHER_BYTES_PER_ROW * rows_this_rank / (anatomy["gather_grid"] * 1e-6) / 1e9,
+                             "frac": GATHER_BYTES_PER_ROW * rows_this_rank / (anatomy["gather_grid"] * 1e-6) / 1e9 / peak,
+                             "how": "supplementary: the launch as it runs inside the chained step, timed by the kernel's own "
+                                    "GPU-timer stamps (wait passed -> last lane of the grid done)"}},
+            "roofline_tree": roofline_tree,
             "cpu_baseline": cpu, "launch": launch_mode, "value_eager_launches": eager_value,
-            "learner_step_us": {"total": 1e3 * ms / K, "gather": gather_ms * 1e3},
+            "learner_step_us": {"total": 1e3 * ms / K, "gather_alone": gather_ms * 1e3},
             "record_exchange_us": exchange_us, "step_anatomy_us": anatomy,
+            "aql": aql_block, "learner_updates_per_s": learner,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

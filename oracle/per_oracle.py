@@ -15,7 +15,8 @@ draws, and commits the outputs under `tests/golden/`; `tests/test_oracle_golden.
 replays the same inputs through this file and demands bit-equality for tree
 nodes / indices and 1e-5 relative for float results.  When `/root/reference` is
 present (the build container), `tests/test_oracle_vs_reference.py` additionally
-runs randomised op sequences through both.
+runs randomised op sequences (add / sample / update interleavings, duplicate indices,
+ring wrap-around) through both and compares every tree node and every sampled index.
 
 Two forms of every tree routine are given:
   * scalar, list-backed classes (`HeapTree`, `ReplayOracle`) — same data
@@ -219,7 +220,21 @@ class ReplayOracle:
         return np.array(w)
 
     def gather(self, idxes):
-        """memory.py:171-182 (and :380-391 for aql): stack the sampled rows."""
+        """memory.py:171-182 (and :380-391 for aql): stack the sampled rows.  With
+        `lists_like_reference` set on an "apex" oracle the observations come back the way
+        CustomPrioritizedReplayBuffer._encode_sample returns them (memory.py:348-362): two Python
+        lists of references to the stored frames, no copy — that is the form bench.py times as the
+        CPU baseline, since it is the class ApeX.py uses."""
+        if self.variant == "apex" and getattr(self, "lists_like_reference", False):
+            obs, act, rew, nxt, done = [], [], [], [], []
+            for k in idxes:
+                o, a, r, n, d = self.rows[k]
+                obs.append(o)
+                act.append(np.asarray(a))
+                rew.append(np.asarray(r))
+                nxt.append(n)
+                done.append(np.asarray(d))
+            return (obs, np.array(act), np.array(rew), nxt, np.array(done))
         cols = list(zip(*[self.rows[k] for k in idxes]))
         return tuple(np.array([np.asarray(x) for x in col]) for col in cols)
 

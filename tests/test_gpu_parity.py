@@ -282,12 +282,20 @@ def test_exact_leaf_path_full_size(memory, monkeypatch):
 
 # ------------------------------------------------------------------------------------ gather
 @pytest.mark.parametrize("obs_shape,size,batch", [((4, 84, 84), 6000, 512), ((4, 84, 84), 300, 37), ((3, 5), 1000, 64),
-                                                  ((17,), 500, 33)])
-def test_gather_matches_stored_rows(memory, obs_shape, size, batch):
-    """Atari-shaped rows go through the TMA bulk path (28224 = 4 x 7056 B pieces); odd sizes
-    through the byte mover.  Includes ring wrap-around (more adds than slots)."""
+                                                  ((17,), 500, 33), ((48,), 700, 129), ((16,), 900, 257), ((4, 84, 84), 5000, 3000)])
+@pytest.mark.parametrize("mover", ["tma", "ldg", "bal16", "bal16_nopipe", "bal32", "bal32_d2"])
+def test_gather_matches_stored_rows(memory, obs_shape, size, batch, mover):
+    """Every mover of the gather (per_tune "gather_mode": 0 = TMA bulk copies through shared-memory rings,
+    1 = one 7 056-byte piece per warp through registers, 2 = balanced shares, 16- or 32-byte vectors, with and
+    without the software pipeline) returns the stored bytes; rows whose size is not a multiple of 16 bytes take
+    the byte mover whatever the mode.  Includes ring wrap-around (more adds than slots)."""
+    import per_native as pn
     gen = torch.Generator(device="cuda").manual_seed(9)
     buf = memory.PrioritizedReplayBuffer(size, 0.6)
+    tune = {"tma": dict(gather_mode=0), "ldg": dict(gather_mode=1), "bal16": dict(gather_mode=2, gather_vbytes=16, gather_depth=8, gather_pipe=1),
+            "bal16_nopipe": dict(gather_mode=2, gather_vbytes=16, gather_depth=16, gather_pipe=0),
+            "bal32": dict(gather_mode=2, gather_vbytes=32, gather_depth=4, gather_pipe=1),
+            "bal32_d2": dict(gather_mode=2, gather_vbytes=32, gather_depth=2, gather_pipe=0, gather_ctas_per_sm=8)}[mover]
     total = size + size // 3
     obs = torch.randint(0, 256, (total,) + obs_shape, dtype=torch.uint8, device="cuda", generator=gen)
     nxt = torch.randint(0, 256, (total,) + obs_shape, dtype=torch.uint8, device="cuda", generator=gen)
@@ -299,6 +307,8 @@ def test_gather_matches_stored_rows(memory, obs_shape, size, batch):
         buf.add_batch_device(obs[lo:hi].contiguous(), nxt[lo:hi].contiguous(), act[lo:hi].contiguous(),
                              rew[lo:hi].contiguous(), done[lo:hi].contiguous())
     assert len(buf) == size and buf._next_idx == total % size
+    for k, v in tune.items():
+        pn.check(pn.lib.per_tune(buf._h, k.encode(), v))
     slot_src = np.arange(size)
     slot_src[: total - size] = np.arange(size, total)  # slots overwritten after the wrap
     d = buf.sample_device(batch, 0.5, uniforms=np.random.default_rng(1).random(batch))

@@ -1,16 +1,16 @@
 """Sweeps the launch shape of the frame-gather kernel (per_tune) on a B200 and prints
-microseconds per launch and GB/s (algorithmic bytes).  Kernel-only timing:
-CUDA events around back-to-back launches on one stream, random rows from a ring much larger
-than L2.  Usage: python tools/gather_sweep.py [--ring 262144] [--batch 512]"""
+microseconds per launch and GB/s (algorithmic bytes).  Kernel-only timing: a CUDA
+graph of M launches, each with its own index set (so no launch re-reads rows another one left in
+L2; the ring is much larger than L2), one CUDA-event pair around the replay.  Every shape's output is
+checked byte for byte against torch indexing of a kept copy of the ring.
+Usage: python tools/gather_sweep.py [--ring 262144] [--batch 512] [--quick]"""
 import argparse
-import itertools
 import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "ape-x_b200")]
 
-import numpy as np
 import torch
 
 import __graft_entry__ as entry
@@ -22,7 +22,8 @@ import per_native as pn
 ap = argparse.ArgumentParser()
 ap.add_argument("--ring", type=int, default=1 << 18)
 ap.add_argument("--batch", type=int, default=512)
-ap.add_argument("--iters", type=int, default=200)
+ap.add_argument("--launches", type=int, default=32, help="gather launches per graph (each with its own indices)")
+ap.add_argument("--reps", type=int, default=10)
 ap.add_argument("--quick", action="store_true")
 args = ap.parse_args()
 
@@ -30,127 +31,105 @@ OBS = (4, 84, 84)
 B = args.batch
 buf = memory.PrioritizedReplayBuffer(args.ring, 0.6)
 gen = torch.Generator(device="cuda").manual_seed(0)
+keep_obs, keep_nxt = [], []
 for lo in range(0, args.ring, 8192):
     m = min(8192, args.ring - lo)
     obs = torch.randint(0, 256, (m,) + OBS, dtype=torch.uint8, device="cuda", generator=gen)
-    buf.add_batch_device(obs, obs, torch.zeros(m, dtype=torch.int64, device="cuda"),
+    nxt = torch.randint(0, 256, (m,) + OBS, dtype=torch.uint8, device="cuda", generator=gen)
+    buf.add_batch_device(obs, nxt, torch.arange(lo, lo + m, dtype=torch.int64, device="cuda"),
                          torch.zeros(m, device="cuda"), torch.zeros(m, device="cuda"))
-idxs = [torch.randint(0, args.ring, (B,), dtype=torch.int64, device="cuda", generator=gen).sort().values for _ in range(16)]
+    keep_obs.append(obs)
+    keep_nxt.append(nxt)
+ring_obs, ring_nxt = torch.cat(keep_obs), torch.cat(keep_nxt)
+del keep_obs, keep_nxt
+M = args.launches
+idxs = [torch.randint(0, args.ring, (B,), dtype=torch.int64, device="cuda", generator=gen).sort().values for _ in range(M)]
 o_obs = torch.empty((B,) + OBS, dtype=torch.uint8, device="cuda")
 o_nxt = torch.empty_like(o_obs)
 o_act = torch.empty(B, dtype=torch.int64, device="cuda")
 o_rew = torch.empty(B, device="cuda")
 o_done = torch.empty(B, device="cuda")
-sp = pn.stream_ptr()
 h = buf._h
 bytes_per_launch = 2 * (2 * 28224 + 16) * B
+pn.check(pn.lib.per_tune(h, b"pdl", 0))  # launches of one graph must not overlap: kernel-only time
 
 
 def tune(**kw):
     # shrink first, then grow, so every intermediate shape is valid
+    pn.check(pn.lib.per_tune(h, b"gather_mode", 1))
     pn.check(pn.lib.per_tune(h, b"gather_stages", 2))
     pn.check(pn.lib.per_tune(h, b"gather_warps", 1))
     pn.check(pn.lib.per_tune(h, b"gather_piece", 16))
-    for k in ("gather_mode", "gather_ctas_per_sm"):
+    pn.check(pn.lib.per_tune(h, b"gather_ctas_per_sm", kw.get("gather_ctas_per_sm", 2)))
+    pn.check(pn.lib.per_tune(h, b"gather_piece", kw.get("gather_piece", 7056)))
+    pn.check(pn.lib.per_tune(h, b"gather_warps", kw.get("gather_warps", 4)))
+    pn.check(pn.lib.per_tune(h, b"gather_stages", kw.get("gather_stages", 2)))
+    for k in ("gather_depth", "gather_pipe", "gather_vbytes"):
         if k in kw:
             pn.check(pn.lib.per_tune(h, k.encode(), kw[k]))
-    pn.check(pn.lib.per_tune(h, b"gather_piece", kw.get("gather_piece", 7056)))
-    pn.check(pn.lib.per_tune(h, b"gather_warps", kw.get("gather_warps", 8)))
-    pn.check(pn.lib.per_tune(h, b"gather_stages", kw.get("gather_stages", 3)))
+    pn.check(pn.lib.per_tune(h, b"gather_mode", kw.get("gather_mode", 1)))
 
 
-def run(n):
-    for i in range(n):
-        rc = pn.lib.per_gather(h, pn.ptr(idxs[i % 16]), B, pn.ptr(o_obs), pn.ptr(o_nxt), pn.ptr(o_act), pn.ptr(o_rew),
-                               pn.ptr(o_done), None, sp)
-        if rc:
-            pn.check(rc)
+def launch(i, sp):
+    rc = pn.lib.per_gather(h, pn.ptr(idxs[i % M]), B, pn.ptr(o_obs), pn.ptr(o_nxt), pn.ptr(o_act), pn.ptr(o_rew),
+                           pn.ptr(o_done), None, sp)
+    if rc:
+        pn.check(rc)
 
 
 def measure():
-    run(10)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        launch(0, pn.stream_ptr(side))
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            for i in range(M):
+                launch(i, pn.stream_ptr(side))
+    torch.cuda.current_stream().wait_stream(side)
+    g.replay()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    run(args.iters)
-    e1.record()
+    best = 1e9
+    for _ in range(args.reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e3 / M)
+    return best
+
+
+def correct():
+    o_obs.zero_()
+    o_nxt.zero_()
+    launch(3, pn.stream_ptr())
     torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) * 1e3 / args.iters
-    # correctness spot check against torch indexing
-    ref = buf  # noqa
-    return us
+    k = idxs[3]
+    return bool(torch.equal(o_obs, ring_obs[k]) and torch.equal(o_nxt, ring_nxt[k]) and torch.equal(o_act, k))
 
 
-def check():
-    got = o_obs.clone()
-    d = buf.sample_device(B, 0.5, uniforms=np.random.default_rng(0).random(B))
-    return bool(torch.equal(d["obs"][:1], d["obs"][:1])) and got.shape == o_obs.shape
-
-
-print("mode warps stages piece ctas/sm |   us/launch    GB/s   frac_of_6555.8")
-shapes = []
-if args.quick:
-    shapes = [(0, 8, 3, 7056, 1), (0, 8, 6, 2352, 1), (1, 8, 0, 7056, 4)]
-else:
-    for piece in (3528 * 2, 14112, 28224):
-        for warps in (1, 2, 4, 8):
-            for stages in (2, 3, 4):
-                for ctas in (1, 2, 3, 4, 6, 8):
-                    smem = warps * stages * piece + 256
-                    if smem > 200 * 1024 or (smem + 1024) * ctas > 228 * 1024:
-                        continue
-                    shapes.append((0, warps, stages, piece, ctas))
-    for piece in (2352, 7056, 14112, 28224):
-        for ctas in (1, 2, 4, 8):
-            shapes.append((1, 8, 2, piece, ctas))
+shapes = []  # (label, kwargs)
+shapes.append(("ldg16 piece7056 2/sm", dict(gather_mode=1, gather_ctas_per_sm=2)))
+shapes.append(("tma 4w2s 4/sm", dict(gather_mode=0, gather_warps=4, gather_stages=2, gather_piece=7056, gather_ctas_per_sm=4)))
+for vb, depths in ((16, (4, 8, 12, 16)), (32, (2, 4, 6, 8))):
+    for d in depths:
+        for pipe in (0, 1):
+            for ctas in ((2, 4) if args.quick else (1, 2, 3, 4, 6, 8)):
+                shapes.append(("bal vb%d d%d pipe%d %d/sm" % (vb, d, pipe, ctas),
+                               dict(gather_mode=2, gather_vbytes=vb, gather_depth=d, gather_pipe=pipe, gather_ctas_per_sm=ctas)))
+print("%-28s |   us/launch     GB/s   frac_of_6555.8  ok" % "shape")
 best = None
-for mode, warps, stages, piece, ctas in shapes:
+for label, kw in shapes:
     try:
-        tune(gather_mode=mode, gather_warps=warps, gather_stages=max(stages, 2), gather_piece=piece, gather_ctas_per_sm=ctas)
+        tune(**kw)
     except Exception as e:
-        print(mode, warps, stages, piece, ctas, "invalid:", str(e)[:60])
+        print(label, "invalid:", str(e)[:60])
         continue
     us = measure()
+    ok = correct()
     gbs = bytes_per_launch / us / 1e3
-    print("%4d %5d %6d %5d %7d | %10.2f %8.1f %8.3f" % (mode, warps, stages, piece, ctas, us, gbs, gbs / 6555.8), flush=True)
-    if best is None or us < best[0]:
-        best = (us, mode, warps, stages, piece, ctas)
+    print("%-28s | %10.2f %9.1f %8.3f   %s" % (label, us, gbs, gbs / 6555.8, ok), flush=True)
+    if ok and (best is None or us < best[0]):
+        best = (us, label)
 print("best:", best)
-# fused widening (per_gather_cast) against gather + torch .float() on the same rows
-tune(gather_mode=0, gather_warps=4, gather_stages=2, gather_piece=7056, gather_ctas_per_sm=4)
-f_obs = torch.empty((B,) + OBS, dtype=torch.float32, device="cuda")
-f_nxt = torch.empty_like(f_obs)
-h_obs = torch.empty((B,) + OBS, dtype=torch.bfloat16, device="cuda")
-h_nxt = torch.empty_like(h_obs)
-
-
-def t_of(fn):
-    for _ in range(5):
-        fn()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(100):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) * 10.0
-
-
-def two_step():
-    run(1)
-    f_obs.copy_(o_obs)
-    f_nxt.copy_(o_nxt)
-
-
-t2 = t_of(two_step)
-t32 = t_of(lambda: pn.lib.per_gather_cast(h, pn.ptr(idxs[0]), B, 0, 1.0, pn.ptr(f_obs), pn.ptr(f_nxt), pn.ptr(o_act), pn.ptr(o_rew), pn.ptr(o_done), sp))
-t16 = t_of(lambda: pn.lib.per_gather_cast(h, pn.ptr(idxs[0]), B, 1, 1.0, pn.ptr(h_obs), pn.ptr(h_nxt), pn.ptr(o_act), pn.ptr(o_rew), pn.ptr(o_done), sp))
-print("widening: gather u8 + 2x torch copy_ to f32 %.1f us | per_gather_cast f32 %.1f us (%.0f GB/s algorithmic: read 28.9 MB, write 115.6 MB) | bf16 %.1f us"
-      % (t2, t32, (B * 2 * 28224 * 5) / t32 / 1e3, t16))
-# final correctness check of the best shape against torch indexing
-us, mode, warps, stages, piece, ctas = best
-tune(gather_mode=mode, gather_warps=warps, gather_stages=max(stages, 2), gather_piece=piece, gather_ctas_per_sm=ctas)
-run(1)
-torch.cuda.synchronize()
-print("check ok" if o_obs.shape[0] == B else "check failed")
