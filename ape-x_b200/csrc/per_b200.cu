@@ -23,8 +23,7 @@ struct seg_tree_s {
     int kind;
     TreeRef t;        // exactly one of sum / mnn is set
     double *v;
-    u64 *stamps;
-    u64 epoch;
+    u64 *stamps;      // last-write-wins arbitration scratch, all zero between calls
     u64 *status;      // device word
     int sm_count;
 };
@@ -36,7 +35,6 @@ struct per_buffer_s {
     int64_t obs_bytes, obs_stride, extra_bytes, extra_stride;
     TreeRef t;
     u64 *stamps;
-    u64 epoch;
     // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5,
     // word 3 sharded-sample epoch, word 4 retired-warp counter, words 5-6 owned-strata range tags
     u64 *scal;
@@ -183,14 +181,6 @@ int64_t shard_need(int64_t global_len, int64_t idx_base, int64_t cap) {
     return need;
 }
 
-u64 next_epoch(u64 &epoch, u64 *stamps, int64_t cap, cudaStream_t s) {
-    if (++epoch >= (u64(1) << 32)) {  // 2^32 calls: start the stamps over
-        cudaMemsetAsync(stamps, 0, sizeof(u64) * cap, s);
-        epoch = 1;
-    }
-    return epoch << 32;
-}
-
 int read_status(u64 *d_status, int64_t *h_out, cudaStream_t s) {
     u64 w = 0;
     PER_CUDA(cudaMemcpyAsync(&w, d_status, sizeof w, cudaMemcpyDeviceToHost, s));
@@ -206,6 +196,7 @@ extern "C" {
 
 const char *per_last_error(void) { return err_slot().c_str(); }
 int per_destroy(per_buffer *b);
+int seg_destroy(seg_tree *t);
 int per_version(void) { return 100; }
 
 // ---------------------------------------------------------------------------------- trees
@@ -225,11 +216,16 @@ int seg_create(seg_tree **out, int device, int64_t capacity, int kind) {
     t->t.cap = capacity;
     t->t.L = ilog2_exact(capacity);
     (kind == PER_TREE_SUM ? t->t.sum : t->t.mnn) = t->v;
-    PER_CUDA(cudaMalloc(&t->stamps, sizeof(u64) * capacity));
-    PER_CUDA(cudaMemsetAsync(t->stamps, 0, sizeof(u64) * capacity, 0));
-    PER_CUDA(cudaMalloc(&t->status, sizeof(u64)));
-    PER_CUDA(cudaMemsetAsync(t->status, 0, sizeof(u64), 0));
-    PER_CUDA(cudaStreamSynchronize(0));
+    cudaError_t e = cudaMalloc(&t->stamps, sizeof(u64) * capacity);
+    if (e == cudaSuccess) e = cudaMemsetAsync(t->stamps, 0, sizeof(u64) * capacity, 0);
+    if (e == cudaSuccess) e = cudaMalloc(&t->status, sizeof(u64));
+    if (e == cudaSuccess) e = cudaMemsetAsync(t->status, 0, sizeof(u64), 0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+    if (e != cudaSuccess) {  // nothing of a half-built tree stays behind
+        cudaGetLastError();
+        seg_destroy(t);
+        return fail(e == cudaErrorMemoryAllocation ? PER_ERR_NOMEM : PER_ERR_CUDA, "seg_create: %s", cudaGetErrorString(e));
+    }
     *out = t;
     return PER_OK;
 }
@@ -261,7 +257,6 @@ int seg_set(seg_tree *t, const int64_t *d_idx, const double *d_val, int64_t n, v
     a.n = n;
     a.len_limit = t->t.cap;
     a.stamps = t->stamps;
-    a.epoch_hi = next_epoch(t->epoch, t->stamps, t->t.cap, s);
     a.status = t->status;
     return run_update(a, nullptr, 0, t->sm_count, s);
 }
@@ -302,6 +297,19 @@ int seg_read(seg_tree *t, double *d_out, void *stream) {
     DeviceGuard g(t->device);
     PER_CUDA(cudaMemcpyAsync(d_out, t->v, sizeof(double) * 2 * t->t.cap, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return PER_OK;
+}
+
+static int read_leaf(const double *nodes, int64_t cap, int64_t idx, double *h_out, cudaStream_t s) {
+    if (idx < 0 || idx >= cap) return fail(PER_ERR_ASSERT, "0 <= idx < capacity");  // memory.py:90
+    PER_CUDA(cudaMemcpyAsync(h_out, nodes + cap + idx, sizeof(double), cudaMemcpyDeviceToHost, s));
+    PER_CUDA(cudaStreamSynchronize(s));
+    return PER_OK;
+}
+
+int seg_get(seg_tree *t, int64_t idx, double *h_out, void *stream) {
+    if (!t || !h_out) return fail(PER_ERR_ARG, "seg_get: bad argument");
+    DeviceGuard g(t->device);
+    return read_leaf(t->v, t->t.cap, idx, h_out, (cudaStream_t)stream);
 }
 
 int seg_status(seg_tree *t, int64_t *h_out, void *stream) {
@@ -411,18 +419,28 @@ static int ensure_host_path(per_buffer *b, int64_t rows, cudaStream_t s) {
     free_host_path(b);
     int64_t cap = 512;
     while (cap < rows) cap *= 2;
-    PER_CUDA(cudaMalloc(&h.d_u, sizeof(double) * cap));
-    PER_CUDA(cudaMalloc(&h.d_w64, sizeof(double) * cap));
-    PER_CUDA(cudaMalloc(&h.d_idx, sizeof(int64_t) * cap));
-    PER_CUDA(cudaMalloc(&h.d_act, sizeof(int64_t) * cap));
-    PER_CUDA(cudaMalloc(&h.d_rew, sizeof(float) * cap));
-    PER_CUDA(cudaMalloc(&h.d_done, sizeof(float) * cap));
-    PER_CUDA(cudaMalloc(&h.d_obs, (size_t)b->obs_bytes * cap));
-    PER_CUDA(cudaMalloc(&h.d_next, (size_t)b->obs_bytes * cap));
-    if (b->extra_bytes) PER_CUDA(cudaMalloc(&h.d_extra, (size_t)b->extra_bytes * cap));
-    PER_CUDA(cudaMalloc(&h.d_upd, 16 * (size_t)cap));
-    PER_CUDA(cudaHostAlloc(&h.h_pin, 24 * (size_t)cap, cudaHostAllocDefault));
-    PER_CUDA(cudaEventCreateWithFlags(&h.up_done, cudaEventDisableTiming));
+    cudaError_t e = cudaSuccess;
+    auto grab = [&e](void **p, size_t bytes) {
+        if (e == cudaSuccess && bytes) e = cudaMalloc(p, bytes);
+    };
+    grab((void **)&h.d_u, sizeof(double) * cap);
+    grab((void **)&h.d_w64, sizeof(double) * cap);
+    grab((void **)&h.d_idx, sizeof(int64_t) * cap);
+    grab((void **)&h.d_act, sizeof(int64_t) * cap);
+    grab((void **)&h.d_rew, sizeof(float) * cap);
+    grab((void **)&h.d_done, sizeof(float) * cap);
+    grab((void **)&h.d_obs, (size_t)b->obs_bytes * cap);
+    grab((void **)&h.d_next, (size_t)b->obs_bytes * cap);
+    grab((void **)&h.d_extra, (size_t)b->extra_bytes * cap);
+    grab((void **)&h.d_upd, 16 * (size_t)cap);
+    if (e == cudaSuccess) e = cudaHostAlloc(&h.h_pin, 24 * (size_t)cap, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h.up_done, cudaEventDisableTiming);
+    if (e != cudaSuccess) {  // all or nothing: a later, smaller request starts from a clean slate
+        cudaGetLastError();
+        free_host_path(b);
+        return fail(e == cudaErrorMemoryAllocation ? PER_ERR_NOMEM : PER_ERR_CUDA, "host-buffer staging for %lld rows: %s",
+                    (long long)cap, cudaGetErrorString(e));
+    }
     h.have_event = true;
     h.cap = cap;
     return PER_OK;
@@ -515,6 +533,7 @@ int per_add_batch(per_buffer *b, const void *d_obs, const void *d_next, const in
     a.max_prio = b->max_prio();
     int rc = run_update(a, nullptr, 0, b->sm_count, s);
     if (rc) return rc;
+    b->last_sample_idx = nullptr;                                      // rows changed: no sample is bound any more
     b->cursor = (b->cursor + n) % b->ring_size;                        // memory.py:169
     b->len = b->len + n > b->ring_size ? b->ring_size : b->len + n;    // memory.py:165-168
     return PER_OK;
@@ -932,7 +951,6 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.n = n;
     a.len_limit = b->len;
     a.stamps = b->stamps;
-    a.epoch_hi = next_epoch(b->epoch, b->stamps, b->t.cap, s);
     a.status = b->status();
     a.max_prio = b->max_prio();
     a.batch_max = batch_max;
@@ -956,6 +974,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     a.sorted_fast = b->sorted_update;
     a.cluster_max = b->upd_cluster_max;
+    if (a.sorted_idx) b->last_sample_idx = nullptr;  // the binding to that sample ends with its first update (see per_sample_sharded)
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);
 }
 
@@ -1073,6 +1092,7 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
     t.out_prio = d_out_prio ? d_out_prio : b->td_scratch + b->td_scratch_cap;
     t.out_loss = d_out_loss;
     t.red = b->td_red();
+    t.status = b->status();
     if (batch <= UPD_CLUSTER_MAX_ITEMS) {
         if (d_idx) return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, &t, s);
         UpdArgs a;
@@ -1096,6 +1116,24 @@ int per_tree_read(per_buffer *b, int which, double *d_out, void *stream) {
     DeviceGuard g(b->device);
     PER_CUDA(cudaMemcpyAsync(d_out, which == PER_TREE_SUM ? b->t.sum : b->t.mnn, sizeof(double) * 2 * b->t.cap,
                              cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return PER_OK;
+}
+
+int per_tree_get(per_buffer *b, int which, int64_t idx, double *h_out, void *stream) {
+    if (!b || !h_out || (which != PER_TREE_SUM && which != PER_TREE_MIN)) return fail(PER_ERR_ARG, "per_tree_get: bad argument");
+    DeviceGuard g(b->device);
+    return read_leaf(which == PER_TREE_SUM ? b->t.sum : b->t.mnn, b->t.cap, idx, h_out, (cudaStream_t)stream);
+}
+
+int per_tree_reduce(per_buffer *b, int which, int64_t start, int64_t end, double *d_out, void *stream) {
+    if (!b || !d_out || (which != PER_TREE_SUM && which != PER_TREE_MIN)) return fail(PER_ERR_ARG, "per_tree_reduce: bad argument");
+    if (end < 0) end += b->t.cap;  // memory.py:71-72
+    if (start < 0 || end > b->t.cap || end - 1 < start)
+        return fail(PER_ERR_ASSERT, "per_tree_reduce: empty or out-of-range [%lld, %lld)", (long long)start, (long long)end);
+    DeviceGuard g(b->device);
+    k_range_reduce<<<1, 32, 0, (cudaStream_t)stream>>>(which == PER_TREE_SUM ? b->t.sum : b->t.mnn, b->t.cap, start, end - 1,
+                                                       which == PER_TREE_SUM, d_out);
+    PER_CUDA(cudaGetLastError());
     return PER_OK;
 }
 
@@ -1294,7 +1332,6 @@ namespace {
 constexpr int NOALLOC_MAX_DEVICES = 64;
 struct NoallocDevice {
     u64 *base = nullptr;  // device address of g_noalloc_scratch on this device
-    u64 epoch = 0;        // call counter; a stamp of an earlier call can never win a later one
     int sm_count = 0;
 };
 NoallocDevice g_noalloc_dev[NOALLOC_MAX_DEVICES];
@@ -1336,7 +1373,6 @@ int seg_set_noalloc(int device, double *d_sum_nodes, double *d_min_nodes, int64_
     a.n = n;
     a.len_limit = capacity;
     a.stamps = nd.base + SEG_NOALLOC_HEADER_WORDS;
-    a.epoch_hi = next_epoch(nd.epoch, a.stamps, SEG_NOALLOC_MAX_CAPACITY, s);  // clears the stamps only on 2^32 wrap
     a.status = d_status ? reinterpret_cast<u64 *>(d_status) : nd.base;
     return run_update(a, nullptr, 0, nd.sm_count, s);
 }

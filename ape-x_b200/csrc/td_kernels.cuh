@@ -20,7 +20,19 @@ struct TdArgs {
     float *out_prio;  // 0.9*max(td) + 0.1*td + 1e-6   (scratch or caller's)
     float *out_loss;  // mean(huber(td) * w), may be null
     float *red;       // [0] running max of td, [1] running sum of loss terms
+    u64 *status;      // device status word (PER_STATUS_BAD_INDEX for an action outside [0, nA)); may be null
 };
+
+// The action column indexes the Q row (q.gather(1, actions), utils.py:71): an action outside [0, nA) would read
+// another row; it is reported through the status word and row 0's column is used instead.
+__device__ __forceinline__ int64_t td_action(const TdArgs &a, int64_t b) {
+    const int64_t act = a.act[b];
+    if (act < 0 || act >= a.nA) {
+        if (a.status) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
+        return 0;
+    }
+    return act;
+}
 
 // |td| of row b  (utils.py:71-76)
 __device__ __forceinline__ float td_row(const TdArgs &a, int64_t b) {
@@ -31,22 +43,7 @@ __device__ __forceinline__ float td_row(const TdArgs &a, int64_t b) {
         float x = qn[i];
         if (x > bv) { bv = x; best = i; }
     }
-    const float q_a = a.q[b * a.nA + a.act[b]];
-    const float boot = a.q_tgt[b * a.nA + best];
-    const float y = __fadd_rn(a.rew[b], __fmul_rn(__fmul_rn(a.gamma_n, boot), __fsub_rn(1.0f, a.done[b])));
-    return fabsf(__fsub_rn(y, q_a));
-}
-
-// Same, with the row of q_next already in shared memory (coalesced staging by the caller).
-__device__ __forceinline__ float td_row_from(const TdArgs &a, int64_t b, const float *qn) {
-    int best = 0;
-    float bv = qn[0];
-#pragma unroll 1
-    for (int i = 1; i < (int)a.nA; ++i) {
-        float x = qn[i];
-        if (x > bv) { bv = x; best = i; }
-    }
-    const float q_a = a.q[b * a.nA + a.act[b]];
+    const float q_a = a.q[b * a.nA + td_action(a, b)];
     const float boot = a.q_tgt[b * a.nA + best];
     const float y = __fadd_rn(a.rew[b], __fmul_rn(__fmul_rn(a.gamma_n, boot), __fsub_rn(1.0f, a.done[b])));
     return fabsf(__fsub_rn(y, q_a));
@@ -59,8 +56,11 @@ __device__ __forceinline__ float td_huber(float td) {  // utils.py:79
     return td < 1.0f ? __fmul_rn(__fmul_rn(0.5f, td), td) : __fsub_rn(td, 0.5f);
 }
 
+// max that keeps a NaN, like torch.max (utils.py:77: one NaN TD error makes every priority of the batch NaN, and
+// update_priorities then refuses them, memory.py:315); fmaxf alone would drop it
+__device__ __forceinline__ float max_keep_nan(float x, float y) { return (x != x) ? x : ((y != y) ? y : fmaxf(x, y)); }
 __device__ __forceinline__ float warp_max_f32(float x) {
-    for (int o = 16; o; o >>= 1) x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+    for (int o = 16; o; o >>= 1) x = max_keep_nan(x, __shfl_xor_sync(0xffffffffu, x, o));
     return x;
 }
 __device__ __forceinline__ float warp_sum_f32(float x) {
@@ -74,7 +74,7 @@ __global__ void k_td_pass1(TdArgs a) {
     for (int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; b < a.batch; b += (int64_t)gridDim.x * blockDim.x) {
         float td = td_row(a, b);
         a.out_td[b] = td;
-        mx = fmaxf(mx, td);
+        mx = max_keep_nan(mx, td);
     }
     mx = warp_max_f32(mx);
     if ((threadIdx.x & 31) == 0) atomic_max_pos_f32(a.red, mx);

@@ -57,8 +57,10 @@ struct UpdArgs {
     double alpha;
     int64_t n;
     int64_t len_limit;        // valid indices are [0, len_limit)
-    u64 *stamps;              // cap entries; null when indices are known distinct
-    u64 epoch_hi;             // call counter << 32
+    u64 *stamps;              // cap entries, all zero between calls; null when indices are known distinct.  Arbitration of
+                              // duplicates: atomicMax(stamps[k], j + 1); the item whose stamp survives wins and puts the
+                              // entry back to zero with its leaf write, so nothing outlives the call (a launch replayed from
+                              // a CUDA graph, or another tree sharing the array, starts from zeros again)
     u64 *status;
     double *max_prio;         // device scalar `_max_priority`; may be null (stand-alone trees)
     double batch_max;         // LEAF_GIVEN: raw-priority maximum of the batch (<=0: none)
@@ -112,6 +114,16 @@ __device__ __forceinline__ int64_t upd_index(const UpdArgs &a, int64_t j) {
     }
     int64_t k = a.ring_start + j;
     return k >= a.ring_size ? k - a.ring_size : k;
+}
+
+// Would the reference accept item j (memory.py:315-316)?  No status side effects, no pow: what the stamp pass of the
+// multi-launch form needs, so that a rejected item never holds a stamp.
+__device__ __forceinline__ bool upd_item_ok(const UpdArgs &a, int64_t j, int64_t &k) {
+    k = upd_index(a, j);
+    if (k == IDX_SKIP || k < 0 || k >= a.len_limit) return false;
+    if (a.src_kind == LEAF_PRIO_F64) return static_cast<const double *>(a.src)[j] > 0.0;
+    if (a.src_kind == LEAF_PRIO_F32) return static_cast<const float *>(a.src)[j] > 0.0f;
+    return true;
 }
 
 // Raw priority (for the running max) and leaf value of item j.  Returns false for an
@@ -353,7 +365,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         int64_t act_b = 0;
         float rew_b = 0.0f, done_b = 0.0f, w_b = 0.0f, q_a = 0.0f;
         if (have) {
-            act_b = td.act[b];
+            act_b = td_action(td, b);
             rew_b = td.rew[b];
             done_b = td.done[b];
             if (td.out_loss) w_b = td.w[b];
@@ -413,7 +425,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             const float *home = cl.map_shared_rank(s_clu, 0);
             float m = tid < ncta ? home[tid] : 0.0f;
             float l = tid < ncta ? home[UPD_MAX_CTAS + tid] : 0.0f;
-            m = warp_max_f32(m);
+            m = warp_max_f32(m);  // keeps a NaN (see max_keep_nan)
             if (tid == 0) f_red[32] = m;
             if (td.out_loss && rank == 0) {
                 float acc_l = 0.0f;
@@ -622,7 +634,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             if (a.sorted_idx) {
                 if (lo + i + 1 < (int)a.n && a.idx[lo + i + 1] == a.idx[lo + i]) kk = -1;  // the next item overwrites this one
             } else if (a.stamps) {
-                atomicMax(a.stamps + k, a.epoch_hi | (u64)(lo + i));
+                atomicMax(a.stamps + k, (u64)(lo + i) + 1);
             }
         }
         s_k[i] = kk;
@@ -632,7 +644,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
 #pragma unroll 1
         for (int i = tid; i < cnt; i += T) {
             const int kk = s_k[i];
-            if (kk >= 0 && __ldcg(a.stamps + kk) != (a.epoch_hi | (u64)(lo + i))) s_k[i] = -1;  // a later item wins
+            if (kk >= 0) {
+                if (__ldcg(a.stamps + kk) != (u64)(lo + i) + 1) s_k[i] = -1;  // a later item wins
+                else a.stamps[kk] = 0;  // the winner clears the entry (losers that look later still see "not mine")
+            }
         }
     }
     UPD_TRACE(2);
@@ -820,13 +835,17 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
 // ---------------------------------------------------------------------------------------
 __global__ void k_upd_stamp(UpdArgs a) {
     for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < a.n; j += (int64_t)gridDim.x * blockDim.x) {
-        int64_t k = upd_index(a, j);
-        if (k >= 0 && k < a.len_limit) atomicMax(a.stamps + k, a.epoch_hi | (u64)j);
+        int64_t k;
+        if (upd_item_ok(a, j, k)) atomicMax(a.stamps + k, (u64)j + 1);
     }
 }
 
+// The winner of a leaf clears its stamp on the way (see UpdArgs::stamps).
 __device__ __forceinline__ bool upd_is_winner(const UpdArgs &a, int64_t j, int64_t k) {
-    return !a.stamps || __ldcg(a.stamps + k) == (a.epoch_hi | (u64)j);
+    if (!a.stamps) return true;
+    if (__ldcg(a.stamps + k) != (u64)j + 1) return false;
+    a.stamps[k] = 0;
+    return true;
 }
 
 __global__ void k_upd_leaf(UpdArgs a) {

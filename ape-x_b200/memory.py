@@ -54,19 +54,24 @@ class _HostStage(object):
         self.down_bufs = {}
 
     def up(self, name, array):
+        """One pinned buffer per (name, row shape, dtype), grown to the largest row count seen: a caller that
+        uploads 1, 2, 3, ... rows at a time (per-row add interleaved with sample requests) keeps reusing it
+        instead of pinning a new block per size."""
         a = np.ascontiguousarray(array)
-        key = (name, a.shape, a.dtype.str)
+        n = a.shape[0] if a.ndim else 1
+        key = (name, a.shape[1:], a.dtype.str)
         ent = self.up_bufs.get(key)
-        if ent is None:
-            ent = [torch.empty(a.shape, dtype=torch.from_numpy(np.empty(0, dtype=a.dtype)).dtype, pin_memory=True),
-                   torch.cuda.Event()]
+        if ent is not None:
+            ent[1].synchronize()  # the previous copy out of this buffer has finished
+        if ent is None or ent[0].shape[0] < n:
+            cap = max(n, 2 * ent[0].shape[0] if ent is not None else 0)
+            tdt = torch.from_numpy(np.empty(0, dtype=a.dtype)).dtype
+            ent = [torch.empty((cap,) + a.shape[1:], dtype=tdt, pin_memory=True), torch.cuda.Event()]
             self.up_bufs[key] = ent
-        else:
-            ent[1].synchronize()
-        ent[0].numpy()[...] = a
-        d = ent[0].to(self.device, non_blocking=True)
+        ent[0].numpy()[:n] = a.reshape((n,) + a.shape[1:])
+        d = ent[0][:n].to(self.device, non_blocking=True)
         ent[1].record()
-        return d
+        return d.reshape(a.shape)
 
     def out_slot(self, name, shape, dtype):
         """One of RING pinned host tensors for a result the native library writes by itself (per_sample_host)."""
@@ -171,8 +176,11 @@ class SegmentTree(object):
         self.set_batch([int(idx)], [float(val)])
 
     def __getitem__(self, idx):
+        """memory.py:89-91: one leaf (8 bytes cross the bus, not the node array)."""
         assert 0 <= idx < self._capacity
-        return float(self._value[self._capacity + int(idx)])
+        v = _n.C.c_double(0.0)
+        _n.check(_n.lib.seg_get(self._h, int(idx), _n.C.byref(v), _n.stream_ptr()))
+        return v.value
 
 
 class SumSegmentTree(SegmentTree):
@@ -224,19 +232,27 @@ class _TreeView(object):
         return self._owner.tree_values(self._which)
 
     def __getitem__(self, idx):
+        """`_it_sum[idx]` (memory.py:293): one leaf."""
         assert 0 <= idx < self._capacity
-        return float(self._value[self._capacity + int(idx)])
+        o = self._owner
+        o._flush()
+        if o._h is None:
+            return 0.0 if self._which == _n.TREE_SUM else float("inf")
+        v = _n.C.c_double(0.0)
+        _n.check(_n.lib.per_tree_get(o._h, self._which, int(idx), _n.C.byref(v), _n.stream_ptr()))
+        return v.value
 
     def reduce(self, start=0, end=None):
-        # host-side restatement is not needed: full range = root; partial ranges go through a
-        # scratch tree of the same leaves so the association is the device kernel's.
-        v = self._value
-        if (start, end) in ((0, None), (0, self._capacity)):
-            return float(v[1])
-        t = (SumSegmentTree if self._which == _n.TREE_SUM else MinSegmentTree)(self._capacity, self._owner._device)
-        lv = v[self._capacity:]
-        t.set_batch(np.arange(self._capacity), lv)
-        return t.reduce(start, end)
+        """`_it_sum.sum(start, end)` / `_it_min.min(start, end)` (memory.py:54-74) on the buffer's own tree."""
+        o = self._owner
+        o._flush()
+        if end is None:
+            end = self._capacity
+        if o._h is None:
+            return 0.0 if self._which == _n.TREE_SUM else float("inf")
+        out = torch.empty(1, dtype=torch.float64, device=o._device)
+        _n.check(_n.lib.per_tree_reduce(o._h, self._which, int(start), int(end), _n.ptr(out), _n.stream_ptr()))
+        return float(out.item())
 
     sum = reduce
     min = reduce
@@ -513,6 +529,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         w32 = torch.empty(batch_size, dtype=torch.float32, device=self._device)
         _n.check(_n.lib.per_sample_indices(self._h, _n.ptr(u), batch_size, float(beta), _n.ptr(idx), _n.ptr(w64),
                                            _n.ptr(w32), _n.stream_ptr()))
+        self._bound_idx = idx  # the native side binds this address to the sample until its update (per_b200.h): keep it allocated
         out = {"idx": idx, "weights": w32, "weights64": w64}
         if gather:
             if obs_dtype is not None and self._obs_dtype == np.uint8:

@@ -40,6 +40,9 @@ SIGNATURES = {
     "seg_reduce": (C.c_int, [_p, _i64, _i64, _p, _p]),
     "seg_find_prefixsum": (C.c_int, [_p, _p, _i64, _p, _p]),
     "seg_read": (C.c_int, [_p, _p, _p]),
+    "seg_get": (C.c_int, [_p, _i64, C.POINTER(_f64), _p]),
+    "per_tree_get": (C.c_int, [_p, C.c_int, _i64, C.POINTER(_f64), _p]),
+    "per_tree_reduce": (C.c_int, [_p, C.c_int, _i64, _i64, _p, _p]),
     "seg_capacity": (_i64, [_p]),
     "seg_status": (C.c_int, [_p, C.POINTER(_i64), _p]),
     "aql_create": (C.c_int, [C.POINTER(_p), C.c_int, C.c_int, C.c_int]),

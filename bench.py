@@ -345,6 +345,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true", help="world > 1: skip the start-up parity check against the oracle")
     ap.add_argument("--no-extras", action="store_true", help="skip the AQL and whole-learner-step rows (N=1)")
     ap.add_argument("--global-batch", type=int, default=0,
                     help="strong scaling: fix the GLOBAL stratified batch (e.g. 4096) and give every GPU global/N strata "
@@ -478,6 +479,13 @@ def main():
     # k_shard_record (+ NCCL's all-gather kernel, not ours) and B > 2048 uses the multi-launch update
     launches_per_step = 3 if (world == 1 or use_mailbox) else 4
 
+    if world > 1 and not args.no_parity_check:
+        # the sharded path against the single-tree oracle on the very GPUs about to be timed (tests/multi_gpu_parity.py;
+        # a checker only: a small separate replay, before anything is measured)
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import multi_gpu_parity
+        multi_gpu_parity.run_check(rank, world, local_rank, size=40000, steps=4, log=sys.stderr.write)
+        dist.barrier()
     if use_mailbox:
         # self-check: records through the mailboxes must give the indices the all-gathered records give
         pn.check(lib.per_shard_record(h, glen, a_rec, sp))

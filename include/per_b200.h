@@ -81,6 +81,9 @@ int seg_find_prefixsum(seg_tree *t, const double *d_mass, int64_t n, int64_t *d_
 
 /* Copies the 2*capacity node array (`_value`, memory.py:36) to d_out. */
 int seg_read(seg_tree *t, double *d_out, void *stream);
+/* SegmentTree.__getitem__ (memory.py:89-91): leaf idx to *h_out (8 bytes cross the bus, not the
+ * tree).  idx outside [0, capacity) is PER_ERR_ASSERT (memory.py:90).  Synchronises `stream`. */
+int seg_get(seg_tree *t, int64_t idx, double *h_out, void *stream);
 int64_t seg_capacity(const seg_tree *t);
 /* Reads and clears the status word.  Synchronises `stream`. */
 int seg_status(seg_tree *t, int64_t *h_out, void *stream);
@@ -156,10 +159,11 @@ int nstep_assemble(int device, int64_t n_streams, const int64_t *d_offsets, cons
  *  - The first call on each device looks up the array's device address
  *    (cudaGetSymbolAddress, with that device current) and caches it; make that first call
  *    before any stream capture begins.
- *  - All calls on a device share the one array, which keeps what the previous call wrote
- *    (stamps carry a call counter, so stale entries never win; they are cleared only when
- *    the counter wraps after 2^32 calls).  Two calls whose kernels overlap on the GPU
- *    (different streams without ordering, or two host threads) race on it: order them. */
+ *  - All calls on a device share the one array.  It must be all zero when a call starts and
+ *    every call leaves it so: the item that wins a leaf puts that leaf's entry back to zero
+ *    as it writes the leaf, so trees of different sizes can take turns and a call replayed
+ *    from a CUDA graph starts clean.  Two calls whose kernels overlap on the GPU (different
+ *    streams without ordering, or two host threads) race on it: order them. */
 #define SEG_NOALLOC_MAX_CAPACITY (1 << 20)
 int seg_set_noalloc(int device, double *d_sum_nodes, double *d_min_nodes, int64_t capacity,
                     const int64_t *d_idx, const double *d_val, int64_t n, uint64_t *d_status,
@@ -317,7 +321,18 @@ int per_shard_attach_record(per_buffer *b, double *d_record, int64_t global_len)
  * The strata a shard owns are contiguous (masses ascend), and the kernel leaves their range
  * on the device: per_gather / per_update_* / per_td_priority_update calls that are handed the
  * SAME d_out_idx buffer and batch then visit only that range instead of skipping -1 entries one
- * by one, so per-rank work stays proportional to the rank's share of the batch. */
+ * by one, so per-rank work stays proportional to the rank's share of the batch.
+ *
+ * Binding between a sample and the calls that follow it (this entry point and per_sample_indices
+ * alike): the library remembers the address and length of the index buffer a sample wrote.  A
+ * per_gather / per_gather_cast / per_update_* / per_td_priority_update call that passes exactly
+ * that buffer is taken to work on THAT sample: its indices ascend (so duplicates are adjacent and
+ * the update needs no arbitration pass) and, sharded, only the owned strata range is visited.
+ * The contents must therefore be unchanged since the sample wrote them, and the buffer must stay
+ * allocated until the update has been issued (a freed buffer's address can come back from the
+ * allocator holding other indices).  The binding ends with the first update that uses it, with
+ * per_add_batch, and with the next sample; any other index buffer takes the general path.  An
+ * index buffer that is found not to ascend on the bound path sets PER_STATUS_BAD_INDEX. */
 int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch,
                        double beta, int64_t global_len, int64_t *d_out_idx, double *d_out_w64,
                        float *d_out_w32, void *stream);
@@ -383,6 +398,12 @@ int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_
 
 /* Copies one tree's node array (`_it_sum._value` / `_it_min._value`) to d_out[2*capacity]. */
 int per_tree_read(per_buffer *b, int which, double *d_out, void *stream);
+/* `_it_sum[idx]` / `_it_min[idx]` (memory.py:89-91, used at :293) and `_it_sum.sum(start, end)` /
+ * `_it_min.min(start, end)` (memory.py:54-74, used at :244,289) on the buffer's own trees: one leaf
+ * to *h_out (synchronises `stream`), or the range reduction with the reference's association to
+ * d_out[0] (stream-ordered).  Same argument rules as seg_get / seg_reduce. */
+int per_tree_get(per_buffer *b, int which, int64_t idx, double *h_out, void *stream);
+int per_tree_reduce(per_buffer *b, int which, int64_t start, int64_t end, double *d_out, void *stream);
 
 #ifdef __cplusplus
 }

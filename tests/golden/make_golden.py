@@ -251,6 +251,39 @@ def gen_td(utl):
     np.savez_compressed(os.path.join(HERE, "td.npz"), **out)
 
 
+def td_aql_inputs(case):
+    """Inputs of the compute_loss_AQL fixture, regenerated from a seed (numpy's Generator streams are stable),
+    so that the fixture file only carries the reference's outputs.  Shared with tests/test_gpu_parity.py."""
+    B, K, n_steps = [(256, 1000, 1), (64, 1000, 3)][case]
+    rng = np.random.default_rng(7700 + case)
+    f = np.float32
+    q, qn, qt = (rng.standard_normal((B, K)).astype(f) for _ in range(3))
+    a = rng.integers(0, K, size=B).astype(np.int64)
+    r = (rng.integers(-1, 2, size=B) * 1.3).astype(f)
+    d = (rng.random(B) < 0.1).astype(f)
+    w = rng.random(B).astype(f)
+    return q, qn, qt, a, r, d, w, n_steps
+
+
+def gen_td_aql(utl):
+    """utils.compute_loss_AQL (utils.py:44-61) at AQL's real shape [B, K = 1000]: the 'models' are table look-ups,
+    so the Q values are the inputs."""
+    import torch
+    out = {}
+    for case in range(2):
+        q, qn, qt, a, r, d, w, n_steps = td_aql_inputs(case)
+        B = q.shape[0]
+        tq, tqn, tqt = torch.from_numpy(q), torch.from_numpy(qn), torch.from_numpy(qt)
+        s, s2 = torch.zeros(B, 1), torch.ones(B, 1)
+        online = lambda x, a_mu: tq if float(x[0, 0]) == 0.0 else tqn
+        target = lambda x, a_mu: tqt
+        batch = (s, torch.from_numpy(a), torch.from_numpy(r), s2, torch.from_numpy(d), None, torch.from_numpy(w))
+        loss, prios = utl.compute_loss_AQL(online, target, batch, n_steps, 0.99)
+        out[f"c{case}_loss"] = float(loss)
+        out[f"c{case}_prios"] = np.asarray(prios)
+    np.savez_compressed(os.path.join(HERE, "td_aql.npz"), **out)
+
+
 def gen_aql():
     """Q_Network.act (model.py:294-335) of the real reference, continuous and discrete, NoisyLinear
     in training mode.  model.py imports gym at module level; a two-line stand-in satisfies it
@@ -287,6 +320,9 @@ def main():
     if "--only-aql" in sys.argv:
         gen_aql()
         return
+    if "--only-td-aql" in sys.argv:
+        gen_td_aql(load_reference("utils"))
+        return
     mem = load_reference("memory")
     mem.np = numpy1_shim()
     rnd = Replay()
@@ -299,6 +335,7 @@ def main():
     gen_nstep(mem)
     utl = load_reference("utils")
     gen_td(utl)
+    gen_td_aql(utl)
     gen_aql()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):

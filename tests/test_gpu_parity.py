@@ -455,3 +455,177 @@ def test_gather_cast_equals_torch_widening(memory, dtype, scale):
     for k in ("obs", "next_obs"):
         want = (plain[k].float() * np.float32(scale)).to(dtype)
         assert cast[k].dtype == dtype and torch.equal(cast[k], want), k
+
+
+# ------------------------------------------------------- TD kernel: AQL's [B, K = 1000] shape, large batches
+def _golden_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(GOLDEN, "make_golden.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+@pytest.mark.parametrize("case", [0, 1])
+def test_td_priority_golden_compute_loss_aql(memory, case):
+    """utils.compute_loss_AQL (utils.py:44-61) at its real shape, K = 1000 candidate actions per row: the Q rows of
+    one CTA do not fit the staging buffer, so the prologue of k_update_cluster reads them in place (the branch
+    `staged == false`).  Golden priorities / loss from the real reference (tests/golden/td_aql.npz; the inputs are
+    regenerated from the fixture's seed)."""
+    q, qn, qt, a, r, d, w, n_steps = _golden_module().td_aql_inputs(case)
+    g = load("td_aql.npz")
+    B = q.shape[0]
+    buf = memory.CustomPrioritizedReplayBuffer(4096, 0.6)
+    fill_device(buf, 4096, (16,), rng_seed=1)
+    dev = lambda x: torch.as_tensor(x).cuda()
+    smp = buf.sample_device(B, 0.4, uniforms=np.random.default_rng(case).random(B), gather=False)
+    before = buf._it_sum._value[4096:].copy()
+    loss, prio, td = buf.td_priority_update(dev(q), dev(qn), dev(qt), dev(a), dev(r), dev(d), dev(w), n_steps, 0.99, idx=smp["idx"])
+    np.testing.assert_allclose(prio.cpu().numpy(), g[f"c{case}_prios"], rtol=RTOL)
+    np.testing.assert_allclose(float(loss), float(g[f"c{case}_loss"]), rtol=RTOL)
+    ol, op, otd = po.td_priorities(q, qn, qt, a, r, d, w, n_steps, 0.99)
+    np.testing.assert_allclose(td.cpu().numpy(), otd, rtol=RTOL, atol=1e-7)
+    sv = buf._it_sum._value
+    want = po.apply_updates(before, smp["idx"].cpu().numpy(), po.pow_alpha(prio.double().cpu().numpy(), 0.6))
+    assert np.abs(bits(sv[4096:]).astype(np.int64) - bits(want).astype(np.int64)).max() <= 2
+    assert np.array_equal(bits(sv)[1:], bits(po.build_tree(sv[4096:], "sum"))[1:])
+
+
+@pytest.mark.parametrize("batch,nA", [(20000, 4), (20000, 1000), (5000, 1000), (4096, 37)])
+def test_td_priority_large_batches_and_action_counts(memory, batch, nA):
+    """The multi-launch TD form (k_td_pass1 / k_td_pass2, batches above 4096) and the one-launch form with action
+    counts other than Atari's 18, against the oracle's float32 restatement of utils.py:71-80; then the leaves."""
+    size = 1 << 15
+    rng = np.random.default_rng(batch + nA)
+    buf = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    fill_device(buf, size, (16,), rng_seed=3, chunk=1 << 15)
+    idx = torch.as_tensor(rng.integers(0, size, size=batch)).cuda()
+    f32 = lambda *s: torch.as_tensor(rng.standard_normal(s).astype(np.float32)).cuda()
+    q, qn, qt = f32(batch, nA), f32(batch, nA), f32(batch, nA)
+    a = torch.as_tensor(rng.integers(0, nA, size=batch)).cuda()
+    r, d, w = f32(batch), torch.as_tensor((rng.random(batch) < 0.1).astype(np.float32)).cuda(), f32(batch).abs()
+    before = buf._it_sum._value[size:].copy()
+    loss, prio, td = buf.td_priority_update(q, qn, qt, a, r, d, w, 3, 0.99, idx=idx)
+    ol, op, otd = po.td_priorities(q.cpu().numpy(), qn.cpu().numpy(), qt.cpu().numpy(), a.cpu().numpy(), r.cpu().numpy(),
+                                   d.cpu().numpy(), w.cpu().numpy(), 3, 0.99)
+    np.testing.assert_allclose(prio.cpu().numpy(), op, rtol=RTOL)
+    np.testing.assert_allclose(td.cpu().numpy(), otd, rtol=RTOL, atol=1e-7)
+    np.testing.assert_allclose(float(loss), float(ol), rtol=1e-4)
+    sv, mv = buf._it_sum._value, buf._it_min._value
+    want = po.apply_updates(before, idx.cpu().numpy(), po.pow_alpha(prio.double().cpu().numpy(), 0.6))
+    assert np.abs(bits(sv[size:]).astype(np.int64) - bits(want).astype(np.int64)).max() <= 2
+    assert np.array_equal(bits(sv)[1:], bits(po.build_tree(sv[size:], "sum"))[1:])
+    assert np.array_equal(bits(mv)[1:], bits(po.build_tree(mv[size:], "min"))[1:])
+
+
+@pytest.mark.parametrize("batch", [256, 6000])
+def test_td_nan_and_bad_action_are_reported(memory, batch):
+    """torch.max propagates a NaN TD error into every priority of the batch (utils.py:77) and update_priorities
+    then asserts priority > 0 (memory.py:315): here every priority comes out NaN, nothing is written to the trees
+    and the status word says so.  An action outside [0, nA) is reported as a bad index instead of reading another row."""
+    size = 4096
+    buf = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    fill_device(buf, size, (16,), rng_seed=4)
+    g = torch.Generator(device="cuda").manual_seed(batch)
+    q, qn, qt = (torch.randn(batch, 18, device="cuda", generator=g) for _ in range(3))
+    a = torch.randint(0, 18, (batch,), device="cuda", generator=g)
+    r, d, w = torch.randn(batch, device="cuda", generator=g), torch.zeros(batch, device="cuda"), torch.ones(batch, device="cuda")
+    idx = torch.randint(0, size, (batch,), device="cuda", generator=g)
+    before = buf._it_sum._value.copy()
+    q_nan = q.clone()
+    q_nan[batch // 2, int(a[batch // 2])] = float("nan")
+    _, prio, _ = buf.td_priority_update(q_nan, qn, qt, a, r, d, w, 3, 0.99, idx=idx)
+    assert bool(torch.isnan(prio).all())
+    with pytest.raises(AssertionError, match="priority > 0"):
+        buf._raise_status()
+    assert np.array_equal(bits(buf._it_sum._value), bits(before))
+    a_bad = a.clone()
+    a_bad[3] = 18
+    buf.td_priority_update(q, qn, qt, a_bad, r, d, w, 3, 0.99, idx=None)
+    with pytest.raises(AssertionError, match="idx"):
+        buf._raise_status()
+
+
+# --------------------------------------------------------------- uniform sampler, tree views, graph replay
+def test_uniform_replay_buffer_sample_matches_the_oracle(memory):
+    """ReplayBuffer.sample (memory.py:184-205): indices from random.randint on the global RNG, rows stacked."""
+    import random
+    rng = np.random.default_rng(12)
+    size, n = 500, 730  # wraps
+    buf = memory.ReplayBuffer(size)
+    ora = po.ReplayOracle(size, 0.0, "per")
+    for i in range(n):
+        row = (rng.integers(0, 256, size=(3, 4), dtype=np.uint8), int(rng.integers(0, 6)), float(rng.standard_normal()),
+               rng.integers(0, 256, size=(3, 4), dtype=np.uint8), float(i % 7 == 0))
+        buf.add(*row)
+        ora.add(*row)
+    assert len(buf) == len(ora) == size and buf._next_idx == ora.cursor == n % size
+    for batch in (1, 32, 700):
+        random.seed(batch)
+        got = buf.sample(batch)
+        random.seed(batch)
+        idxes = [random.randint(0, len(ora) - 1) for _ in range(batch)]  # memory.py:204
+        want = ora.gather(idxes)
+        assert len(got) == 5
+        for gcol, wcol in zip(got, want):
+            assert gcol.shape == wcol.shape
+            assert np.array_equal(gcol, np.asarray(wcol, dtype=gcol.dtype))
+
+
+def test_tree_views_read_single_leaves_and_ranges(memory):
+    """`buffer._it_sum[idx]`, `_it_sum.sum(start, end)`, `_it_min.min(...)` (memory.py:244,289,293) on the buffer's
+    own trees, against the oracle's trees after the same adds."""
+    rng = np.random.default_rng(3)
+    size = 300  # 512 leaves
+    buf = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    ora = po.ReplayOracle(size, 0.6, "apex")
+    o = np.zeros((2, 2), dtype=np.uint8)
+    for i in range(size):
+        p = float(abs(rng.standard_normal()) + 1e-3)
+        buf.add(o, 0, 0.0, o, 0.0, p)
+        ora.add(o, 0, 0.0, o, 0.0, p)
+    for k in (0, 1, 77, 299, 300, 511):
+        assert bits(buf._it_sum[k]) == bits(ora.sum_tree.get(k)) and bits(buf._it_min[k]) == bits(ora.min_tree.get(k))
+    with pytest.raises(AssertionError):
+        buf._it_sum[512]
+    for a, b in ((0, None), (0, 299), (5, 123), (100, 101), (0, -1), (17, -200)):
+        assert bits(buf._it_sum.sum(a, b)) == bits(ora.sum_tree.reduce(a, b))
+        assert bits(buf._it_min.min(a, b)) == bits(ora.min_tree.reduce(a, b))
+    assert bits(buf._it_sum.sum()) == bits(ora.sum_tree.reduce()) and bits(buf._it_min.min()) == bits(ora.min_tree.reduce())
+
+
+def test_update_priorities_replayed_from_a_cuda_graph(memory):
+    """A captured per_update_priorities call on an arbitrary (unsorted, duplicated) index buffer, replayed while the
+    buffer's contents change: the arbitration state a replay leaves behind must not decide the next one."""
+    import per_native as pn
+    size, n = 1 << 14, 900
+    buf = memory.PrioritizedReplayBuffer(size, 0.6)
+    fill_device(buf, size, (16,), rng_seed=6, with_prio=False)
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    idx = torch.zeros(n, dtype=torch.int64, device="cuda")
+    pr = torch.ones(n, dtype=torch.float64, device="cuda")
+    rounds = []
+    for r in range(4):
+        i = torch.randint(0, size, (n,), dtype=torch.int64, device="cuda", generator=gen)
+        if r % 2 == 0:
+            i[n - 60:] = i[0]                # a leaf with many duplicates: its winner is a late item ...
+        else:
+            i[5] = rounds[-1][0][0]          # ... and next round the same leaf appears once, early
+        rounds.append((i, torch.rand(n, dtype=torch.float64, device="cuda", generator=gen) + 1e-3))
+    leaves = buf._it_sum._value[size:].copy()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            pn.check(pn.lib.per_update_priorities(buf._h, pn.ptr(idx), pn.ptr(pr), pn.PRIO_F64, n, pn.stream_ptr(side)))
+    torch.cuda.current_stream().wait_stream(side)
+    for i, p in rounds:
+        idx.copy_(i)
+        pr.copy_(p)
+        g.replay()
+        leaves = po.apply_updates(leaves, i.cpu().numpy(), po.pow_alpha(p.cpu().numpy(), 0.6))
+    torch.cuda.synchronize()
+    sv = buf._it_sum._value
+    assert np.abs(bits(sv[size:]).astype(np.int64) - bits(leaves).astype(np.int64)).max() <= 2
+    assert np.array_equal(bits(sv)[1:], bits(po.build_tree(sv[size:], "sum"))[1:])

@@ -7,8 +7,10 @@ seg_create, and works on node arrays the caller owns.
 Collected last on purpose (file name): a run that stops at the first failure has then
 already run every other test.  The check: same batches through the existing entry point
 (seg_create + seg_set) and through the new one, called through the C ABI, two calls in a row
-on the same arrays (the second call sees the stamps the first one left behind); the node
-arrays must be identical bit for bit — the tolerance the other tree tests use.
+on the same arrays (the second call works in the array the first one used); the node
+arrays must be identical bit for bit — the tolerance the other tree tests use.  Further cases: trees of
+different sizes taking turns on the shared array, a call without a status word, and the same call replayed
+from a CUDA graph over changing, duplicated indices (the shared array must be back to all-zero after every call).
 """
 import ctypes as C
 
@@ -108,3 +110,73 @@ def test_noalloc_rejects_oversize_and_bad_shapes(native):
     assert rc == pn.PER_ERR_ASSERT  # capacity must be a power of two, like memory.py:34
     rc = pn.lib.seg_set_noalloc(dev.index, None, None, 64, pn.ptr(idx), pn.ptr(one), 1, None, pn.stream_ptr())
     assert rc == pn.PER_ERR_ARG
+
+
+def test_noalloc_trees_of_different_sizes_take_turns(native):
+    """Two trees of different capacity share the one static array: calls alternate between them, with
+    index sets that overlap in their low leaves; each tree must match its own seg_set reference."""
+    pn = native
+    dev = torch.device("cuda", torch.cuda.current_device())
+    caps = (1 << 10, 1 << 14)
+    gen = torch.Generator(device=dev).manual_seed(5)
+    batches = {c: [] for c in caps}
+    for r in range(3):
+        for c in caps:
+            n = 700
+            idx = torch.randint(0, 1 << 10, (n,), dtype=torch.int64, device=dev, generator=gen)  # same low leaves in both trees
+            idx[:100] = idx[300:400]
+            batches[c].append((idx, torch.rand(n, dtype=torch.float64, device=dev, generator=gen) + 1e-9))
+    nodes = {c: torch.zeros(2 * c, dtype=torch.float64, device=dev) for c in caps}
+    for r in range(3):
+        for c in caps:  # alternate: a, b, a, b, ...
+            idx, val = batches[c][r]
+            pn.check(pn.lib.seg_set_noalloc(dev.index, pn.ptr(nodes[c]), None, c, pn.ptr(idx), pn.ptr(val), idx.numel(),
+                                            None, pn.stream_ptr()))  # no status word: the library's own fallback word is used
+    torch.cuda.synchronize()
+    for c in caps:
+        assert np.array_equal(bits(nodes[c]), bits(reference_nodes(pn, c, pn.TREE_SUM, batches[c], dev)))
+
+
+def test_noalloc_replayed_from_a_cuda_graph(native):
+    """One captured call, replayed while the contents of its index / value buffers change between replays
+    (duplicates included).  Every replay must behave like a fresh call: nothing a replay leaves in the
+    shared array may decide the next one."""
+    pn = native
+    dev = torch.device("cuda", torch.cuda.current_device())
+    cap, n = 1 << 12, 600
+    gen = torch.Generator(device=dev).manual_seed(11)
+    idx = torch.zeros(n, dtype=torch.int64, device=dev)
+    val = torch.zeros(n, dtype=torch.float64, device=dev)
+    nodes = torch.zeros(2 * cap, dtype=torch.float64, device=dev)
+    status = torch.zeros(1, dtype=torch.int64, device=dev)
+
+    def call(stream):
+        pn.check(pn.lib.seg_set_noalloc(dev.index, pn.ptr(nodes), None, cap, pn.ptr(idx), pn.ptr(val), n, pn.ptr(status),
+                                        pn.stream_ptr(stream)))
+
+    rounds = []
+    for r in range(4):
+        i = torch.randint(0, cap, (n,), dtype=torch.int64, device=dev, generator=gen)
+        # round r: a leaf that had many duplicates (late winner) in round r-1 now appears once, early in the batch
+        i[n - 50:] = i[0] if r % 2 == 0 else i[n - 50:]
+        if r % 2 == 1:
+            i[3] = rounds[-1][0][0]
+        rounds.append((i, torch.rand(n, dtype=torch.float64, device=dev, generator=gen) + 1e-9))
+    idx.copy_(rounds[0][0])
+    val.copy_(rounds[0][1])
+    call(torch.cuda.current_stream())  # first call on the device happens outside the capture (address look-up)
+    nodes.zero_()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            call(side)
+    torch.cuda.current_stream().wait_stream(side)
+    for i, v in rounds:
+        idx.copy_(i)
+        val.copy_(v)
+        g.replay()
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0
+    assert np.array_equal(bits(nodes), bits(reference_nodes(pn, cap, pn.TREE_SUM, rounds, dev)))
