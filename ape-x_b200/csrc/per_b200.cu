@@ -358,7 +358,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
         }                                                                                          \
     } while (0)
     TRY_ALLOC(b->stamps, sizeof(u64) * cap);
-    TRY_ALLOC(b->scal, sizeof(u64) * 24);
+    TRY_ALLOC(b->scal, sizeof(u64) * 48);
     TRY_ALLOC(b->obs, b->obs_stride * ring_size);
     TRY_ALLOC(b->next, b->obs_stride * ring_size);
     TRY_ALLOC(b->extra, b->extra_stride * ring_size);
@@ -369,7 +369,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
-    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 24, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 48, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
@@ -661,10 +661,10 @@ int per_timeline(per_buffer *b, int64_t *h_out, int64_t max_entries, int64_t *h_
     return PER_OK;
 }
 
-int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream) {
-    if (!b || !h_out6) return fail(PER_ERR_ARG, "per_update_trace: bad argument");
+int per_update_trace(per_buffer *b, int64_t *h_out16, void *stream) {
+    if (!b || !h_out16) return fail(PER_ERR_ARG, "per_update_trace: bad argument");
     DeviceGuard g(b->device);
-    PER_CUDA(cudaMemcpyAsync(h_out6, b->scal + 11, sizeof(u64) * 6, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PER_CUDA(cudaMemcpyAsync(h_out16, b->scal + 11, sizeof(u64) * 16, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     PER_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     return PER_OK;
 }

@@ -194,8 +194,66 @@ __device__ __forceinline__ void dense_load(const TreeRef &t, int64_t a, int k, d
         if (t.mnn) s_min[n + i] = ldcg_f64(t.mnn + (a << k) + i);
     }
 }
+// The 10-generation rebuild of a 1 024-node row by a 1 024-thread CTA, shaped for what bounds it: instruction issue
+// (all 32 warps walking the generations in lock step issue ~5 000 warp instructions for 2 046 useful operations and meet
+// at ten barriers) and shared-memory banks (a thread that walks 16 consecutive nodes alone makes every access a 32-way
+// conflict).  Here 8 warps take the sum tree and 8 the min tree; a thread loads 4 consecutive row nodes (two 16-byte
+// loads, conflict-free), folds two generations in registers, and the warp folds five more through xor-shuffles (the
+// lane whose bit is clear holds the LEFT child; both lanes form left (op) right): seven generations without a barrier.
+// The 8 nodes that are left per tree go to the root in one warp each.  Every node is op(left, right) of its children in
+// that order (memory.py:82-87): same bits as the level-by-level form below.
+template <bool IS_SUM>
+__device__ __forceinline__ void dense_fast10_tree(double *s, const int w /* warp of this tree, 0..7 */, const int lane) {
+    auto op = [](double x, double y) { return IS_SUM ? __dadd_rn(x, y) : fmin(x, y); };
+    const int i = w * 32 + lane;  // 4 row nodes per thread: 1024 + 4 i ..
+    const double2 c0 = *reinterpret_cast<const double2 *>(s + 1024 + 4 * i);
+    const double2 c1 = *reinterpret_cast<const double2 *>(s + 1024 + 4 * i + 2);
+    const double g1a = op(c0.x, c0.y), g1b = op(c1.x, c1.y);
+    *reinterpret_cast<double2 *>(s + 512 + 2 * i) = make_double2(g1a, g1b);
+    double v = op(g1a, g1b);
+    s[256 + i] = v;
+#pragma unroll
+    for (int g = 1; g <= 5; ++g) {  // generations 3..7: row 256 -> 8
+        const double o = __shfl_xor_sync(0xffffffffu, v, 1 << (g - 1));
+        const bool left = ((lane >> (g - 1)) & 1) == 0;
+        v = left ? op(v, o) : op(o, v);
+        if ((lane & ((1 << g) - 1)) == 0) s[(256 >> g) + (i >> g)] = v;
+    }
+}
+template <bool IS_SUM>
+__device__ __forceinline__ void dense_fast10_top(double *s, const int lane) {  // row of 8 at s[8..15] -> root
+    auto op = [](double x, double y) { return IS_SUM ? __dadd_rn(x, y) : fmin(x, y); };
+    double v = lane < 8 ? s[8 + lane] : 0.0;
+#pragma unroll
+    for (int g = 1; g <= 3; ++g) {
+        const double o = __shfl_xor_sync(0xffffffffu, v, 1 << (g - 1));
+        const bool left = ((lane >> (g - 1)) & 1) == 0;
+        v = left ? op(v, o) : op(o, v);
+        if (lane < 8 && (lane & ((1 << g) - 1)) == 0) s[(8 >> g) + (lane >> g)] = v;
+    }
+}
+__device__ __forceinline__ void dense_build_fast10(const TreeRef &t, double *s_sum, double *s_min) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp < 8) {
+        if (t.sum) dense_fast10_tree<true>(s_sum, warp, lane);
+    } else if (warp < 16) {
+        if (t.mnn) dense_fast10_tree<false>(s_min, warp - 8, lane);
+    }
+    __syncthreads();
+    if (warp == 0) {
+        if (t.sum) dense_fast10_top<true>(s_sum, lane);
+    } else if (warp == 8) {
+        if (t.mnn) dense_fast10_top<false>(s_min, lane);
+    }
+    __syncthreads();
+}
+
 // Expects the bottom row in s_sum / s_min [n, 2n) and a CTA barrier behind the stores that filled it; ends with a barrier.
 __device__ __forceinline__ void dense_build(const TreeRef &t, int64_t a, int k, double *s_sum, double *s_min) {
+    if (k == 10 && blockDim.x == 1024) {
+        dense_build_fast10(t, s_sum, s_min);
+        return;
+    }
     // all generations in shared memory first (CTA barriers down to 32 nodes, then one warp) ...
 #pragma unroll 1
     for (int j = k - 1; j >= 5; --j) {
@@ -373,16 +431,47 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         // the target network's rows as well when both fit: Q_target(s', argmax) then needs no dependent global load
         const bool staged_t = staged && (int64_t)2 * cnt * nA <= UPD_STAGE_FLOATS;
         if (staged) {
+            // The slice's rows are one contiguous block of cnt * nA floats per table: 16-byte loads, up to three per
+            // thread and table requested before the first one is stored (a slice of 512 rows, the 8-GPU case, in one
+            // round trip instead of one per 1 024 floats).
             const float *src = td.q_next + (int64_t)lo * nA;
             const float *src_t = td.q_tgt + (int64_t)lo * nA;
+            const int nf = cnt * nA;
+            if ((nf & 3) == 0 && ((((uintptr_t)src) | ((uintptr_t)src_t)) & 15) == 0) {
+                const int nv = nf >> 2;
+                const float4 *s4 = reinterpret_cast<const float4 *>(src), *t4 = reinterpret_cast<const float4 *>(src_t);
+                float4 *d4 = reinterpret_cast<float4 *>(s_q), *dt4 = reinterpret_cast<float4 *>(s_q + nf);
 #pragma unroll 1
-            for (int e = tid; e < cnt * nA; e += T) {
-                s_q[e] = src[e];
-                if (staged_t) s_q[cnt * nA + e] = src_t[e];
+                for (int base = tid; base < nv; base += 3 * T) {
+                    float4 x[3], y[3];
+#pragma unroll
+                    for (int u = 0; u < 3; ++u) {
+                        const int e = base + u * T;
+                        if (e < nv) {
+                            x[u] = s4[e];
+                            if (staged_t) y[u] = t4[e];
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 3; ++u) {
+                        const int e = base + u * T;
+                        if (e < nv) {
+                            d4[e] = x[u];
+                            if (staged_t) dt4[e] = y[u];
+                        }
+                    }
+                }
+            } else {
+#pragma unroll 1
+                for (int e = tid; e < nf; e += T) {
+                    s_q[e] = src[e];
+                    if (staged_t) s_q[nf + e] = src_t[e];
+                }
             }
         }
         if (have) q_a = td.q[b * nA + act_b];
         __syncthreads();
+        UPD_TRACE(6);
         float mx = 0.0f, acc = 0.0f;
         if (have) {
             const float *qn = staged ? s_q + tid * nA : td.q_next + b * nA;
@@ -407,6 +496,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             f_red[32 + (tid >> 5)] = acc;
         }
         __syncthreads();
+        UPD_TRACE(7);
         if (tid < 32) {
             float m = tid < nwarp ? f_red[tid] : 0.0f;
             float l = tid < nwarp ? f_red[32 + tid] : 0.0f;
@@ -419,6 +509,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
         }
         cl.sync();
+        UPD_TRACE(8);
         if (tid < 32) {
             // one warp per CTA fetches the per-CTA partials from CTA 0 (DSMEM moves ~17 B/cycle: 4096 threads
             // reading them all would cost microseconds) and leaves the batch max in local shared memory
@@ -434,6 +525,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
         }
         __syncthreads();
+        UPD_TRACE(9);
         mx = f_red[32];
 #pragma unroll 1
         for (int i = tid; i < cnt; i += T) {
@@ -529,6 +621,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
         }
         __syncthreads();
+        UPD_TRACE(10);
         int m = 0;  // survivors of this CTA
         for (int w = 0; w < SORT_SLICE_MAX / 32; ++w) m += S.warp_cnt[w];
         if (tid < SORT_SLICE_MAX && kk >= 0) {  // compact: surviving leaves, still ascending
@@ -616,6 +709,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
                 }
             }
         }
+        UPD_TRACE(11);
         cl.sync();  // every CTA's leaves and unshared ancestors are in global memory
         UPD_TRACE(3);
         UPD_TRACE(4);
@@ -739,6 +833,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
             dense_load(a.t, 1, top, s_sum, s_min);
             __syncthreads();
+            UPD_TRACE(12);
             const bool chains = s_srt[SRT_CHAINS] != 0;  // some node below the dense top is shared between CTAs (a sample that crowds)
             if (chains) {
                 if (tid < UPD_MAX_CTAS * SORT_CLIMB_MAX) {  // children of every chain node: one round trip
@@ -826,6 +921,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
                                a.publish_to ? __ldcg(a.d_epoch) + 1 : 0);
         }
         dense_write(a.t, 1, top, s_sum, s_min);
+        UPD_TRACE(13);
         if (tl_on) tl_stamp(a.tl, 3, 9);
     }
 }

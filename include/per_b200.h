@@ -382,10 +382,13 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * No reference counterpart. */
 int per_tune(per_buffer *b, const char *key, int64_t value);
 
-/* Diagnostics: after per_tune(b, "update_trace", 1) the one-launch update kernel stores the GPU
- * global timer (ns) at its phase boundaries {start, TD done, arbitration done, leaves written,
- * sparse rounds done, top rebuilt}; this reads the six stamps of the last launch.  Synchronises. */
-int per_update_trace(per_buffer *b, int64_t *h_out6, void *stream);
+/* Diagnostics: after per_tune(b, "update_trace", 1) thread 0 of CTA 0 of the one-launch update kernel stores the GPU
+ * global timer (ns) at its phase boundaries; this reads the 16 stamps of the last launch (0 where a phase did not
+ * run): [0] past the launch wait, [1] TD done, [2] arbitration done, [3] leaves written / cluster barrier passed,
+ * [4] sparse rounds done, [5] top rebuilt, and finer ones: [6] TD inputs staged, [7] CTA maximum known,
+ * [8] cluster barrier of the TD phase passed, [9] batch maximum known, [10] sorted path: leaves and siblings in,
+ * [11] sorted path: climb done, [12] dense top loaded, [13] dense top written out.  Synchronises. */
+int per_update_trace(per_buffer *b, int64_t *h_out16, void *stream);
 /* Diagnostics: after per_tune(b, "timeline", entries) thread 0 of CTA 0 of every sample / gather /
  * update launch stores, into the six entries that launch owns (plain stores, nothing waits for
  * them; a launch captured in a CUDA graph keeps its entries across replays, so after a run the

@@ -1,3 +1,3 @@
-set -x
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/r2_t2.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/r2_t2.log
-timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --timeline > gpurun_out/r2_bench2.json 2> gpurun_out/r2_bench2.err; echo "bench rc=$?"; cut -c1-300 gpurun_out/r2_bench2.json; tail -3 gpurun_out/r2_bench2.err | cut -c1-900
+for K in 20 200; do
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps $K --warmup 5 --timeline > gpurun_out/r2_bench_n8_k$K.json 2> gpurun_out/r2_bench_n8_k$K.err; echo "bench rc=$?"; cut -c1-220 gpurun_out/r2_bench_n8_k$K.json; grep -E "parity ok on rank 0|rank 0 timeline|rank 7 timeline" gpurun_out/r2_bench_n8_k$K.err | cut -c1-800
+done

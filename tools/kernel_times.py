@@ -86,7 +86,7 @@ for B in args.batch:
     for _ in range(50):
         lib.per_td_priority_update(h, P(q), P(qn), P(qt), 18, P(act), P(rew), P(done), P(w32), 0.97, P(idx), B, P(o_prio), None,
                                    P(o_loss), sp)
-        st6 = (pn.C.c_int64 * 6)()
+        st6 = (pn.C.c_int64 * 16)()
         pn.check(lib.per_update_trace(h, st6, sp))
         tr.append([st6[i + 1] - st6[i] for i in range(5)])
     pn.check(lib.per_tune(h, b"update_trace", 0))

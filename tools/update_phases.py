@@ -1,0 +1,55 @@
+"""Fine-grained phase stamps of k_update_cluster (per_update_trace, GPU global timer, thread 0 of CTA 0): sample ->
+fused TD + update of that sample, plain launches, median over many launches.
+Usage: python tools/update_phases.py [--cap 1048576] [--batch 512 4096]"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "ape-x_b200")]
+import numpy as np
+import torch
+
+import __graft_entry__ as entry
+
+entry.build()
+import memory
+import per_native as pn
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--cap", type=int, default=1 << 20)
+ap.add_argument("--batch", type=int, nargs="+", default=[512, 1024, 4096])
+ap.add_argument("--iters", type=int, default=200)
+args = ap.parse_args()
+dev = torch.device("cuda")
+buf = memory.CustomPrioritizedReplayBuffer(args.cap, 0.6)
+gen = torch.Generator(device=dev).manual_seed(0)
+for lo in range(0, args.cap, 1 << 16):
+    m = min(1 << 16, args.cap - lo)
+    o = torch.zeros((m, 16), dtype=torch.uint8, device=dev)
+    buf.add_batch_device(o, o, torch.zeros(m, dtype=torch.int64, device=dev), torch.zeros(m, device=dev),
+                         torch.zeros(m, device=dev), priorities=torch.rand(m, dtype=torch.float64, device=dev, generator=gen) + 1e-3)
+h, lib, P = buf._h, pn.lib, pn.ptr
+sp = pn.stream_ptr()
+pn.check(lib.per_tune(h, b"update_trace", 1))
+NAMES = ["wait passed", "TD done", "arbitration", "leaves/barrier", "rounds done", "top rebuilt", "TD staged", "CTA max", "TD cl.sync",
+         "batch max", "leaves+sib in", "climb done", "top loaded", "top written", "-", "-"]
+ORDER = [0, 6, 7, 8, 9, 1, 10, 2, 11, 3, 4, 12, 5, 13]
+for B in args.batch:
+    u = [torch.rand(B, dtype=torch.float64, device=dev, generator=gen) for _ in range(8)]
+    idx = torch.empty(B, dtype=torch.int64, device=dev)
+    w32 = torch.empty(B, device=dev)
+    q, qn, qt = (torch.randn(B, 18, device=dev, generator=gen) for _ in range(3))
+    act = torch.randint(0, 18, (B,), device=dev, generator=gen)
+    rew, done = torch.randn(B, device=dev, generator=gen), torch.zeros(B, device=dev)
+    o_prio, o_loss = torch.empty(B, device=dev), torch.empty(1, device=dev)
+    rows, clk = [], []
+    for it in range(args.iters):
+        pn.check(lib.per_sample_indices(h, P(u[it % 8]), B, 0.4, P(idx), None, P(w32), sp))
+        pn.check(lib.per_td_priority_update(h, P(q), P(qn), P(qt), 18, P(act), P(rew), P(done), P(w32), 0.97, P(idx), B, P(o_prio),
+                                            None, P(o_loss), sp))
+        st = (pn.C.c_int64 * 16)()
+        pn.check(lib.per_update_trace(h, st, sp))
+        rows.append([st[i] - st[0] for i in range(16)])
+    med = np.median(np.array(rows[20:]), axis=0) / 1e3
+    print("batch %d: " % B + " | ".join("%s %.2f" % (NAMES[i], med[i]) for i in ORDER if med[i] > 0 or i == 0))
