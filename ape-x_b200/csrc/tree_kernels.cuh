@@ -553,7 +553,7 @@ __device__ __forceinline__ void owned_strata(const SampleArgs &a, const ShardVie
     else hi = first_stratum_search(a, v, a.rank + 1, lane);
 }
 
-constexpr int SAMPLE_THREADS = 512;  // few, large CTAs: warp 0 of each polls the mailbox flags while the update kernel in front still runs
+constexpr int SAMPLE_THREADS = 128;  // one CTA per 4 owned strata: the descents spread over ~160 SMs (512-thread CTAs: +1 us per step, A/B in profiles/r02_notes.md)
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
     __shared__ double s_top[32];

@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libper_b200.so")
+LIB_PATH = os.environ.get("PER_B200_LIB") or os.path.join(_HERE, "libper_b200.so")  # override: A/B runs of two builds
 
 PER_OK, PER_ERR_ASSERT, PER_ERR_CUDA, PER_ERR_ARG, PER_ERR_NOMEM = 0, -1, -2, -3, -4
 STATUS_BAD_PRIORITY, STATUS_BAD_INDEX, STATUS_BAD_PREFIXSUM, STATUS_NSTEP_EMPTY = 1, 2, 4, 8

@@ -672,8 +672,10 @@ def main():
         else:
             pn.check(lib.per_sample_indices(h, u_ptrs[(7 * i + 3) % n_u], GB, BETA, P(idx_sets[i]), None, a_w32, sp))
     torch.cuda.synchronize()
-    rows_per_set = [int((t >= 0).sum().item()) for t in idx_sets]
-    pdl_default = 3
+    if world > 1:  # this rank's rows of each sample, as a dense index list (strata of other ranks hold -1)
+        idx_sets = [t[t >= 0].contiguous() for t in idx_sets]
+    rows_per_set = [int(t.numel()) for t in idx_sets]
+    pdl_default = 3 if world == 1 else 7
     pn.check(lib.per_tune(h, b"pdl", 0))
     gather_ms = None
     try:
@@ -683,7 +685,7 @@ def main():
 
             def gather_block():
                 for i in range(M_SETS):
-                    rc = lib.per_gather(h, P(idx_sets[i]), GB, P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp_side)
+                    rc = lib.per_gather(h, P(idx_sets[i]), rows_per_set[i], P(o_obs), P(o_nxt), P(o_act), P(o_rew), P(o_done), None, sp_side)
                     if rc:
                         pn.check(rc)
             gather_block()

@@ -366,7 +366,7 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * normal use; defaults are the measured best).  Keys: "gather_mode" (0 TMA bulk copies
  * through shared memory, 1 register-staged LDG/STG), "gather_warps", "gather_stages",
  * "gather_piece" (bytes, multiple of 16), "gather_ctas_per_sm"; "update_trace" (0/1, see
- * per_update_trace); "pdl" (bit mask, default 3: 1 = sampling kernels, 2 = gather, 4 = the one-launch
+ * per_update_trace); "pdl" (bit mask, default 3, 7 on a shard of a sharded replay: 1 = sampling kernels, 2 = gather, 4 = the one-launch
  * update are launched with programmatic stream serialization and begin with
  * griddepcontrol.wait, so their launch and prologue overlap the tail of the kernel in front;
  * measured on B200 the cluster launch of the update loses from it, profiles/r01_notes.md);
