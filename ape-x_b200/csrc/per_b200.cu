@@ -681,6 +681,16 @@ int per_shard_publish(per_buffer *b, int64_t global_len, void *stream) {
     return PER_OK;
 }
 
+int per_shard_deliver(per_buffer *b, const int64_t *d_idx, const float *d_w32, int64_t batch, int64_t *d_dst_idx,
+                      float *d_dst_w32, void *stream) {
+    if (!b || !d_idx || batch < 0 || (!d_dst_idx && !d_dst_w32)) return fail(PER_ERR_ARG, "per_shard_deliver: bad argument");
+    if (batch == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    k_shard_deliver<<<grid_for(batch, 256, b->sm_count), 256, 0, (cudaStream_t)stream>>>(d_idx, d_w32, batch, d_dst_idx, d_dst_w32);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
 int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u, int64_t batch, double beta,
                        int64_t global_len, int64_t *d_out_idx, double *d_out_w64, float *d_out_w32, void *stream) {
     if (!b || batch <= 0 || !d_u || !d_out_idx || (!d_records && !b->mailbox))

@@ -553,6 +553,18 @@ __device__ __forceinline__ void owned_strata(const SampleArgs &a, const ShardVie
     else hi = first_stratum_search(a, v, a.rank + 1, lane);
 }
 
+// Learner-ward delivery of a sharded sample's scalars: the strata this shard owns (idx != -1) are copied into the
+// learner GPU's full-batch index / weight arrays (peer-mapped: plain stores over NVLink).  Strata of other shards are
+// left alone, their owners write them.
+__global__ void k_shard_deliver(const int64_t *idx, const float *w32, int64_t n, int64_t *dst_idx, float *dst_w32) {
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = idx[q];
+        if (k == -1) continue;
+        if (dst_idx) dst_idx[q] = k;
+        if (dst_w32 && w32) dst_w32[q] = w32[q];
+    }
+}
+
 constexpr int SAMPLE_THREADS = 128;  // one CTA per 4 owned strata: the descents spread over ~160 SMs (512-thread CTAs: +1 us per step, A/B in profiles/r02_notes.md)
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {

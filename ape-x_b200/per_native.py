@@ -66,6 +66,7 @@ SIGNATURES = {
     "per_ipc_free": (C.c_int, [C.c_int, _p]),
     "per_shard_attach_exchange": (C.c_int, [_p, _p, _p]),
     "per_shard_publish": (C.c_int, [_p, _i64, _p]),
+    "per_shard_deliver": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p]),
     "per_shard_exchange_stats": (C.c_int, [_p, C.POINTER(_i64), _p]),
     "per_sample_sharded": (C.c_int, [_p, _p, _p, _i64, _f64, _i64, _p, _p, _p, _p]),
     "per_capacity": (_i64, [_p]),

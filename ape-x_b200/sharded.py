@@ -100,6 +100,29 @@ class PeerBuffer(object):
         return PeerBuffer(p.value, nbytes, device, False)
 
 
+class LearnerBatch(object):
+    """The learner GPU's batch buffers as every rank sees them: allocated once on `learner_rank` (CUDA IPC),
+    mapped into all other ranks, so that each shard's gather kernel stores the rows it owns straight into the
+    learner's memory over NVLink and the learner's priorities are read back the same way (SURVEY.md section 8e;
+    the reference moves both as pickles over ZeroMQ, origin_repo/replay.py:29-45, origin_repo/learner.py:71-131).
+    Fields (full global batch): obs, next_obs (obs_dtype [B, ...]), act int64, rew / done / weights / prio float32,
+    idx int64.  `local` is True on the learner rank, where the fields are ordinary views of its own memory."""
+    FIELDS = ("obs", "next_obs", "act", "rew", "done", "idx", "weights", "prio")
+
+    def __init__(self, bufs, views, batch, learner_rank, local, group):
+        self.bufs, self.views, self.batch = bufs, views, batch
+        self.learner_rank, self.local, self.group = learner_rank, local, group
+
+    def __getitem__(self, k):
+        return self.views[k]
+
+    def fence(self):
+        """Everything every rank has issued so far has landed (stream sync + barrier over the ranks)."""
+        import torch.distributed as dist
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)
+
+
 def exchange_records(rec, group=None):
     """All-gather of one 4-double record per rank (the only collective of a sample)."""
     import torch.distributed as dist
@@ -242,6 +265,7 @@ class ShardedReplay(object):
         w64 = pre["weights64"] if "weights64" in pre else torch.empty(batch, dtype=torch.float64, device=self.device)
         _n.check(_n.lib.per_sample_sharded(self._h, _n.ptr(recs), _n.ptr(u), batch, float(beta), self._len, _n.ptr(idx),
                                            _n.ptr(w64), _n.ptr(w32), sp))
+        self._bound_idx = idx  # the native side binds this address to the sample until its update: keep it allocated
         res = {"idx": idx, "weights": w32, "weights64": w64, "records": recs}
         if gather:
             res.update(self.gather_device(idx, out))
@@ -262,6 +286,51 @@ class ShardedReplay(object):
         _n.check(_n.lib.per_gather(self._h, _n.ptr(idx), b, _n.ptr(out["obs"]), _n.ptr(out["next_obs"]), _n.ptr(out["act"]),
                                    _n.ptr(out["rew"]), _n.ptr(out["done"]), _n.ptr(out.get("a_mu")), _n.stream_ptr()))
         return out
+
+    # -- learner-ward delivery over NVLink ---------------------------------------------------------
+    def open_learner_batch(self, batch, learner_rank=0, group=None):
+        """Collective, once: the learner rank allocates the batch buffers, everybody maps them."""
+        import torch.distributed as dist
+        el = torch.empty(0, dtype=self.obs_dtype).element_size()
+        row = int(np.prod(self.obs_shape))
+        spec = {"obs": (self.obs_dtype, (batch,) + self.obs_shape, batch * row * el),
+                "next_obs": (self.obs_dtype, (batch,) + self.obs_shape, batch * row * el),
+                "act": (torch.int64, (batch,), batch * 8), "rew": (torch.float32, (batch,), batch * 4),
+                "done": (torch.float32, (batch,), batch * 4), "idx": (torch.int64, (batch,), batch * 8),
+                "weights": (torch.float32, (batch,), batch * 4), "prio": (torch.float32, (batch,), batch * 4)}
+        box = [None]
+        bufs = {}
+        if self.rank == learner_rank:
+            handles = {}
+            for k, (_, _, nb) in spec.items():
+                bufs[k], handles[k] = PeerBuffer.alloc(nb, self.device.index)
+            box = [handles]
+        dist.broadcast_object_list(box, src=learner_rank, group=group)
+        if self.rank != learner_rank:
+            bufs = {k: PeerBuffer.open(box[0][k], spec[k][2], self.device.index) for k in spec}
+        views = {k: bufs[k].view(spec[k][0], spec[k][1]) for k in spec}
+        dist.barrier(group=group)
+        return LearnerBatch(bufs, views, batch, learner_rank, self.rank == learner_rank, group)
+
+    def sample_to_learner(self, lb, beta, uniforms):
+        """One global stratified sample delivered to the learner GPU: this rank samples (the record exchange is in the
+        kernel), gathers the rows it owns straight into the learner's obs / next_obs / act / rew / done, and stores its
+        strata's indices and importance weights into the learner's idx / weights.  Returns this rank's own result dict
+        (idx holds -1 for strata of other ranks) — keep its `idx`: update_from_learner wants that buffer back."""
+        d = self.sample_device(lb.batch, beta, uniforms, gather=False)
+        sp = _n.stream_ptr()
+        _n.check(_n.lib.per_gather(self._h, _n.ptr(d["idx"]), lb.batch, _n.ptr(lb.bufs["obs"]), _n.ptr(lb.bufs["next_obs"]),
+                                   _n.ptr(lb.bufs["act"]), _n.ptr(lb.bufs["rew"]), _n.ptr(lb.bufs["done"]), None, sp))
+        _n.check(_n.lib.per_shard_deliver(self._h, _n.ptr(d["idx"]), _n.ptr(d["weights"]), lb.batch, _n.ptr(lb.bufs["idx"]),
+                                          _n.ptr(lb.bufs["weights"]), sp))
+        return d
+
+    def update_from_learner(self, lb, idx):
+        """The learner has written the batch's new priorities into lb["prio"] (and fenced): every rank applies the
+        entries of the strata it owns, reading them out of the learner's memory over NVLink.  `idx`: the index buffer
+        sample_to_learner returned on this rank."""
+        _n.check(_n.lib.per_update_priorities(self._h, _n.ptr(idx), _n.ptr(lb.bufs["prio"]), _n.PRIO_F32, lb.batch, _n.stream_ptr()))
+        self._rec_fresh = True
 
     # -- update ---------------------------------------------------------------------------------
     def update_priorities_device(self, idx, priorities):

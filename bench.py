@@ -196,11 +196,13 @@ def reference_arm(args, rank):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n_gpus):
-    return {"workload": "Ape-X learner replay step, configs[1]: ring 2^20 Atari transitions per GPU (59.2 GB HBM), "
-                        "batch %d per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions" % BATCH,
-            "ring_per_gpu": RING, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
-            "sharding": "none" if n_gpus == 1 else "one replay of %d x 2^20 transitions cut into %d contiguous slices; "
+def workload_config(n_gpus, ring=None):
+    ring = ring or RING
+    return {"workload": "Ape-X learner replay step, configs[%d]: ring 2^%d Atari transitions per GPU (%.1f GB HBM), "
+                        "batch %d per GPU, alpha 0.6, beta 0.4, n-step 3, 18 actions"
+                        % (3 if (n_gpus == 8 and ring == 1 << 21) else 1, int(np.log2(ring)), ring * 56464 / 1e9, BATCH),
+            "ring_per_gpu": ring, "batch_per_gpu": BATCH, "obs": "uint8[4,84,84]",
+            "sharding": "none" if n_gpus == 1 else "one replay of %d x ring_per_gpu transitions cut into %d contiguous slices; "
                         "per step one exchange of a 32-byte record per rank (peer-memory mailboxes written by the sampling kernel over "
                         "NVLink, or --nccl-exchange), global stratified batch %d" % (n_gpus, n_gpus, BATCH * n_gpus),
             "l2": "inputs (59 GB ring) larger than L2; no flush", "parallelism": "shard%d" % n_gpus}
@@ -345,6 +347,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ring", type=int, default=RING, help="rows per GPU (debug: smaller ring)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--parity-size", type=int, default=40000,
+                    help="world > 1: transitions of the small replay the start-up parity check runs on (configs[3] as written: 16777216)")
     ap.add_argument("--no-parity-check", action="store_true", help="world > 1: skip the start-up parity check against the oracle")
     ap.add_argument("--no-extras", action="store_true", help="skip the AQL and whole-learner-step rows (N=1)")
     ap.add_argument("--global-batch", type=int, default=0,
@@ -484,7 +488,8 @@ def main():
         # a checker only: a small separate replay, before anything is measured)
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import multi_gpu_parity
-        multi_gpu_parity.run_check(rank, world, local_rank, size=40000, steps=4, log=sys.stderr.write)
+        multi_gpu_parity.run_check(rank, world, local_rank, size=args.parity_size, steps=4 if args.parity_size < (1 << 20) else 2,
+                                   log=sys.stderr.write)
         dist.barrier()
     if use_mailbox:
         # self-check: records through the mailboxes must give the indices the all-gathered records give
@@ -822,6 +827,45 @@ def main():
     e2e = {"value": GB * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "steps": e2e_steps, "api": api}
 
+    # ---- learner-ward delivery (SURVEY 8e data movement): every rank's rows into rank 0's memory over NVLink ----------
+    p2p = None
+    if world > 1 and use_mailbox and not args.no_extras:
+        lb = shard.open_learner_batch(GB, learner_rank=0)
+        if rank == 0:
+            lb["prio"].copy_(torch.rand(GB, device=dev) + 1e-3)
+        lb.fence()
+
+        def p2p_step(i):
+            d = shard.sample_to_learner(lb, BETA, u_all[i % n_u])   # sample + gather into the learner's buffers + idx / weights
+            shard.update_from_learner(lb, d["idx"])                 # owned priorities read back over NVLink + tree update
+            return d
+
+        for i in range(5):
+            d_last = p2p_step(i)
+        lb.fence()
+        n_p2p = 50
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(n_p2p):
+            d_last = p2p_step(5 + i)
+        e1.record(stream)
+        lb.fence()
+        p2p_us = max_over_ranks(e0.elapsed_time(e1) * 1e3 / n_p2p)
+        own0 = torch.tensor([int((d_last["idx"] >= 0).sum().item()) if rank == 0 else 0], device=dev)
+        dist.all_reduce(own0)
+        remote_rows = GB - int(own0.item())
+        nv_peak = 770.0  # measured peer copy per direction on this pool (B200_PROFILING.md)
+        p2p = {"us_per_step": p2p_us, "rows_per_s_into_learner": GB / (p2p_us * 1e-6),
+               "rows_crossing_nvlink_per_step": remote_rows,
+               "nvlink_ingest_GBps": remote_rows * (2 * OBS_BYTES + 16) / (p2p_us * 1e-6) / 1e9,
+               "nvlink_peak_GBps": nv_peak, "frac": remote_rows * (2 * OBS_BYTES + 16) / (p2p_us * 1e-6) / 1e9 / nv_peak,
+               "api": "sharded.ShardedReplay.sample_to_learner() / update_from_learner(): rows, indices and weights stored into "
+                      "rank 0's batch buffers by the owners' kernels (CUDA IPC mappings, plain stores over NVLink), priorities read "
+                      "back from rank 0's memory; plain launches, CUDA events, max over ranks",
+               "note": "one learner GPU takes at most ~0.77 TB/s: the sample+update rate of the headline is with every GPU training "
+                       "on the strata it owns"}
+        del lb
+
     # ---- the other measurement rows of SURVEY section 8(d), N = 1 only -------------------------------
     aql_block = learner = None
     if rank == 0 and world == 1 and not args.no_extras:
@@ -873,7 +917,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.global_batch else "weak", "vs_baseline": None,
-            "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world),
+            "dtype": "f64 trees / u8 frames / f32 TD", "data": "synthetic", "config": workload_config(world, ring),
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic if (world == 1 and traffic_kernel == kernel_name) else None,
@@ -890,7 +934,7 @@ def main():
             "cpu_baseline": cpu, "launch": launch_mode, "value_eager_launches": eager_value,
             "learner_step_us": {"total": 1e3 * ms / K, "gather_alone": gather_ms * 1e3},
             "record_exchange_us": exchange_us, "step_anatomy_us": anatomy,
-            "aql": aql_block, "learner_updates_per_s": learner,
+            "aql": aql_block, "learner_updates_per_s": learner, "p2p": p2p,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -352,6 +352,15 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
  * number of times.  per_shard_publish publishes the record for the NEXT sample by itself (used to
  * emulate several ranks on one GPU, where one rank's kernel cannot wait for another's). */
 int per_ipc_alloc(int device, int64_t bytes, void **d_ptr, uint8_t *h_handle64);
+/* Learner-ward delivery (sampled transitions move peer-to-peer to the learner GPU; the reference
+ * ships them as pickles over ZeroMQ, origin_repo/replay.py:38-45, origin_repo/learner.py:71-131).  The row columns get
+ * there by passing peer-mapped output pointers to per_gather; this call does the same for the sample's scalars: for
+ * every stratum this shard owns (d_idx[q] != -1) it stores d_idx[q] / d_w32[q] into the learner's full-batch arrays
+ * d_dst_idx / d_dst_w32 (peer-mapped; either may be NULL).  Returned priorities need no call of their own: hand the
+ * learner's (peer-mapped) priority array to per_update_priorities together with the sample's index buffer and the
+ * update reads just the owned entries over NVLink. */
+int per_shard_deliver(per_buffer *b, const int64_t *d_idx, const float *d_w32, int64_t batch, int64_t *d_dst_idx,
+                      float *d_dst_w32, void *stream);
 int per_ipc_open(int device, const uint8_t *h_handle64, void **d_ptr);
 int per_ipc_close(int device, void *d_ptr);
 int per_ipc_free(int device, void *d_ptr);

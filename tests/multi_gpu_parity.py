@@ -58,8 +58,9 @@ def run_check(rank, world, device, size=40000, batch=None, steps=5, obs_shape=(2
     prio = rng.random(n_add) + 1e-3
     t = lambda a: torch.as_tensor(a).to(dev)
     shard = sharded.ShardedReplay(size, alpha, rank, world, obs_shape=obs_shape, device=dev)
-    for lo in range(0, n_add, 3777):  # uneven chunks that cross slice borders
-        hi = min(n_add, lo + 3777)
+    chunk = max(3777, n_add // 97)   # uneven chunks that cross slice borders
+    for lo in range(0, n_add, chunk):
+        hi = min(n_add, lo + chunk)
         shard.add_batch_device(t(obs[lo:hi]), t(nxt[lo:hi]), t(act[lo:hi]), t(rew[lo:hi]), t(done[lo:hi]), t(prio[lo:hi]))
     shard.enable_peer_exchange()
     cap = po.next_pow2(size)
@@ -130,6 +131,86 @@ def run_check(rank, world, device, size=40000, batch=None, steps=5, obs_shape=(2
     return True
 
 
+def run_p2p_check(rank, world, device, rows_per_gpu=4096, batch=None, steps=3, obs_shape=(4, 84, 84), alpha=0.6, beta=0.4,
+                  seed=21, log=None):
+    """Learner-ward delivery on real peers (SURVEY.md section 8e data movement): every rank's gather stores the rows it
+    owns into rank 0's batch buffers over NVLink, its strata's indices / weights likewise; rank 0 (the learner) checks
+    the complete batch against the single-tree oracle and the stored rows byte for byte, writes new priorities into its
+    own memory, and every rank applies its share by reading them over NVLink; the trees are compared with the oracle's."""
+    import torch
+    import torch.distributed as dist
+
+    import per_native as pn
+    import sharded
+    from oracle import per_oracle as po
+    from oracle import shard_oracle as so
+
+    batch = batch or 256 * world
+    dev = torch.device("cuda", device)
+    size = rows_per_gpu * world
+    rng = np.random.default_rng(seed)
+    obs = rng.integers(0, 256, size=(size,) + obs_shape, dtype=np.uint8)
+    nxt = rng.integers(0, 256, size=(size,) + obs_shape, dtype=np.uint8)
+    act = rng.integers(0, 18, size=size).astype(np.int64)
+    rew = rng.standard_normal(size).astype(np.float32)
+    done = (rng.random(size) < 0.05).astype(np.float32)
+    prio = rng.random(size) + 1e-3
+    t = lambda a: torch.as_tensor(a).to(dev)
+    shard = sharded.ShardedReplay(size, alpha, rank, world, obs_shape=obs_shape, device=dev)
+    for lo in range(0, size, 1024):
+        hi = min(size, lo + 1024)
+        shard.add_batch_device(t(obs[lo:hi]), t(nxt[lo:hi]), t(act[lo:hi]), t(rew[lo:hi]), t(done[lo:hi]), t(prio[lo:hi]))
+    shard.enable_peer_exchange()
+    shard.enable_early_publish()
+    lb = shard.open_learner_batch(batch, learner_rank=0)
+    cap = po.next_pow2(size)
+    cap_l = cap // world
+
+    def single_tree():
+        mine = torch.as_tensor(shard.tree_values(pn.TREE_SUM)[cap_l:]).to(dev)
+        mine_m = torch.as_tensor(shard.tree_values(pn.TREE_MIN)[cap_l:]).to(dev)
+        a, b = [torch.empty_like(mine) for _ in range(world)], [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(a, mine)
+        dist.all_gather(b, mine_m)
+        return po.build_tree(torch.cat(a).cpu().numpy(), "sum"), po.build_tree(torch.cat(b).cpu().numpy(), "min")
+
+    sv, mv = single_tree()
+    for step in range(steps):
+        u = rng.random(batch)
+        if lb.local:
+            for k in ("obs", "next_obs"):
+                lb[k].zero_()
+            lb["idx"].fill_(-7)
+        lb.fence()
+        d = shard.sample_to_learner(lb, beta, torch.as_tensor(u).to(dev))
+        lb.fence()  # every rank's rows, indices and weights are in the learner's memory
+        want = po.descend_many(sv, po.stratified_masses(po.prefix_total(sv, size - 1), batch, u))
+        if lb.local:
+            assert np.array_equal(lb["idx"].cpu().numpy(), want), "indices delivered to the learner differ from the single tree's"
+            np.testing.assert_allclose(lb["weights"].cpu().numpy(), po.is_weights(sv, mv, want, size, beta).astype(np.float32), rtol=1e-5)
+            assert np.array_equal(lb["obs"].cpu().numpy(), obs[want]) and np.array_equal(lb["next_obs"].cpu().numpy(), nxt[want])
+            assert np.array_equal(lb["act"].cpu().numpy(), act[want]) and np.array_equal(lb["rew"].cpu().numpy(), rew[want])
+            assert np.array_equal(lb["done"].cpu().numpy(), done[want])
+            newp = (rng.random(batch) + 1e-3).astype(np.float32)
+            lb["prio"].copy_(torch.as_tensor(newp))
+        else:
+            newp = (rng.random(batch) + 1e-3).astype(np.float32)  # same stream on every rank: the oracle's copy
+        lb.fence()  # the learner's priorities are in place
+        shard.update_from_learner(lb, d["idx"])
+        assert shard.status() == 0
+        exp = po.apply_updates(sv[cap:], want, newp.astype(np.float64) ** alpha)
+        sv, mv = single_tree()
+        np.testing.assert_allclose(sv[cap:], exp, rtol=4e-15)
+        assert np.array_equal(bits(shard.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, rank, world))[1:])
+        assert np.array_equal(bits(shard.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, rank, world))[1:])
+    lb.fence()
+    if log:
+        log("P2P delivery ok on rank %d of %d: %d steps of %d strata gathered into rank 0's buffers over NVLink (rows byte-exact, "
+            "indices = single-tree oracle), priorities read back from the learner's memory, shard trees == subtrees\n" % (rank, world, steps, batch))
+    del shard
+    return True
+
+
 if __name__ == "__main__":
     import torch
     import torch.distributed as dist
@@ -142,6 +223,7 @@ if __name__ == "__main__":
     for early in (False, True):
         run_check(rank, world, local, early_publish=early, seed=3 + int(early), log=sys.stderr.write)
     run_check(rank, world, local, size=(1 << 16) + 77, batch=4096, steps=3, seed=9, log=sys.stderr.write)
+    run_p2p_check(rank, world, local, log=sys.stderr.write)
     dist.barrier()
     dist.destroy_process_group()
     print("rank", rank, "ok")

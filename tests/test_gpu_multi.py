@@ -40,4 +40,4 @@ def test_sharded_replay_on_real_peers_matches_the_single_tree_oracle():
             raise
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, "rank %d failed:\n%s" % (r, o[-3000:])
-        assert "rank %d ok" % r in o and o.count("multi-GPU parity ok") == 3
+        assert "rank %d ok" % r in o and o.count("multi-GPU parity ok") == 3 and o.count("P2P delivery ok") == 1
