@@ -495,6 +495,62 @@ __global__ void __launch_bounds__(GATHER_MAX_WARPS * 32) k_gather_cast(GatherArg
     }
 }
 
+// Gather + widen into CHANNELS-LAST batches: the learner's first layer is a cuDNN convolution
+// (model.py:33, fed by ApeX.py:50,53 / origin_repo/learner.py:102-110), which runs fastest on NHWC tensors.  A stored
+// observation is C planes of `plane` bytes (uint8[4,84,84]: C = 4, plane = 7 056); the output row q holds, for every
+// pixel p, the C widened channel values next to each other: out[q][p][c] = scale * ring[k][c][p].  One thread takes 4
+// consecutive pixels: one 32-bit load per plane (a warp reads 128 contiguous bytes of each plane), four C-wide vector
+// stores (a warp writes 2 KB contiguous at float32).  C == 4 only (the Atari frame stack).
+template <typename OutVec4>
+__device__ __forceinline__ OutVec4 cast4(float a, float b, float c, float d);
+template <>
+__device__ __forceinline__ float4 cast4<float4>(float a, float b, float c, float d) { return make_float4(a, b, c, d); }
+struct BF16x4 { __nv_bfloat162 lo, hi; };
+struct F16x4 { __half2 lo, hi; };
+template <>
+__device__ __forceinline__ BF16x4 cast4<BF16x4>(float a, float b, float c, float d) {
+    BF16x4 r;
+    r.lo = __floats2bfloat162_rn(a, b);
+    r.hi = __floats2bfloat162_rn(c, d);
+    return r;
+}
+template <>
+__device__ __forceinline__ F16x4 cast4<F16x4>(float a, float b, float c, float d) {
+    F16x4 r;
+    r.lo = __floats2half2_rn(a, b);
+    r.hi = __floats2half2_rn(c, d);
+    return r;
+}
+
+template <typename OutVec4>
+__global__ void __launch_bounds__(256) k_gather_cast_nhwc(GatherArgs a, int plane, float scale) {
+    int64_t first_q, last_q;
+    gather_range(a, first_q, last_q);
+    gather_scalars(a, first_q, last_q);
+    const int quads = plane >> 2;                       // 4-pixel groups per plane
+    const int64_t per_class = (last_q - first_q) * quads;
+    const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nthreads = (int64_t)gridDim.x * blockDim.x;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+        if (!a.cast_out[c]) continue;
+        const RowClass &rc = a.rc[c];
+        OutVec4 *out = reinterpret_cast<OutVec4 *>(a.cast_out[c]);
+        for (int64_t w = tid; w < per_class; w += nthreads) {
+            const int64_t q = first_q + w / quads;
+            const int g = (int)(w % quads);
+            const int64_t k = gather_row_of(a, q);
+            if (k < 0) continue;
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(rc.src + k * rc.src_stride) + g;
+            const uint32_t p0 = __ldg(src), p1 = __ldg(src + quads), p2 = __ldg(src + 2 * quads), p3 = __ldg(src + 3 * quads);
+            OutVec4 *dst = out + (q * plane + 4 * (int64_t)g);  // one OutVec4 per pixel
+#pragma unroll
+            for (int px = 0; px < 4; ++px)
+                dst[px] = cast4<OutVec4>(u8_to_f32(p0, px) * scale, u8_to_f32(p1, px) * scale, u8_to_f32(p2, px) * scale,
+                                         u8_to_f32(p3, px) * scale);
+        }
+    }
+}
+
 // Fallback mover for row classes whose size is not a multiple of 16 B (small non-Atari
 // observations, e.g. CartPole's float32[4]): byte-granular, one warp per row.
 __global__ void k_gather_bytes(GatherArgs a) {

@@ -895,6 +895,44 @@ int per_gather_cast(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_
     return PER_OK;
 }
 
+int per_gather_cast_nhwc(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_dtype, float scale, int channels,
+                         void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew, float *d_out_done, void *stream) {
+    if (!b || batch < 0 || (batch && !d_idx) || out_dtype < 0 || out_dtype > 2) return fail(PER_ERR_ARG, "per_gather_cast_nhwc: bad argument");
+    if (channels != 4) return fail(PER_ERR_ARG, "per_gather_cast_nhwc: 4 channels (the Atari frame stack) only, got %d", channels);
+    if (b->obs_bytes % 16 || b->obs_bytes == 0) return fail(PER_ERR_ARG, "per_gather_cast_nhwc: an observation must be 4 planes of a multiple of 4 bytes");
+    if (batch == 0) return PER_OK;
+    DeviceGuard g(b->device);
+    GatherArgs a;
+    memset(&a, 0, sizeof a);
+    void *outs[2] = {d_out_obs, d_out_next};
+    const uint8_t *srcs[2] = {b->obs, b->next};
+    for (int c = 0; c < 2; ++c) {
+        a.rc[c].src = srcs[c];
+        a.rc[c].src_stride = b->obs_stride;
+        a.rc[c].row_bytes = b->obs_bytes;
+        a.cast_out[c] = (uint8_t *)outs[c];
+    }
+    a.idx = d_idx;
+    a.batch = batch;
+    a.n_rows = b->len;
+    a.act = b->act; a.rew = b->rew; a.done = b->done;
+    a.out_act = d_out_act; a.out_rew = d_out_rew; a.out_done = d_out_done;
+    a.status = b->status();
+    a.idx_base = b->idx_base;
+    a.skip_foreign = b->n_shards > 1;
+    a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    const int plane = (int)(b->obs_bytes / 4);
+    const int64_t work = batch * (plane / 4);
+    int64_t grid = (work + 255) / 256;
+    if (grid > (int64_t)b->sm_count * 8) grid = (int64_t)b->sm_count * 8;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (out_dtype == CAST_F32) k_gather_cast_nhwc<float4><<<(unsigned)grid, 256, 0, s>>>(a, plane, scale);
+    else if (out_dtype == CAST_BF16) k_gather_cast_nhwc<BF16x4><<<(unsigned)grid, 256, 0, s>>>(a, plane, scale);
+    else k_gather_cast_nhwc<F16x4><<<(unsigned)grid, 256, 0, s>>>(a, plane, scale);
+    PER_CUDA(cudaGetLastError());
+    return PER_OK;
+}
+
 int per_tune(per_buffer *b, const char *key, int64_t value) {
     if (!b || !key) return fail(PER_ERR_ARG, "per_tune: bad argument");
     GatherTune t = b->tune;

@@ -423,15 +423,24 @@ class ReplayBuffer(object):
                                    _n.ptr(done), _n.ptr(extra), _n.stream_ptr()))
         return obs, act, rew, nxt, done, extra
 
-    def _gather_cast_device(self, idx_t, dtype, scale):
-        """Extension: the gather fused with the learner's uint8 -> float widening (ApeX.py:50,53)."""
+    def _gather_cast_device(self, idx_t, dtype, scale, channels_last=False):
+        """Extension: the gather fused with the learner's uint8 -> float widening (ApeX.py:50,53); channels_last hands
+        the convolution NHWC memory (torch.channels_last tensors of the usual [B, C, H, W] shape)."""
         code = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[dtype]
         b = idx_t.numel()
-        obs = torch.empty((b,) + tuple(self._obs_shape), dtype=dtype, device=self._device)
-        nxt = torch.empty_like(obs)
         act = torch.empty(b, dtype=torch.int64, device=self._device)
         rew = torch.empty(b, dtype=torch.float32, device=self._device)
         done = torch.empty(b, dtype=torch.float32, device=self._device)
+        if channels_last:
+            assert len(self._obs_shape) == 3 and self._obs_shape[0] == 4, "channels_last needs [4, H, W] observations"
+            obs = torch.empty((b,) + tuple(self._obs_shape), dtype=dtype, device=self._device, memory_format=torch.channels_last)
+            nxt = torch.empty_like(obs)  # preserves the format
+            _n.check(_n.lib.per_gather_cast_nhwc(self._h, _n.C.c_void_p(idx_t.data_ptr()), b, code, float(scale), 4,
+                                                 _n.C.c_void_p(obs.data_ptr()), _n.C.c_void_p(nxt.data_ptr()), _n.ptr(act),
+                                                 _n.ptr(rew), _n.ptr(done), _n.stream_ptr()))
+            return obs, act, rew, nxt, done, None
+        obs = torch.empty((b,) + tuple(self._obs_shape), dtype=dtype, device=self._device)
+        nxt = torch.empty_like(obs)
         _n.check(_n.lib.per_gather_cast(self._h, _n.ptr(idx_t), b, code, float(scale), _n.ptr(obs), _n.ptr(nxt), _n.ptr(act),
                                         _n.ptr(rew), _n.ptr(done), _n.stream_ptr()))
         return obs, act, rew, nxt, done, None
@@ -510,12 +519,13 @@ class PrioritizedReplayBuffer(ReplayBuffer):
     def _draw_uniforms(self, batch_size):
         return np.array([random.random() for _ in range(batch_size)], dtype=np.float64)  # memory.py:247
 
-    def sample_device(self, batch_size, beta, uniforms=None, gather=True, obs_dtype=None, obs_scale=1.0):
+    def sample_device(self, batch_size, beta, uniforms=None, gather=True, obs_dtype=None, obs_scale=1.0, channels_last=False):
         """Extension: sample() with every output left on the GPU.  Returns a dict with
         idx (int64), weights (float32), weights64, and — if gather — obs, act, rew, next_obs,
         done (and a_mu).  `uniforms`: optional float64 CUDA / host vector replacing the draws.
         obs_dtype = torch.float32 / bfloat16 / float16 widens the uint8 frames inside the gather
-        (value * obs_scale), replacing the learner's torch.FloatTensor(states) (ApeX.py:50,53)."""
+        (value * obs_scale), replacing the learner's torch.FloatTensor(states) (ApeX.py:50,53); channels_last=True
+        returns them as torch.channels_last tensors (NHWC memory) for the convolution trunk."""
         assert beta > 0
         self._flush()
         if uniforms is None:
@@ -533,7 +543,7 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         out = {"idx": idx, "weights": w32, "weights64": w64}
         if gather:
             if obs_dtype is not None and self._obs_dtype == np.uint8:
-                obs, act, rew, nxt, done, extra = self._gather_cast_device(idx, obs_dtype, obs_scale)
+                obs, act, rew, nxt, done, extra = self._gather_cast_device(idx, obs_dtype, obs_scale, channels_last)
             else:
                 obs, act, rew, nxt, done, extra = self._gather_device(idx)
             out.update(obs=obs, act=act, rew=rew, next_obs=nxt, done=done)

@@ -79,6 +79,7 @@ SIGNATURES = {
     "per_sample_indices": (C.c_int, [_p, _p, _i64, _f64, _p, _p, _p, _p]),
     "per_gather": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "per_gather_cast": (C.c_int, [_p, _p, _i64, C.c_int, C.c_float, _p, _p, _p, _p, _p, _p]),
+    "per_gather_cast_nhwc": (C.c_int, [_p, _p, _i64, C.c_int, C.c_float, C.c_int, _p, _p, _p, _p, _p, _p]),
     "per_update_priorities": (C.c_int, [_p, _p, _p, C.c_int, _i64, _p]),
     "per_update_leaves": (C.c_int, [_p, _p, _p, _f64, _i64, _p]),
     "per_pow_alpha_host": (C.c_int, [_p, _f64, _p, _i64]),

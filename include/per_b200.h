@@ -233,6 +233,14 @@ int per_gather_cast(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_
                     void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew,
                     float *d_out_done, void *stream);
 
+/* The same with CHANNELS-LAST output rows (the layout cuDNN's convolutions prefer; the learner's first layer is one,
+ * model.py:33): an observation is `channels` planes (uint8[4,84,84]: 4 planes of 7 056 bytes) and output row q holds, for
+ * every pixel, its `channels` widened values next to each other — the memory of a torch tensor of shape
+ * [batch, C, H, W] in torch.channels_last format.  channels must be 4 and the plane size a multiple of 4 bytes. */
+int per_gather_cast_nhwc(per_buffer *b, const int64_t *d_idx, int64_t batch, int out_dtype, float scale, int channels,
+                         void *d_out_obs, void *d_out_next, int64_t *d_out_act, float *d_out_rew, float *d_out_done,
+                         void *stream);
+
 /* PrioritizedReplayBuffer.update_priorities (memory.py:300-320), sequential
  * semantics (a later duplicate wins), running max raised.  Priorities are float64
  * (prio_dtype PER_PRIO_F64) or float32 (PER_PRIO_F32, what utils.py:77 hands back);

@@ -88,3 +88,30 @@ def test_snapshot_restore_is_exact(mods, tmp_path, cls_name, fill):
     random.seed(9); s1 = buf.sample(32, 0.5)
     random.seed(9); s2 = back.sample(32, 0.5)
     assert list(s1[-1]) == list(s2[-1]) and np.array_equal(s1[-2], s2[-2])
+
+
+@pytest.mark.parametrize("dtype,scale", [(torch.float32, 1.0), (torch.bfloat16, 1.0 / 255.0), (torch.float16, 1.0)])
+def test_gather_cast_channels_last_equals_torch(mods, dtype, scale):
+    """SURVEY section 8(f) row 3, second half: the widened batch in channels-last (NHWC) memory, as the learner's
+    convolution trunk wants it (ApeX.py:50-55 -> model.py:33), against torch's own conversion of the plain uint8 gather:
+    x.to(dtype) * scale, .contiguous(memory_format=torch.channels_last) — same values, same strides, same bytes."""
+    memory = mods[0]
+    size, batch = 3000, 257
+    gen = torch.Generator(device="cuda").manual_seed(4)
+    buf = memory.PrioritizedReplayBuffer(size, 0.6)
+    obs = torch.randint(0, 256, (size, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=gen)
+    nxt = torch.randint(0, 256, (size, 4, 84, 84), dtype=torch.uint8, device="cuda", generator=gen)
+    buf.add_batch_device(obs, nxt, torch.arange(size, device="cuda"), torch.zeros(size, device="cuda"), torch.zeros(size, device="cuda"))
+    u = np.random.default_rng(2).random(batch)
+    plain = buf.sample_device(batch, 0.5, uniforms=u)
+    d = buf.sample_device(batch, 0.5, uniforms=u, obs_dtype=dtype, obs_scale=scale, channels_last=True)
+    assert torch.equal(d["idx"], plain["idx"]) and torch.equal(d["act"], plain["act"])
+    for k in ("obs", "next_obs"):
+        want = (plain[k].to(torch.float32) * scale).to(dtype).contiguous(memory_format=torch.channels_last)
+        got = d[k]
+        assert got.shape == want.shape and got.stride() == want.stride() and got.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(got, want)
+        assert torch.equal(got.permute(0, 2, 3, 1).contiguous().view(-1), want.permute(0, 2, 3, 1).contiguous().view(-1))
+    # and it feeds a convolution without a layout change
+    conv = torch.nn.Conv2d(4, 8, 8, 4).cuda().to(dtype).to(memory_format=torch.channels_last)
+    assert conv(d["obs"]).shape == (batch, 8, 20, 20)
