@@ -643,24 +643,33 @@ class CustomPrioritizedReplayBuffer(PrioritizedReplayBuffer):
         self._stage((state, action, reward, next_state, done), priority)
         self._max_priority = max(self._max_priority, priority)
 
+    def prepare_chunk(self, states, actions, rewards, next_states, dones, priorities):
+        """Host half of add_chunk: stacks the rows and raises the priorities to alpha (libm pow).  Touches no buffer
+        state, so any number of threads may prepare chunks at the same time (replay_ops.ReplayServer does)."""
+        self._ensure_native(states[0])
+        pr = np.asarray(priorities, dtype=np.float64)
+        return {"n": len(actions),
+                "obs": np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in states]),
+                "next": np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in next_states]),
+                "act": np.asarray(actions, dtype=np.int64), "rew": np.asarray(rewards, dtype=np.float32),
+                "done": np.asarray(dones, dtype=np.float32), "leaf": _pow_alpha_exact(pr, self._alpha), "max": float(pr.max())}
+
+    def commit_chunk(self, c):
+        """Device half of add_chunk: one upload and one launch; one caller at a time (like every buffer call)."""
+        self._sync_max_priority()
+        self._flush()
+        up = self._host.up
+        self.add_batch_device(up("obs", c["obs"]), up("next", c["next"]), up("act", c["act"]), up("rew", c["rew"]),
+                              up("done", c["done"]), leaves=up("leaf", c["leaf"]), batch_max=c["max"])
+        self._max_priority = max(self._max_priority, c["max"])
+
     def add_chunk(self, states, actions, rewards, next_states, dones, priorities):
         """Extension: `for i: self.add(states[i], actions[i], rewards[i], next_states[i], dones[i],
         priorities[i])` for one actor chunk (batchrecorder.py:133-137) as a single upload and
         launch; same slots, same leaves (libm pow on the host), same running max."""
-        n = len(actions)
-        if n == 0:
+        if len(actions) == 0:
             return
-        self._sync_max_priority()
-        self._ensure_native(states[0])
-        self._flush()
-        pr = np.asarray(priorities, dtype=np.float64)
-        obs = np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in states])
-        nxt = np.stack([np.asarray(s, dtype=self._obs_dtype).reshape(self._obs_shape) for s in next_states])
-        up = self._host.up
-        self.add_batch_device(up("obs", obs), up("next", nxt), up("act", np.asarray(actions, dtype=np.int64)),
-                              up("rew", np.asarray(rewards, dtype=np.float32)), up("done", np.asarray(dones, dtype=np.float32)),
-                              leaves=up("leaf", _pow_alpha_exact(pr, self._alpha)), batch_max=float(pr.max()))
-        self._max_priority = max(self._max_priority, float(pr.max()))
+        self.commit_chunk(self.prepare_chunk(states, actions, rewards, next_states, dones, priorities))
 
 
 class CustomPrioritizedReplayBuffer_AQL(PrioritizedReplayBuffer):

@@ -155,6 +155,103 @@ def run_driver(which):
             sys.modules.pop(m, None)
 
 
+def run_replay_server():
+    """origin_repo/replay.py UNMODIFIED: its three worker coroutines (replay.py:77-146) with their global asyncio.Lock and
+    thread-pool executor, fed through in-memory stand-ins for the ZeroMQ DEALER sockets by a script that plays the actors
+    (100 chunks of 8 n-step transitions, the wire tuple of origin_repo/actor.py:105-109) and the learner (batch
+    requests, priorities sent back as float32 like origin_repo/learner.py).  The buffer it holds is the recording one."""
+    import asyncio
+    import _pickle as pickle
+    from concurrent.futures import ThreadPoolExecutor
+    trace = Trace()
+    mods = ("memory", "utils", "arguments", "replay", "model", "gym", "tensorboardX")
+    for m in mods:
+        sys.modules.pop(m, None)
+    sys.modules["memory"] = recording_memory(trace)
+    added = [os.path.join(TESTS, "stubs"), os.path.join(REF, "origin_repo"), REF]
+    sys.path[:0] = added
+    chunk_rows, n_chunks = 8, 100
+    try:
+        replay = _load("replay", os.path.join(REF, "origin_repo", "replay.py"))
+
+        class FakeSocket(object):
+            def __init__(self):
+                self.inbox, self.sent = asyncio.Queue(), asyncio.Queue()
+
+            def connect(self, addr):
+                self.addr = addr
+
+            async def recv_multipart(self, copy=False):
+                return await self.inbox.get()
+
+            async def send_multipart(self, parts, copy=True):
+                await self.sent.put(parts)
+
+        sockets = []
+
+        class FakeContext(object):
+            @staticmethod
+            def instance():
+                return FakeContext()
+
+            def socket(self, kind):
+                s = FakeSocket()
+                sockets.append(s)
+                return s
+
+        replay.Context = FakeContext  # replay.py:13 `from zmq.asyncio import Context`; everything else is the file's own code
+        rng = np.random.default_rng(5)
+        random.seed(5)
+
+        async def session():
+            buffer = sys.modules["memory"].CustomPrioritizedReplayBuffer(2000, 0.6)
+            exe, event, lock = ThreadPoolExecutor(), asyncio.Event(), asyncio.Lock()
+            tasks = [asyncio.ensure_future(replay.recv_batch_worker(buffer, exe, event, lock, 500)),
+                     asyncio.ensure_future(replay.recv_prios_worker(buffer, exe, event, lock)),
+                     asyncio.ensure_future(replay.send_batch_worker(buffer, exe, event, lock, 64, 0.4))]
+            await asyncio.sleep(0.05)  # the workers create and connect their sockets
+            by_addr = {s.addr: s for s in sockets}
+            batch_in, prios_in, batch_out = by_addr["ipc:///tmp/5101.ipc"], by_addr["ipc:///tmp/5102.ipc"], by_addr["ipc:///tmp/5103.ipc"]
+            for c in range(n_chunks):  # actors: chunks of n-step transitions with their priorities
+                states = [rng.standard_normal(4).astype(np.float32) for _ in range(chunk_rows)]
+                nexts = [rng.standard_normal(4).astype(np.float32) for _ in range(chunk_rows)]
+                batch = [states, [int(a) for a in rng.integers(0, 3, size=chunk_rows)], [float(r) for r in rng.standard_normal(chunk_rows)],
+                         nexts, [np.float32(d) for d in (rng.random(chunk_rows) < 0.1)]]
+                prios = np.abs(rng.standard_normal(chunk_rows)) + 1e-6
+                await batch_in.inbox.put((b"actor", pickle.dumps((batch, prios))))
+                await batch_in.sent.get()  # the ack (replay.py:94)
+            await asyncio.wait_for(event.wait(), 5)  # threshold reached at the 100th chunk (replay.py:99-106)
+            for step in range(6):  # learner: ask for a batch, train, send priorities back; one more chunk arrives in between
+                await batch_out.inbox.put((b"learner", b""))
+                ident, data = await batch_out.sent.get()
+                got = pickle.loads(data)
+                newp = (np.abs(rng.standard_normal(64)) + 1e-6).astype(np.float32)
+                await prios_in.inbox.put((b"learner", pickle.dumps((got[-1], newp))))
+                await prios_in.sent.get()
+                if step % 2 == 1:
+                    states = [rng.standard_normal(4).astype(np.float32) for _ in range(chunk_rows)]
+                    batch = [states, [1] * chunk_rows, [0.5] * chunk_rows, states, [np.float32(0)] * chunk_rows]
+                    await batch_in.inbox.put((b"actor", pickle.dumps((batch, np.full(chunk_rows, 0.25)))))
+                    await batch_in.sent.get()
+            for t in tasks:
+                t.cancel()
+            exe.shutdown(wait=False)
+            return buffer
+
+        buf = asyncio.run(session())
+        cap, n = buf._it_sum._capacity, len(buf)
+        final = {"leaves_sum": np.array(buf._it_sum._value[cap:cap + n], dtype=np.float64),
+                 "leaves_min": np.array(buf._it_min._value[cap:cap + n], dtype=np.float64),
+                 "root_sum": float(buf._it_sum._value[1]), "root_min": float(buf._it_min._value[1]), "cap": cap,
+                 "len": n, "next_idx": int(buf._next_idx), "max_priority": float(buf._max_priority)}
+        return trace.events, final, chunk_rows
+    finally:
+        for p in added:
+            sys.path.remove(p)
+        for m in mods:
+            sys.modules.pop(m, None)
+
+
 def pack(events, final, prefix, out):
     """Flattens one driver's events into arrays (no pickled objects in the fixture)."""
     kinds, a, b = [], [], []
@@ -207,13 +304,16 @@ def generate():
     for which in DRIVERS:
         events, final = run_driver(which)
         pack(events, final, which, out)
+    events, final, chunk_rows = run_replay_server()
+    pack(events, final, "replay_server", out)
+    out["replay_server_chunk_rows"] = chunk_rows
     return out
 
 
 if __name__ == "__main__":
     fixture = generate()
     np.savez_compressed(OUT, **fixture)
-    for d in DRIVERS:
+    for d in DRIVERS + ("replay_server",):
         k = fixture[d + "_ev_kind"]
         print("%-8s %-34s adds %5d  samples %3d  updates %3d  final len %d" % (
             d, str(fixture[d + "_cls"]), int(fixture[d + "_add_act"].shape[0]), int((k == 1).sum()), int((k == 2).sum()),

@@ -46,6 +46,24 @@ def test_committed_trace_is_what_the_unmodified_driver_does(tracer, driver):
         assert all(out[k].dtype == g[k].dtype and out[k].shape[1:] == g[k].shape[1:] for k in keys if k.startswith(driver + "_s_col"))
 
 
+def test_committed_trace_is_what_the_unmodified_replay_server_does(tracer):
+    """origin_repo/replay.py's worker coroutines, run unmodified over in-memory sockets (one worker of each kind, a
+    scripted actor / learner).  Its sender seeds the global RNG from the clock (replay.py:128-129), so the draws — and
+    with them the sampled batches and the updates that answer them — differ from run to run in the reference itself;
+    the ingest and the shape of the session do not."""
+    g = np.load(os.path.join(GOLDEN, "dropin_trace.npz"), allow_pickle=False)
+    events, final, chunk_rows = tracer.run_replay_server()
+    out = {}
+    tracer.pack(events, final, "replay_server", out)
+    assert chunk_rows == int(g["replay_server_chunk_rows"])
+    for k, v in out.items():
+        v = np.asarray(v)
+        if "_add_" in k or "_ev_" in k or k.endswith(("_cls", "_size", "_alpha", "_final_len", "_final_next_idx", "_final_cap")):
+            assert np.array_equal(v, g[k]), k
+        else:
+            assert v.shape == g[k].shape and v.dtype == g[k].dtype, k
+
+
 def test_every_recorded_call_binds_to_the_dropin_signatures():
     """Same constructor / add / sample / update_priorities signatures as memory.py: the exact
     positional and keyword shapes the drivers use must bind (no GPU needed to check that)."""

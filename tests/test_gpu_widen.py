@@ -32,6 +32,77 @@ def actor_chunk(rng, n, shape=(4, 84, 84)):
     return batch, prios
 
 
+def test_replay_server_concurrent_workers_match_the_oracle(mods):
+    """replay_ops.ReplayServer with real concurrency: three actor threads pushing chunks, a learner thread that samples and
+    returns priorities, all at once, no global lock around the operations.  The server logs the order in which the
+    operations were enqueued; the same operations in that order through the oracle's sequential port of the reference
+    buffer (oracle/per_oracle.py ReplayOracle) must give the same sampled indices, the same rows and, bit for bit, the
+    same trees — i.e. the short enqueue lock + stream order keep the reference's sequential semantics."""
+    import threading
+    from oracle import per_oracle as po
+    memory, ops, _ = mods
+    size = 1500
+    buf = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    log = []
+    server = ops.ReplayServer(buf, n_senders=2, log=log)
+    rngs = [np.random.default_rng(100 + t) for t in range(3)]
+    warm = actor_chunk(np.random.default_rng(99), 200, shape=(2, 8))
+    server.push_batch(pickle.dumps(warm))
+    samples, errors = [], []
+
+    def actor(t):
+        try:
+            for _ in range(12):
+                server.push_batch(pickle.dumps(actor_chunk(rngs[t], 40, shape=(2, 8))))
+        except Exception as exc:  # noqa: BLE001
+            errors.append(exc)
+
+    def learner():
+        try:
+            rng = np.random.default_rng(7)
+            for _ in range(15):
+                out = pickle.loads(server.sample_batch(64, 0.4))
+                samples.append(out)
+                server.update_prios(pickle.dumps((out[-1], (np.abs(rng.standard_normal(64)) + 1e-6).astype(np.float32))))
+        except Exception as exc:  # noqa: BLE001
+            errors.append(exc)
+
+    threads = [threading.Thread(target=actor, args=(t,)) for t in range(3)] + [threading.Thread(target=learner)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join(timeout=120)
+    assert not errors, errors
+    assert [s for s, _, _ in log] == list(range(len(log))) and len(log) == 1 + 36 + 30
+    ora = po.ReplayOracle(size, 0.6, "apex")
+    k = 0
+    for _, kind, payload in log:
+        if kind == "push":
+            c = payload
+            for i in range(c["n"]):
+                ora.add(c["obs"][i], int(c["act"][i]), float(c["rew"][i]), c["next"][i], float(c["done"][i]), 0.0)
+                # the chunk carries leaves (priority ** alpha, libm); put them in as the reference's add would
+                slot = (ora.cursor - 1) % size
+                ora.sum_tree.set(slot, float(c["leaf"][i]))
+                ora.min_tree.set(slot, float(c["leaf"][i]))
+            ora.max_priority = max(ora.max_priority, c["max"])
+        elif kind == "sample":
+            n, beta, u, idxes = payload
+            want = ora.sample(n, beta, u)
+            assert list(want[-1]) == idxes == list(samples[k][-1])
+            np.testing.assert_allclose(samples[k][-2], want[-2], rtol=1e-5)
+            for got_col, want_col in zip(samples[k][:5], want[:5]):
+                assert np.array_equal(np.asarray(got_col), np.asarray(want_col, dtype=np.asarray(got_col).dtype))
+            k += 1
+        else:
+            idx, pr = payload
+            ora.update_priorities([int(i) for i in idx], [float(p) for p in pr])
+    assert k == 15 and len(buf) == len(ora) and buf._next_idx == ora.cursor
+    assert np.array_equal(bits(buf._it_sum._value)[1:], bits(np.array(ora.sum_tree.v))[1:])
+    assert np.array_equal(bits(buf._it_min._value)[1:], bits(np.array(ora.min_tree.v))[1:])
+    assert buf._max_priority == ora.max_priority
+
+
 def test_replay_server_ops_wire_format(mods):
     memory, ops, _ = mods
     rng = np.random.default_rng(0)
