@@ -126,10 +126,34 @@ int grid_for(int64_t n, int threads, int sm_count) {
     return (int)g;
 }
 
+// The dense one-launch form (k_upd_dense_sorted) pays when the batch is the ascending sample just drawn, too large for
+// the per-CTA climb, and dirties enough of the tree that streaming all of it is cheaper than chasing paths.
+bool dense_update_ok(const UpdArgs &a) {
+    return a.dense_counter && a.sorted_idx && a.sorted_fast && !a.publish_to && a.t.sum && a.t.mnn && a.n > 1024 &&
+           a.t.L > DENSE_LG_MAX && a.t.L <= 2 * DENSE_LG_MIN && a.t.cap <= 256 * a.n;  // measured: past 2^20 leaves the tree pair
+                                                                                       // leaves L2 and the multi-launch form wins
+}
+
 // Batched leaf update + re-reduction (K1).  `td` non-null fuses K5 in front (one-CTA form only).
 int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s, bool pdl = false) {
     TdArgs none;
     memset(&none, 0, sizeof none);
+    if (!td && dense_update_ok(a)) {
+        // a large batch that is the sample just drawn: rebuild everything in one streaming launch
+        static bool attr_set = false;
+        if (!attr_set) {
+            PER_CUDA(cudaFuncSetAttribute(k_upd_dense_sorted<DENSE_LG_MIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, DenseShape<DENSE_LG_MIN>::SMEM_BYTES));
+            PER_CUDA(cudaFuncSetAttribute(k_upd_dense_sorted<DENSE_LG_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, DenseShape<DENSE_LG_MAX>::SMEM_BYTES));
+            attr_set = true;
+        }
+        if (a.t.L <= 2 * DENSE_LG_MIN)
+            PER_CUDA(launch_pdl(k_upd_dense_sorted<DENSE_LG_MIN>, dim3((unsigned)(a.t.cap >> DENSE_LG_MIN)), dim3(DenseShape<DENSE_LG_MIN>::THREADS),
+                                DenseShape<DENSE_LG_MIN>::SMEM_BYTES, s, pdl, a, a.dense_counter));
+        else
+            PER_CUDA(launch_pdl(k_upd_dense_sorted<DENSE_LG_MAX>, dim3((unsigned)(a.t.cap >> DENSE_LG_MAX)), dim3(DenseShape<DENSE_LG_MAX>::THREADS),
+                                DenseShape<DENSE_LG_MAX>::SMEM_BYTES, s, pdl, a, a.dense_counter));
+        return PER_OK;
+    }
     if (a.n <= (td || a.range || a.cluster_max <= 0 ? UPD_CLUSTER_MAX_ITEMS : a.cluster_max)) {
         // one launch: a cluster of CTAs, 64 items (8 lanes each) per CTA and round
         int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));
@@ -1025,6 +1049,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     a.sorted_fast = b->sorted_update;
     a.cluster_max = b->upd_cluster_max;
+    a.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
     if (a.sorted_idx) b->last_sample_idx = nullptr;  // the binding to that sample ends with its first update (see per_sample_sharded)
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);
 }
@@ -1144,7 +1169,19 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
     t.out_loss = d_out_loss;
     t.red = b->td_red();
     t.status = b->status();
-    if (batch <= UPD_CLUSTER_MAX_ITEMS) {
+    bool dense = false;
+    if (d_idx && batch > 1024 && batch <= UPD_CLUSTER_MAX_ITEMS) {  // would update_common pick the dense form for this batch?
+        UpdArgs probe;
+        memset(&probe, 0, sizeof probe);
+        probe.t = b->t;
+        probe.n = batch;
+        probe.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
+        probe.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch;
+        probe.sorted_fast = b->sorted_update;
+        probe.publish_to = (b->early_publish && b->mailbox) ? b->d_peer_mailbox : nullptr;
+        dense = dense_update_ok(probe);
+    }
+    if (batch <= UPD_CLUSTER_MAX_ITEMS && !dense) {
         if (d_idx) return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, &t, s);
         UpdArgs a;
         memset(&a, 0, sizeof a);

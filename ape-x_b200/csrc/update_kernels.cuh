@@ -80,6 +80,7 @@ struct UpdArgs {
     u64 *tl;                  // timeline (diagnostics), see tl_stamp: this launch's first entry
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
+    unsigned *dense_counter;  // per-buffer word for k_upd_dense_sorted's "last CTA" election (null: that form is not offered)
 };
 
 // Owned strata of the last sharded sample: tags are (epoch << 32) | value, written with atomicMax
@@ -923,6 +924,166 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
         dense_write(a.t, 1, top, s_sum, s_min);
         UPD_TRACE(13);
         if (tl_on) tl_stamp(a.tl, 3, 9);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Dense form for LARGE sorted batches (the update of the sample just drawn, n > 1 024 items, trees of at most ~256 n
+// leaves): when a batch dirties a sizeable share of the leaves, rebuilding every node costs less than chasing the dirty
+// paths — a pair of 2^20-leaf trees is 16 MB of leaves in and 16 MB of nodes out, a few microseconds of L2 / HBM
+// streaming, against ~30 us for 4 096 scattered 20-level climbs.  ONE launch: CTA c owns leaves [2048 c, 2048 c + 2048):
+//   1. the items that fall there are a contiguous run of the ascending index array, found by a 32-ary search;
+//   2. the CTA's leaves are loaded into shared memory and the items applied to them in index order (equal indices are
+//      adjacent: the last of a run wins, memory.py:314-318); changed leaves are also written out;
+//   3. the 11 generations above them are rebuilt in shared memory and written out (every node = left (op) right);
+//   4. the last CTA to finish (a self-resetting counter) rebuilds the generations above the CTA roots.
+// Same node values as every other form: the node array is a function of the leaves alone.
+// ---------------------------------------------------------------------------------------
+constexpr int DENSE_LG_MAX = 11;                       // leaves per CTA: 2^10 (trees up to 2^20 leaves: every CTA resident at once)
+constexpr int DENSE_LG_MIN = 10;                       //   or 2^11 (up to 2^22 leaves)
+constexpr int DENSE_TOP_MAX_LOG2 = DENSE_LG_MAX;       // CTA roots the last CTA can take (same buffers)
+
+// first position j in [lo, hi) with key(j) >= want (hi if none), keys ascending; all lanes of the warp return it
+__device__ __forceinline__ int64_t dense_lower_bound(const UpdArgs &a, int64_t lo, int64_t hi, int64_t want, int lane) {
+    while (hi - lo > 0) {
+        const int64_t n = hi - lo, step = (n + 31) >> 5;
+        int64_t j = lo + (lane + 1) * step - 1;  // last position of this lane's chunk
+        if (j > hi - 1) j = hi - 1;
+        const bool ge = upd_index(a, j) >= want;
+        const unsigned m = __ballot_sync(0xffffffffu, ge);
+        if (m == 0) return hi;
+        const int f = __ffs(m) - 1;
+        const int64_t cb = lo + f * step;
+        int64_t ce = cb + step - 1;
+        if (ce > hi - 1) ce = hi - 1;
+        lo = cb;
+        hi = ce;  // position ce satisfies the predicate; [cb, ce) undecided
+        if (hi == lo) return lo;
+    }
+    return lo;
+}
+
+template <int LG>
+struct DenseShape {
+    static constexpr int LEAVES = 1 << LG;
+    static constexpr int THREADS = LEAVES / 8;                              // 128 or 256
+    static constexpr int SMEM_BYTES = 2 * 2 * LEAVES * (int)sizeof(double);  // 32 or 64 KB of dynamic shared memory
+};
+
+template <int LG>
+__global__ void __launch_bounds__(DenseShape<LG>::THREADS) k_upd_dense_sorted(UpdArgs a, unsigned *counter) {
+    constexpr int DENSE_LEAVES_LOG2 = LG, DENSE_LEAVES = DenseShape<LG>::LEAVES, DENSE_THREADS = DenseShape<LG>::THREADS;
+    extern __shared__ __align__(16) double s_dense[];
+    double *s_sum = s_dense;                      // relative heap of this CTA's subtree: node (1 << j) + i
+    double *s_min = s_dense + 2 * DENSE_LEAVES;
+    __shared__ int64_t s_run[2];
+    __shared__ int s_last;
+    __shared__ double s_max[DENSE_THREADS / 32];
+    pdl_launch_dependents();
+    pdl_wait();
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int64_t leaf0 = (int64_t)blockIdx.x * DENSE_LEAVES;
+    int first, last;
+    owned_range(a.range, a.n, first, last);
+    if (tid < 32) {
+        const int64_t lo = dense_lower_bound(a, first, last, leaf0, lane);
+        const int64_t hi = dense_lower_bound(a, lo, last, leaf0 + DENSE_LEAVES, lane);
+        if (lane == 0) {
+            s_run[0] = lo;
+            s_run[1] = hi;
+        }
+    }
+    for (int i = tid; i < DENSE_LEAVES; i += DENSE_THREADS) {  // the leaves as they are
+        s_sum[DENSE_LEAVES + i] = ldcg_f64(a.t.sum + a.t.cap + leaf0 + i);
+        s_min[DENSE_LEAVES + i] = ldcg_f64(a.t.mnn + a.t.cap + leaf0 + i);
+    }
+    __syncthreads();
+    const int64_t lo = s_run[0], hi = s_run[1];
+    double my_max = 0.0;
+    for (int64_t j = lo + tid; j < hi; j += DENSE_THREADS) {  // the items of this CTA; the last of an equal run wins
+        int64_t k;
+        double leaf, raw;
+        if (!upd_item(a, j, k, leaf, raw)) continue;
+        my_max = fmax(my_max, raw);
+        const int64_t nxt = j + 1 < hi ? upd_index(a, j + 1) : INT64_MAX;
+        if (nxt < k) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending: not the sample's buffer any more
+        if (nxt == k) continue;
+        const int64_t i = k - leaf0;
+        if (i < 0 || i >= DENSE_LEAVES) {  // cannot happen for an ascending array
+            atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
+            continue;
+        }
+        s_sum[DENSE_LEAVES + i] = leaf;
+        s_min[DENSE_LEAVES + i] = leaf;
+        a.t.sum[a.t.cap + k] = leaf;
+        a.t.mnn[a.t.cap + k] = leaf;
+    }
+    if (a.max_prio) {
+        if (a.src_kind == LEAF_GIVEN) my_max = (tid == 0 && blockIdx.x == 0) ? a.batch_max : 0.0;
+        for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, lane ^ o));
+        if (lane == 0) s_max[tid >> 5] = my_max;
+    }
+    __syncthreads();
+    if (a.max_prio && tid == 0) {
+        double m = 0.0;
+        for (int w = 0; w < DENSE_THREADS / 32; ++w) m = fmax(m, s_max[w]);
+        if (m > 0.0) atomic_max_pos_f64(a.max_prio, m);
+    }
+    // generations above the leaves, level by level (thread i of a level reads one 16-byte pair: conflict-free)
+#pragma unroll 1
+    for (int m = DENSE_LEAVES >> 1; m >= 1; m >>= 1) {
+        for (int i = tid; i < m; i += DENSE_THREADS) {
+            const double2 cs = *reinterpret_cast<const double2 *>(s_sum + 2 * (m + i));
+            const double2 cm = *reinterpret_cast<const double2 *>(s_min + 2 * (m + i));
+            s_sum[m + i] = __dadd_rn(cs.x, cs.y);
+            s_min[m + i] = fmin(cm.x, cm.y);
+        }
+        __syncthreads();
+    }
+    // write the subtree's internal nodes: relative slot p = (1 << j) + i  <->  node ((sub_root << j) + i)
+    const int64_t sub_root = (a.t.cap >> DENSE_LEAVES_LOG2) + blockIdx.x;
+    for (int p = 1 + tid; p < DENSE_LEAVES; p += DENSE_THREADS) {
+        const int j = 31 - __clz(p);
+        const int64_t node = (sub_root << j) + (p - (1 << j));
+        a.t.sum[node] = s_sum[p];
+        a.t.mnn[node] = s_min[p];
+    }
+    // the last CTA to get here rebuilds what is above the CTA roots
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned done = atomicAdd(counter, 1u);
+        s_last = done == gridDim.x - 1;
+        if (s_last) *counter = 0;  // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int top_log2 = a.t.L - DENSE_LEAVES_LOG2;  // log2 of the number of CTA roots (<= DENSE_TOP_MAX_LOG2)
+    const int nroots = 1 << top_log2;
+    for (int i = tid; i < nroots; i += DENSE_THREADS) {
+        s_sum[nroots + i] = ldcg_f64(a.t.sum + nroots + i);
+        s_min[nroots + i] = ldcg_f64(a.t.mnn + nroots + i);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int m = nroots >> 1; m >= 1; m >>= 1) {
+        for (int i = tid; i < m; i += DENSE_THREADS) {
+            const double2 cs = *reinterpret_cast<const double2 *>(s_sum + 2 * (m + i));
+            const double2 cm = *reinterpret_cast<const double2 *>(s_min + 2 * (m + i));
+            s_sum[m + i] = __dadd_rn(cs.x, cs.y);
+            s_min[m + i] = fmin(cm.x, cm.y);
+        }
+        __syncthreads();
+    }
+    for (int p = 1 + tid; p < nroots; p += DENSE_THREADS) {
+        a.t.sum[p] = s_sum[p];
+        a.t.mnn[p] = s_min[p];
+    }
+    if (a.rec_out) {  // sharded replay: the record of the refreshed tree (roots from shared memory need the writes above)
+        __threadfence();
+        __syncthreads();
+        if (tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
     }
 }
 

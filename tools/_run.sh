@@ -1,2 +1,2 @@
-timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --ring 2097152 --parity-size 16777216 --steps 20 --warmup 5 --timeline > gpurun_out/r02_bench_n8_c4.json 2> gpurun_out/r02_bench_n8_c4.err; echo "rc=$?"; grep -E "parity ok on rank 0|rank 0 timeline|Error|error" gpurun_out/r02_bench_n8_c4.err | cut -c1-700
-cut -c1-600 gpurun_out/r02_bench_n8_c4.json
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/r2_t7.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/r2_t7.log
+timeout 900 python tools/tree_sweep.py --caps 16 18 20 22 24 26 --cpu > gpurun_out/r02_tree_sweep.txt 2>&1; echo "sweep rc=$?"; cat gpurun_out/r02_tree_sweep.txt
