@@ -287,6 +287,67 @@ class ShardedReplay(object):
                                    _n.ptr(out["rew"]), _n.ptr(out["done"]), _n.ptr(out.get("a_mu")), _n.stream_ptr()))
         return out
 
+    # -- host-buffer forms (the reference's own calling convention: numpy in, numpy out) -----------------------
+    def _host_stage(self, batch):
+        st = getattr(self, "_hstage", None)
+        if st is None or st["batch"] < batch:
+            dev, pin = dict(device=self.device), dict(pin_memory=True)
+            shape = (batch,) + self.obs_shape
+            st = {"batch": batch,
+                  "d": {"obs": torch.empty(shape, dtype=self.obs_dtype, **dev), "next_obs": torch.empty(shape, dtype=self.obs_dtype, **dev),
+                        "act": torch.empty(batch, dtype=torch.int64, **dev), "rew": torch.empty(batch, dtype=torch.float32, **dev),
+                        "done": torch.empty(batch, dtype=torch.float32, **dev), "idx": torch.empty(batch, dtype=torch.int64, **dev),
+                        "weights": torch.empty(batch, dtype=torch.float32, **dev), "weights64": torch.empty(batch, dtype=torch.float64, **dev)},
+                  "u": torch.empty(batch, dtype=torch.float64, **dev), "u_pin": torch.empty(batch, dtype=torch.float64, **pin),
+                  "up_idx": torch.empty(batch, dtype=torch.int64, **dev), "up_leaf": torch.empty(batch, dtype=torch.float64, **dev),
+                  "up_pin_idx": torch.empty(batch, dtype=torch.int64, **pin), "up_pin_leaf": torch.empty(batch, dtype=torch.float64, **pin),
+                  "h": {"obs": torch.empty(shape, dtype=self.obs_dtype, **pin), "next_obs": torch.empty(shape, dtype=self.obs_dtype, **pin),
+                        "act": torch.empty(batch, dtype=torch.int64, **pin), "rew": torch.empty(batch, dtype=torch.float32, **pin),
+                        "done": torch.empty(batch, dtype=torch.float32, **pin), "idx": torch.empty(batch, dtype=torch.int64, **pin),
+                        "weights64": torch.empty(batch, dtype=torch.float64, **pin)}}
+            self._hstage = st
+        return st
+
+    def sample_host(self, batch, beta, uniforms):
+        """PrioritizedReplayBuffer.sample (memory.py:252-298) for one rank of the sharded replay, host buffers in and out:
+        `uniforms` (the global batch's draws, host float64) go up, this rank's share of the batch comes back as numpy views
+        of pinned staging (valid until the next call): {"lo", "hi"} = the strata [lo, hi) this rank owns, and for those
+        strata obs, next_obs, act, rew, done, weights (float64) and idx (global indices).  The union over ranks is the
+        reference's batch."""
+        st = self._host_stage(batch)
+        st["u_pin"].numpy()[:batch] = np.asarray(uniforms, dtype=np.float64)
+        st["u"][:batch].copy_(st["u_pin"][:batch], non_blocking=True)
+        d = self.sample_device(batch, beta, st["u"][:batch], gather=True, out={k: v[:batch] for k, v in st["d"].items()})
+        st["h"]["idx"][:batch].copy_(d["idx"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        idx_h = st["h"]["idx"].numpy()[:batch]
+        own = np.flatnonzero(idx_h >= 0)
+        lo, hi = (int(own[0]), int(own[-1]) + 1) if own.size else (0, 0)
+        assert hi - lo == own.size, "the strata one shard owns are contiguous"
+        out = {"lo": lo, "hi": hi, "idx": idx_h[lo:hi]}
+        for k in ("obs", "next_obs", "act", "rew", "done", "weights64"):
+            st["h"][k][: hi - lo].copy_(st["d"][k][lo:hi], non_blocking=True)
+            out["weights" if k == "weights64" else k] = st["h"][k].numpy()[: hi - lo]
+        torch.cuda.current_stream().synchronize()
+        return out
+
+    def update_priorities_host(self, idxes, priorities):
+        """update_priorities (memory.py:300-320) with the GLOBAL batch's host arrays on every rank: entries of other
+        ranks' slices are masked out here, leaves are priority ** alpha by the C library's pow (bit-identical trees)."""
+        idx = np.asarray(idxes, dtype=np.int64)
+        pr = np.asarray(priorities, dtype=np.float64)
+        assert idx.shape == pr.shape and np.all(pr > 0) and np.all((idx >= 0) & (idx < self._len))
+        n = idx.size
+        st = self._host_stage(n)
+        mine = (idx // self.geo.cap_local) == self.rank
+        st["up_pin_idx"].numpy()[:n] = np.where(mine, idx, -1)
+        leaves = np.empty(n, dtype=np.float64)
+        _n.check(_n.lib.per_pow_alpha_host(np.ascontiguousarray(pr).ctypes.data, float(self.alpha), leaves.ctypes.data, n))
+        st["up_pin_leaf"].numpy()[:n] = leaves
+        st["up_idx"][:n].copy_(st["up_pin_idx"][:n], non_blocking=True)
+        st["up_leaf"][:n].copy_(st["up_pin_leaf"][:n], non_blocking=True)
+        self.update_leaves_device(st["up_idx"][:n], st["up_leaf"][:n], float(pr.max()))
+
     # -- learner-ward delivery over NVLink ---------------------------------------------------------
     def open_learner_batch(self, batch, learner_rank=0, group=None):
         """Collective, once: the learner rank allocates the batch buffers, everybody maps them."""

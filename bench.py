@@ -796,33 +796,38 @@ def main():
         h2d = 8 * BATCH + 8 * BATCH + 8 * BATCH
         api = "memory.CustomPrioritizedReplayBuffer.sample()/update_priorities() with host numpy in/out"
     else:
-        # sharded API: uniforms arrive from pinned host memory, frames stay on the GPUs that train on
-        # them, the step's result (loss + the batch's new priorities) is read back to the host
-        u_host = [torch.rand(GB, dtype=torch.float64, generator=torch.Generator().manual_seed(i)).pin_memory() for i in range(8)]
-        res_host = torch.empty(GB + 1, dtype=torch.float32).pin_memory()
-        outbuf = {"obs": o_obs, "next_obs": o_nxt, "act": o_act, "rew": o_rew, "done": o_done,
-                  "idx": idx, "weights": w32, "weights64": torch.empty(GB, dtype=torch.float64, device=dev)}
-        u_dev = torch.empty(GB, dtype=torch.float64, device=dev)
-        o_res = torch.empty(GB + 1, dtype=torch.float32, device=dev)  # priorities | loss: one read-back per step
+        # sharded replay through host buffers, the reference's calling convention on every rank: the global batch's
+        # uniforms go up, this rank's share of the batch (frames included) comes back to host memory, and the global
+        # batch's (indices, priorities) go up again for the update
+        rng_e = np.random.default_rng(5)
+        u_host = [rng_e.random(GB) for _ in range(8)]
+        prios_host = [np.abs(rng_e.standard_normal(GB)) + 1e-6 for _ in range(8)]
+        own_rows = torch.zeros(1, dtype=torch.float64, device=dev)
 
-        def e2e_step(i):
-            u_dev.copy_(u_host[i % 8], non_blocking=True)
-            d = shard.sample_device(GB, BETA, u_dev, gather=True, out=outbuf)
-            loss, prio = shard.td_priority_update(q, qn, qt, t_act, t_rew, t_done, t_w, N_STEP, GAMMA, d["idx"],
-                                                  out_prio=o_res[:GB], out_loss=o_res[GB:])
-            res_host.copy_(o_res, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+        def e2e_round(i):
+            out = shard.sample_host(GB, BETA, u_host[i % 8])
+            idx_all = torch.full((GB,), -1, dtype=torch.int64, device=dev)
+            idx_all[out["lo"]:out["hi"]] = torch.as_tensor(out["idx"]).to(dev)
+            dist.all_reduce(idx_all, op=dist.ReduceOp.MAX)  # every rank learns the whole batch's indices (32 KB)
+            shard.update_priorities_host(idx_all.cpu().numpy(), prios_host[i % 8])
+            return out
 
         for i in range(3):
-            e2e_step(i)
+            out = e2e_round(i)
         barrier()
         t0 = time.perf_counter()
         for i in range(e2e_steps):
-            e2e_step(i)
+            out = e2e_round(i)
         torch.cuda.synchronize()
         e2e_s = time.perf_counter() - t0
-        h2d, d2h = 8 * GB, 4 * (GB + 1)
-        api = "sharded.ShardedReplay.sample_device()/td_priority_update(): uniforms from pinned host memory, loss+priorities to host"
+        rows = out["hi"] - out["lo"]
+        own_rows[0] = rows
+        dist.all_reduce(own_rows)
+        # bytes over PCIe per step, summed over the ranks: frames + scalars + weights + indices down; uniforms, indices, leaves up
+        d2h = int(own_rows.item()) * (2 * OBS_BYTES + 8 + 4 + 4 + 8) + world * 8 * GB * 2
+        h2d = world * (8 * GB * 3)
+        api = ("sharded.ShardedReplay.sample_host()/update_priorities_host() on every rank: host uniforms in, the rank's share of "
+               "the batch (frames included) out to pinned host memory, global (indices, priorities) back in")
     e2e_s = max_over_ranks(e2e_s)
     e2e = {"value": GB * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "steps": e2e_steps, "api": api}

@@ -124,6 +124,24 @@ def run_check(rank, world, device, size=40000, batch=None, steps=5, obs_shape=(2
         exp_leaves = po.apply_updates(sv[cap:], want, newp ** alpha)
         sv, mv = check_trees("step %d" % step)
         np.testing.assert_allclose(sv[cap:], exp_leaves, rtol=1e-15 * 4)
+    # the host-buffer forms (numpy in / numpy out on every rank, the reference's calling convention)
+    u = rng.random(batch)
+    h = shard.sample_host(batch, beta, u)
+    want = po.descend_many(sv, po.stratified_masses(po.prefix_total(sv, n_add - 1), batch, u))
+    lo, hi = h["lo"], h["hi"]
+    assert np.array_equal(h["idx"], want[lo:hi]) and np.all(want[lo:hi] // cap_l == rank)
+    assert hi - lo == int(np.sum(want // cap_l == rank))  # all of this rank's strata, nothing else (none at all is possible)
+    if hi > lo:
+        assert (lo == 0 or want[lo - 1] // cap_l < rank) and (hi == batch or want[hi] // cap_l > rank)
+    np.testing.assert_allclose(h["weights"], po.is_weights(sv, mv, want[lo:hi], n_add, beta), rtol=1e-9)
+    assert np.array_equal(h["obs"], obs[want[lo:hi]]) and np.array_equal(h["next_obs"], nxt[want[lo:hi]])
+    assert np.array_equal(h["act"], act[want[lo:hi]]) and np.array_equal(h["rew"], rew[want[lo:hi]]) and np.array_equal(h["done"], done[want[lo:hi]])
+    newp = rng.random(batch) + 1e-3
+    shard.update_priorities_host(want, newp)  # every rank gets the whole batch's pairs and keeps its own
+    exp_leaves = po.apply_updates(sv[cap:], want, po.pow_alpha(newp, alpha))
+    sv, mv = check_trees("host update")
+    assert np.array_equal(bits(sv[cap:]), bits(exp_leaves)), "host-path leaves must be bit-identical (libm pow)"
+    assert shard.status() == 0
     if log:
         log("multi-GPU parity ok on rank %d of %d: %d steps of %d strata, indices bit-exact vs the single-tree oracle, "
             "shard trees == subtrees, records through the mailboxes%s\n" % (rank, world, steps, batch, " (early publish)" if early_publish else ""))

@@ -23,21 +23,28 @@ def free_port():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs at least two GPUs")
-def test_sharded_replay_on_real_peers_matches_the_single_tree_oracle():
+def test_sharded_replay_on_real_peers_matches_the_single_tree_oracle(tmp_path):
+    import time
     n = torch.cuda.device_count()
     world = 1 << (n.bit_length() - 1)  # largest power of two
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), WORLD_SIZE=str(world))
+    logs = [open(tmp_path / ("rank%d.log" % r), "w+") for r in range(world)]
     procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "multi_gpu_parity.py")],
-                              env=dict(env, RANK=str(r), LOCAL_RANK=str(r)), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                              env=dict(env, RANK=str(r), LOCAL_RANK=str(r)), stdout=logs[r], stderr=subprocess.STDOUT, text=True)
              for r in range(world)]
-    outs = []
+    # a rank that fails leaves its peers waiting in a collective: watch all of them and stop the lot at the first failure
+    deadline = time.time() + 420
+    while time.time() < deadline and any(p.poll() is None for p in procs) and not any(p.poll() not in (None, 0) for p in procs):
+        time.sleep(0.5)
     for p in procs:
-        try:
-            outs.append(p.communicate(timeout=900)[0])
-        except subprocess.TimeoutExpired:
-            for q in procs:
-                q.kill()
-            raise
+        if p.poll() is None:
+            p.kill()
+        p.wait()
+    outs = []
+    for f in logs:
+        f.seek(0)
+        outs.append(f.read())
+        f.close()
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, "rank %d failed:\n%s" % (r, o[-3000:])
         assert "rank %d ok" % r in o and o.count("multi-GPU parity ok") == 3 and o.count("P2P delivery ok") == 1
