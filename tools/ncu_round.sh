@@ -6,8 +6,8 @@
 # usage (under gpurun): tools/ncu_round.sh r01d list
 R=${1:-r01}; STAGE=${2:-list}
 mkdir -p gpurun_out
-ARGS="--steps 48 --warmup 5 --no-cpu-baseline --eager"
-KERNELS='k_sample|k_gather_ldg|k_gather_tma|k_update_cluster'
+ARGS="--steps 48 --warmup 5 --no-cpu-baseline --no-extras --eager"
+KERNELS='k_sample|k_gather_bal|k_gather_ldg|k_gather_tma|k_update_cluster'
 case $STAGE in
 list)
   python bench.py $ARGS > gpurun_out/plain_$R.log 2>&1 &&

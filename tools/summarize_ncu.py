@@ -50,6 +50,26 @@ for rep in ("prof_%s.ncu-rep" % tag, "prof_aql_%s.ncu-rep" % tag):
     out.append(",".join(units[i] for i in idx))
     for r in rows[2:]:
         out.append(",".join('"%s"' % r[i] if "," in r[i] else r[i] for i in idx))
+    if rep.startswith("prof_%s" % tag) and "dram__bytes_read.sum" in hdr:  # what bench.py reports as roofline.traffic
+        import json
+        ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        for r in rows[2:]:
+            if "k_gather" in r[ki]:
+                tot = float(r[ri].replace(",", "")) * scale[units[ri]] + float(r[wi].replace(",", "")) * scale[units[wi]]
+                name = "k_gather_bal" if "k_gather_bal" in r[ki] else ("k_gather_tma" if "tma" in r[ki] else "k_gather_ldg<16>")
+                json.dump({"kernel": name, "dram_bytes_per_launch": int(tot), "source": "ncu --set full, %s" % rep,
+                           "dram__bytes_read.sum": r[ri] + " " + units[ri], "dram__bytes_write.sum": r[wi] + " " + units[wi]},
+                          open(os.path.join(P, "%s_gather_traffic.json" % tag), "w"))
+                break
+    if rep.startswith("prof_aql") and "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active" in hdr:
+        import json
+        ti = hdr.index("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active")
+        for r in rows[2:]:
+            if "k_aql_q" in r[hdr.index("Kernel Name")]:
+                json.dump({"sm__pipe_tensor_cycles_active_pct": float(r[ti]), "source": "ncu --set full, %s" % rep},
+                          open(os.path.join(P, "%s_aql_tensor_pipe.json" % tag), "w"))
+                break
 dst = os.path.join(P, "%s_ncu_summary.csv" % tag)
 open(dst, "w").write("\n".join(out) + "\n")
 print(open(dst).read())
