@@ -74,6 +74,7 @@ struct per_buffer_s {
     bool rec_published;        //   ... and one has done so since the last sample
     int pdl;                   // per_tune("pdl", bits): programmatic dependent launch for 1 sampling, 2 gather, 4 update kernels
     int upd_cluster_max;       // per_tune("update_cluster_max", items): larger plain updates take the multi-launch form
+    int upd_max_ctas;          // per_tune("update_ctas", n): cap on the cluster size of the one-launch update (0: none)
     int sorted_update;         // per_tune("sorted_update", 0/1): updates of the sample just drawn take the sorted fast path
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
@@ -155,14 +156,43 @@ int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cuda
         return PER_OK;
     }
     if (a.n <= (td || a.range || a.cluster_max <= 0 ? UPD_CLUSTER_MAX_ITEMS : a.cluster_max)) {
-        // one launch: a cluster of CTAs, 64 items (8 lanes each) per CTA and round
-        int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));
+        // one launch: a cluster of CTAs (at most 16 where the device offers the non-portable size, else 8)
+        static int max_ctas = 0;
+        if (!max_ctas) {
+            PER_CUDA(cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, UPD_SMEM_BYTES));
+            max_ctas = 8;
+            if (cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+                cudaLaunchConfig_t probe;
+                memset(&probe, 0, sizeof probe);
+                probe.gridDim = dim3(UPD_MAX_CTAS);
+                probe.blockDim = dim3(UPD_THREADS);
+                probe.dynamicSmemBytes = UPD_SMEM_BYTES;
+                cudaLaunchAttribute pa[1];
+                pa[0].id = cudaLaunchAttributeClusterDimension;
+                pa[0].val.clusterDim.x = UPD_MAX_CTAS;
+                pa[0].val.clusterDim.y = 1;
+                pa[0].val.clusterDim.z = 1;
+                probe.attrs = pa;
+                probe.numAttrs = 1;
+                int nclusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, k_update_cluster, &probe) == cudaSuccess && nclusters >= 1) max_ctas = UPD_MAX_CTAS;
+            }
+            cudaGetLastError();
+        }
+        // 8 CTAs by default: A/B on one box, 16 CTAs cost +0.3 us per step at 512 items (the phases are latency chains, not
+        // sector throughput; the larger cluster's barriers cost more than the halved per-SM work saves).  16 where it keeps a
+        // sorted batch of 1 025 .. 2 048 items on the per-CTA climb (<= 128 items per CTA), or when asked for (per_tune).
+        int limit = 8;
+        if (a.max_ctas > 0) limit = a.max_ctas < max_ctas ? a.max_ctas : max_ctas;
+        else if (a.sorted_idx && a.sorted_fast && a.n > 8 * SORT_SLICE_MAX && a.n <= 16 * SORT_SLICE_MAX) limit = max_ctas;
+        int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));  // 64 items per CTA and round
         if (ncta < 1) ncta = 1;
-        if (ncta > UPD_MAX_CTAS) ncta = UPD_MAX_CTAS;
+        if (ncta > limit) ncta = limit;
         cudaLaunchConfig_t cfg;
         memset(&cfg, 0, sizeof cfg);
         cfg.gridDim = dim3(ncta);
         cfg.blockDim = dim3(UPD_THREADS);
+        cfg.dynamicSmemBytes = UPD_SMEM_BYTES;
         cfg.stream = s;
         cudaLaunchAttribute attr[2];
         attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -987,6 +1017,10 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->upd_cluster_max = (int)value;
         return PER_OK;
     }
+    if (!strcmp(key, "update_ctas")) {  // largest cluster of the one-launch update (0: what the device gives, 16 on B200)
+        b->upd_max_ctas = (int)value;
+        return PER_OK;
+    }
     if (!strcmp(key, "sorted_update")) {
         b->sorted_update = value != 0;
         return PER_OK;
@@ -1049,6 +1083,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch;
     a.sorted_fast = b->sorted_update;
     a.cluster_max = b->upd_cluster_max;
+    a.max_ctas = b->upd_max_ctas;
     a.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
     if (a.sorted_idx) b->last_sample_idx = nullptr;  // the binding to that sample ends with its first update (see per_sample_sharded)
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);

@@ -30,9 +30,12 @@ constexpr int LIFT = 5;                    // generations recomputed per sparse 
 constexpr int LIFT_LANES = 16;             // lanes that share one item in a sparse round: 2^(LIFT-1), 16 B each
 constexpr int UPD_CLUSTER_MAX_ITEMS = 4096;  // largest batch the one-launch (cluster) form takes
 constexpr int UPD_SLICE_MAX = UPD_CLUSTER_MAX_ITEMS / 8;  // items per CTA at most (8 CTAs above 448 items)
-constexpr int UPD_STAGE_FLOATS = 10240;      // shared staging for Q rows (40 KB; its first 32 KB double as the top-of-tree buffers)
+constexpr int UPD_STAGE_FLOATS = 12288;      // DYNAMIC shared memory: staging for Q rows (48 KB; its first 32 KB double as the top-of-tree
+                                             // buffers, the stage-2 border staging sits behind them)
+constexpr int UPD_SMEM_BYTES = UPD_STAGE_FLOATS * (int)sizeof(float);
 constexpr int UPD_THREADS = 1024;           // 64 items x 16 lanes per sparse pass
-constexpr int UPD_MAX_CTAS = 8;            // portable cluster size
+constexpr int UPD_MAX_CTAS = 16;           // largest cluster the kernel is written for (non-portable size, opted into by the host;
+                                           // used for sorted batches of 1 025 .. 2 048 items and on request, see run_update)
 
 enum LeafSrc : int {
     LEAF_GIVEN = 0,     // float64 leaves supplied by the caller
@@ -70,6 +73,7 @@ struct UpdArgs {
     int64_t rec_need;         //   leaves of this slice inside the global prefix [0, len-1)
     int64_t rec_len;          //   local len
     int cluster_max;          // host side: plain updates above this many items use the multi-launch form (<= 0: the built-in limit)
+    int max_ctas;             // host side: cap on the cluster size of the one-launch form (<= 0: none)
     int sorted_fast;          // sorted_idx: take the per-CTA climb (sorted fast path) instead of the level-synchronous rounds
     int sorted_idx;           // the indices are non-decreasing (they are the stratified sample just drawn): equal
                               // indices are adjacent, so "a later duplicate wins" needs one look at idx[j+1], no atomics
@@ -352,7 +356,7 @@ __device__ __forceinline__ int lca_level(int64_t x, int64_t y) { return x == y ?
 //   phase 4  CTA 0: dense rebuild of depths top_depth(L)..0 in shared memory
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, TdArgs td, int fused_td, int skip_update) {
-    __shared__ __align__(16) float s_raw[UPD_STAGE_FLOATS];  // phase 0: staged Q rows; phases 1-2: leaf values; phase 4: tree tops
+    extern __shared__ __align__(16) float s_raw[];           // UPD_STAGE_FLOATS floats. phase 0: staged Q rows; phases 1-2: leaf values; phase 4: tree tops
     __shared__ int s_k[UPD_SLICE_MAX];                       // leaf index of each surviving item of the slice, else -1
     __shared__ float s_tdv[UPD_SLICE_MAX];                   // |td| of the slice
     double *s_tree = reinterpret_cast<double *>(s_raw);

@@ -431,6 +431,8 @@ def main():
                          ("PER_GATHER_VBYTES", b"gather_vbytes")):
             if os.environ.get(env):
                 pn.check(pn.lib.per_tune(hh, key, int(os.environ[env])))
+    if os.environ.get("PER_UPDATE_CTAS") is not None:  # A/B: cap on the update kernel's cluster size (8 = the portable limit)
+        pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"update_ctas", int(os.environ["PER_UPDATE_CTAS"])))
     if os.environ.get("PER_SORTED_UPDATE") is not None:
         pn.check(pn.lib.per_tune(buf._h if world == 1 else shard._h, b"sorted_update", int(os.environ["PER_SORTED_UPDATE"])))
     if os.environ.get("PER_PDL") is not None:  # A/B switch for tools/pdl_ab.sh (default: on)

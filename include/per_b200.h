@@ -387,6 +387,8 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * update are launched with programmatic stream serialization and begin with
  * griddepcontrol.wait, so their launch and prologue overlap the tail of the kernel in front;
  * measured on B200 the cluster launch of the update loses from it, profiles/r01_notes.md);
+ * "update_ctas" (cap on the thread-block cluster of the one-launch update: 0 = the library's choice, 8 CTAs, or 16 for
+ * sorted batches of 1 025 .. 2 048 items; 16 needs the device's non-portable cluster size);
  * "sorted_update" (default 1: an update of exactly the index buffer the last sample wrote takes
  * the sorted fast path of update_kernels.cuh; 0 = always the level-synchronous rounds);
  * "early_publish" (default 0; needs per_shard_attach_exchange): every priority update ends by

@@ -53,7 +53,7 @@ def priorities(kind, n, gen):
 
 
 @pytest.mark.parametrize("size,batch", [(1 << 16, 512), (1 << 16, 64), (1 << 16, 1000), (5000, 512), (3000, 777), (1 << 11, 256),
-                                        (700, 128), (40, 16), (1 << 20, 512), (1 << 14, 1)])
+                                        (700, 128), (40, 16), (1 << 20, 512), (1 << 14, 1), (1 << 20, 2048), (1 << 16, 1300), (1 << 22, 1025)])
 @pytest.mark.parametrize("kind", ["uniform", "few_hot", "one_block", "two_ends", "steps"])
 def test_sorted_path_equals_generic_path(mods, size, batch, kind):
     memory, pn = mods
