@@ -626,6 +626,10 @@ def main():
         """Runs exactly n_steps steps; returns ms (max over ranks)."""
         t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
+        # an untimed ~100 us spin in front of the start event: the GPU is busy while the host enqueues the event and the
+        # first graph, so the K steps start the moment the event fires (otherwise the host's graph-launch latency, ~15 us,
+        # sits inside a timed region that is only 0.6 ms long at K = 20)
+        torch.cuda._sleep(200000)
         t0.record(stream)
         if use_graphs:
             assert n_steps == K
@@ -722,6 +726,8 @@ def main():
     if graphs is not None:
         cap_tl = 8192
         pn.check(lib.per_tune(h, b"timeline", cap_tl))
+        if args.timeline:
+            pn.check(lib.per_tune(h, b"update_trace", 1))  # + the update kernel's own phase stamps (last launch)
         with torch.cuda.stream(side):
             sp_side = pn.stream_ptr(side)
             probe = [capture(lambda j=j: full_block(j * GRAPH_STEPS_MAX, GRAPH_STEPS_MAX, sp_side)) for j in range(3)]
@@ -738,6 +744,14 @@ def main():
         barrier()
         pn.check(lib.per_timeline(h, arr, cap_tl, pn.C.byref(cnt), sp))
         pn.check(lib.per_tune(h, b"timeline", 0))
+        if args.timeline:
+            st16 = (pn.C.c_int64 * 16)()
+            pn.check(lib.per_update_trace(h, st16, sp))
+            pn.check(lib.per_tune(h, b"update_trace", 0))
+            ph = ["wait passed", "TD done", "arbitration", "leaves/barrier", "rounds done", "top rebuilt", "TD staged", "CTA max",
+                  "TD cl.sync", "batch max", "leaves+sib in", "climb done", "top loaded", "top written"]
+            order = [6, 7, 8, 9, 1, 10, 2, 11, 3, 4, 12, 5, 13]
+            sys.stderr.write("rank %d update phases (us): " % rank + " | ".join("%s %.2f" % (ph[i], (st16[i] - st16[0]) / 1e3) for i in order if st16[i] > st16[0]) + "\n")
         ent = sorted(((int(arr[i]) & ((1 << 56) - 1), (int(arr[i]) >> 56) & 0xff) for i in range(cnt.value)))
         names = {7: "update entered", 8: "update past wait", 12: "TD done", 9: "update CTA0 done", 1: "sample entered",
                  10: "records in", 2: "sample past wait", 11: "strata known", 3: "sample CTA0 done", 4: "gather entered",
