@@ -151,7 +151,7 @@ struct SampleArgs {
 };
 
 constexpr int SHARD_REC = 4;   // doubles per shard record
-constexpr int MAIL_SLOT = 8;   // doubles per mailbox slot: record[4], flag (u64 bits), 3 pad  (64 B)
+constexpr int MAIL_SLOT = 8;   // 64-bit words per mailbox slot (64 B): the record's 4 doubles as 8 self-validating words, see below
 
 __device__ __forceinline__ u64 global_timer_ns() {
     u64 t;
@@ -159,23 +159,29 @@ __device__ __forceinline__ u64 global_timer_ns() {
     return t;
 }
 
-__device__ __forceinline__ u64 ld_acquire_sys(const u64 *p) {
-    u64 v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(u64 *p, u64 v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
 // One warp: computes this shard's record once and stores it where asked: into `rec_out` (4 doubles,
-// the all-gather path) and / or, with the epoch flag, into the slot [epoch & 1][rank] of every rank's
-// mailbox (lane p -> rank p; plain stores to peer-mapped addresses travel over NVLink).  The flag is a
-// system-scope release store, polled with acquire loads.
+// the all-gather path) and / or into the slot [epoch & 1][rank] of every rank's mailbox (lane p -> rank p;
+// plain stores to peer-mapped addresses travel over NVLink).
+//
+// Mailbox wire format — no flag, no fence.  A slot is 8 words of 64 bits; word 2 i carries the HIGH 32 bits of the record's
+// i-th double in its upper half and word 2 i + 1 the LOW 32 bits, each with the low 32 bits of the sample's epoch in its lower
+// half.  Every word is one aligned 8-byte store, which is single-copy atomic, so a reader that sees the epoch it waits for in
+// a word has that word's payload whole, whatever order the eight stores arrive in: it polls until all eight carry the epoch.
+// A release store of a separate flag would first have to wait for the record's stores to be acknowledged by the peer — an
+// NVLink round trip (~2 us) at the end of the update kernel, in front of every sample of every rank.  Slots are double-
+// buffered by epoch parity, so a word of epoch e is overwritten only by epoch e + 2, which no reader confuses with e.
 // The record (one per shard and sample call): the two roots, and the shard-local part of the
 // reference's  sum(0, len-1)  chain (memory.py:244): the prefix over this shard's first `need_local`
 // leaves when the global prefix ends inside this shard.  Nodes are read through L2 (the caller may
 // have just written them).
+__device__ __forceinline__ void st_relaxed_sys_u64(u64 *p, u64 v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ u64 ld_relaxed_sys_u64(const u64 *p) {
+    u64 v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void emit_record_values(const double rs, const double rm, const double partial, int64_t len_local,
                                                    double *rec_out, double *const *peer_mailbox, int n_shards, int rank, u64 epoch) {
     const int lane = threadIdx.x & 31;
@@ -186,10 +192,15 @@ __device__ __forceinline__ void emit_record_values(const double rs, const double
         rec_out[3] = (double)len_local;
     }
     if (peer_mailbox && lane < n_shards) {
-        double *slot = peer_mailbox[lane] + ((epoch & 1) * n_shards + rank) * MAIL_SLOT;
-        reinterpret_cast<double2 *>(slot)[0] = make_double2(rs, rm);
-        reinterpret_cast<double2 *>(slot)[1] = make_double2(partial, (double)len_local);
-        st_release_sys(reinterpret_cast<u64 *>(slot + SHARD_REC), epoch);  // orders the record in front of the flag
+        u64 *slot = reinterpret_cast<u64 *>(peer_mailbox[lane]) + ((epoch & 1) * n_shards + rank) * MAIL_SLOT;
+        const u64 tag = epoch & 0xffffffffull;
+        const double vals[SHARD_REC] = {rs, rm, partial, (double)len_local};
+#pragma unroll
+        for (int i = 0; i < SHARD_REC; ++i) {
+            const u64 bits = (u64)__double_as_longlong(vals[i]);
+            st_relaxed_sys_u64(slot + 2 * i, (bits & 0xffffffff00000000ull) | tag);
+            st_relaxed_sys_u64(slot + 2 * i + 1, (bits << 32) | tag);
+        }
     }
 }
 __device__ __forceinline__ void emit_record(const double *sum, const double *mnn, int64_t cap, int64_t need_local, int64_t len_local,
@@ -203,21 +214,47 @@ __device__ __forceinline__ void publish_record(const double *sum, const double *
     emit_record(sum, mnn, cap, need_local, len_local, nullptr, peer_mailbox, n_shards, rank, epoch);
 }
 
-// All lanes of the calling warp return once every rank's slot of this epoch has arrived in the
-// local mailbox (or after 2 s, with PER_STATUS_EXCHANGE_TIMEOUT set — never a hang).
-__device__ __forceinline__ void await_records(const double *mailbox, int n_shards, u64 epoch, u64 *status) {
+// All lanes of the calling warp return once every rank's slot of this epoch has arrived in the local mailbox (or after
+// 2 s, with PER_STATUS_EXCHANGE_TIMEOUT set — never a hang); the decoded records (4 doubles per rank) are left in `out`
+// (shared memory of the calling CTA, n_shards * SHARD_REC doubles).  Lane l polls the words l, l + 32, ... of the
+// n_shards * 8 words of this epoch's half of the mailbox.
+__device__ __forceinline__ void await_records(const double *mailbox, int n_shards, u64 epoch, u64 *status, double *out) {
     const int lane = threadIdx.x & 31;
-    if (lane < n_shards) {
-        const u64 *flag = reinterpret_cast<const u64 *>(mailbox + ((epoch & 1) * n_shards + lane) * MAIL_SLOT + SHARD_REC);
-        if (ld_acquire_sys(flag) < epoch) {
-            const u64 t0 = global_timer_ns();
-            while (ld_acquire_sys(flag) < epoch) {
-                __nanosleep(100);  // back off: thousands of pollers on one L2 line delay the very write they wait for
-                if (global_timer_ns() - t0 > 2000000000ull) {
-                    atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
-                    break;
-                }
+    const u64 *half = reinterpret_cast<const u64 *>(mailbox) + (epoch & 1) * n_shards * MAIL_SLOT;
+    const u64 tag = epoch & 0xffffffffull;
+    const int nwords = n_shards * MAIL_SLOT;  // <= 128: at most 4 words per lane
+    u64 w[4] = {0, 0, 0, 0};
+    u64 t0 = 0;
+    bool started = false;
+    while (true) {
+        bool all = true;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int k = lane + 32 * j;
+            if (k < nwords && (w[j] & 0xffffffffull) != tag) {
+                w[j] = ld_relaxed_sys_u64(half + k);
+                all = all && (w[j] & 0xffffffffull) == tag;
             }
+        }
+        if (__all_sync(0xffffffffu, all)) break;
+        if (!started) {
+            t0 = global_timer_ns();
+            started = true;
+        }
+        __nanosleep(100);  // back off: thousands of pollers on one L2 line delay the very write they wait for
+        if (global_timer_ns() - t0 > 2000000000ull) {
+            if (lane == 0) atomicOr(status, (u64)PER_STATUS_EXCHANGE_TIMEOUT);
+            break;
+        }
+    }
+    // word k = 8 r + 2 i + h: rank r, value i, half h (0 = high 32 bits).  Pairs (h = 0, 1) sit in adjacent lanes.
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int k = lane + 32 * j;
+        const u64 other = __shfl_down_sync(0xffffffffu, w[j], 1);
+        if (k < nwords && (k & 1) == 0) {
+            const u64 bits = (w[j] & 0xffffffff00000000ull) | (other >> 32);
+            out[k >> 1] = __longlong_as_double((long long)bits);
         }
     }
     __syncwarp();
@@ -434,19 +471,16 @@ struct ShardView {
     double root_sum, root_min, seg;
 };
 
-__device__ __forceinline__ ShardView shard_view(const SampleArgs &a, const u64 epoch, const int lane) {
+__device__ __forceinline__ ShardView shard_view(const SampleArgs &a, const double *mail_recs, const int lane) {
     const int N = a.n_shards;
-    const double *recs = a.recs;
-    int rec_stride = SHARD_REC;
-    if (a.use_mailbox) {  // the records of this epoch are in the mailbox (the caller waited for them)
-        recs = a.mailbox + (epoch & 1) * N * MAIL_SLOT;
-        rec_stride = MAIL_SLOT;
-    }
+    // the records: the caller's all-gathered array, or what await_records decoded out of the mailbox
+    const double *recs = a.use_mailbox ? mail_recs : a.recs;
+    const int rec_stride = SHARD_REC;
     ShardView v;
     // Top of the virtual tree, one node per lane: lanes N..2N-1 hold the shard roots,
     // lanes 1..N-1 their pairwise sums built level by level like memory.py:82-87.
-    double top = (lane >= N && lane < 2 * N) ? __ldcg(recs + (lane - N) * rec_stride) : 0.0;
-    double mn = lane < N ? __ldcg(recs + lane * rec_stride + 1) : __longlong_as_double(0x7ff0000000000000LL);
+    double top = (lane >= N && lane < 2 * N) ? recs[(lane - N) * rec_stride] : 0.0;
+    double mn = lane < N ? recs[lane * rec_stride + 1] : __longlong_as_double(0x7ff0000000000000LL);
     // p_total = sum over global leaves [0, need): shard-aligned blocks come from the top
     // tree (one per set bit of need / cap), the rest from the owning shard's record.
     const int64_t need = a.n_rows - 1;
@@ -455,7 +489,7 @@ __device__ __forceinline__ ShardView shard_view(const SampleArgs &a, const u64 e
     double acc = 0.0;
     bool first = true;
     if (need_lo) {
-        acc = __ldcg(recs + need_hi * rec_stride + 2);
+        acc = recs[need_hi * rec_stride + 2];
         first = false;
     }
     for (int w = N >> 1; w >= 1; w >>= 1) {
@@ -569,6 +603,7 @@ constexpr int SAMPLE_THREADS = 128;  // one CTA per 4 owned strata: the descents
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
     __shared__ double s_top[32];
+    __shared__ double s_recs[16 * SHARD_REC];  // the records of this sample, decoded out of the mailbox by warp 0
     __shared__ double s_scal[3];
     __shared__ int64_t s_range[2];
     const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
@@ -592,7 +627,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
             const u64 t0 = (blockIdx.x == 0 && lane == 0) ? global_timer_ns() : 0;
             if (blockIdx.x == 0 && !a.skip_publish)
                 publish_record(a.sum, a.mnn, a.cap, a.rec_need, a.rec_len, a.peer_mailbox, a.n_shards, a.rank, epoch);
-            await_records(a.mailbox, a.n_shards, epoch, a.status);
+            await_records(a.mailbox, a.n_shards, epoch, a.status, s_recs);
             if (blockIdx.x == 0 && lane == 0 && a.d_wait_stats) {
                 const u64 dt = global_timer_ns() - t0;
                 atomicAdd(a.d_wait_stats, 1ull);
@@ -600,7 +635,7 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
                 atomicMax(a.d_wait_stats + 2, dt);
             }
         }
-        const ShardView v = shard_view(a, epoch, lane);
+        const ShardView v = shard_view(a, s_recs, lane);
         if (tl_on) tl_stamp(a.tl, 1, 10);  // records in, view built
         if (early) pdl_wait();
         if (tl_on) tl_stamp(a.tl, 2, 2);   // the kernel in front has retired

@@ -914,9 +914,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
             }
             if (chains) __syncthreads();
         }
-        // the top in shared memory; the record leaves BEFORE the write-out, so that its system-scope release does not
-        // have to wait for the two thousand node stores to be acknowledged (the record's readers need none of them,
-        // and this rank's own next sample waits for this kernel to retire anyway)
+        // the top in shared memory; the record leaves BEFORE the write-out (its readers need none of the node stores,
+        // and this rank's own next sample waits for this kernel to retire anyway): eight self-validating words per
+        // peer, no fence (see emit_record_values)
         dense_build(a.t, 1, top, s_sum, s_min);
         UPD_TRACE(5);
         if (want_rec && tid < 32) {

@@ -349,8 +349,9 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
  * memory its peers can write (per_ipc_alloc in one process, per_ipc_open in the others; NVLink
  * peer access).  After per_shard_attach_exchange, per_sample_sharded may be called with
  * d_records == NULL: the sampling kernel's first warp then computes this shard's record, stores
- * it into every rank's mailbox (plain stores to peer-mapped addresses + a system-scope fence +
- * an epoch flag), and every warp waits for the n_shards flags of this sample before it descends
+ * it into every rank's mailbox (eight aligned 8-byte stores to peer-mapped addresses, each carrying 32 bits of the record and
+ * the sample's epoch: no flag and no fence — a word that shows the awaited epoch is whole, in whatever order the words
+ * arrive), and one warp per CTA polls until every word of all n_shards slots of this sample shows its epoch before the CTA descends
  * — compute and exchange in ONE kernel, no NCCL launch, capturable in a CUDA graph.  Slots are
  * double-buffered by sample parity (a rank can be at most one sample ahead of its slowest peer,
  * because its next sample needs that peer's next record).  A peer that never publishes does not
