@@ -3,15 +3,17 @@
 //
 // A transition row is two observations (uint8[4,84,84] = 28 224 B each on Atari), an int64
 // action, float32 reward and done, and an optional extra row (AQL's a_mu).  Rows are padded
-// to a multiple of 16 B so that every row start is 16-B aligned; each big row is cut into
-// pieces of at most PIECE_BYTES, one warp per piece.  Two movers for a piece:
-//   k_gather_ldg  (default)  sixteen 16-byte streaming loads in flight per lane, then the stores: the whole
-//                 piece sits in the warp's registers; no shared memory;
-//   k_gather_tma  HBM -> shared memory -> HBM as two TMA bulk copies (cp.async.bulk, SASS UBLKCP) issued by
-//                 ONE lane per warp through an mbarrier ring: no registers are staged, the LSU is idle.
-// Alone they take the same time; inside the learner step the first one wins because the second one's
-// 226 KB/SM of dynamic shared memory slows the tree kernels before and after it (profiles/r01_notes.md).
-// k_gather_cast (gather + uint8 -> float widening) stages through shared memory like k_gather_tma.
+// to a multiple of 16 B so that every row start is 16-B aligned.  Three movers (per_tune "gather_mode"):
+//   k_gather_bal  (2, default) the batch as one linear space of 16-byte vectors cut into equal shares, one per warp of a
+//                 grid sized to exactly the resident CTA slots; register-staged streaming loads / stores;
+//   k_gather_ldg  (1) each row cut into pieces of at most PIECE_BYTES, one warp per piece, sixteen 16-byte streaming
+//                 loads in flight per lane, then the stores;
+//   k_gather_tma  (0) pieces move HBM -> shared memory -> HBM as two TMA bulk copies (cp.async.bulk, SASS UBLKCP) issued
+//                 by ONE lane per warp through an mbarrier ring: no registers are staged, the LSU is idle.
+// Alone: 9.3 / 10.6 / 10.5 us per 512 rows (profiles/r02_gather_sweep.txt); inside the learner step the TMA mover's
+// 226 KB/SM of dynamic shared memory also slows the tree kernels before and after it (profiles/r01_notes.md).
+// k_gather_cast (gather + uint8 -> float widening) stages through shared memory like k_gather_tma; k_gather_cast_nhwc
+// writes channels-last rows.
 // Algorithmic traffic per sampled transition: read 2*28 224+16 B, write the same.
 #pragma once
 #include <cuda_bf16.h>

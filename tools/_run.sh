@@ -1,3 +1,2 @@
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 4 --steps 20 --warmup 5 > gpurun_out/r02_bench_n4.json 2> gpurun_out/r02_bench_n4.err; echo "N=4 rc=$? $(grep -o '"value": [0-9.]*' gpurun_out/r02_bench_n4.json | head -2 | tr '\n' ' ')"
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 20 --warmup 5 > gpurun_out/r02_bench_n2.json 2> gpurun_out/r02_bench_n2.err; echo "N=2 rc=$? $(grep -o '"value": [0-9.]*' gpurun_out/r02_bench_n2.json | head -2 | tr '\n' ' ')"
-timeout 600 python bench.py --impl reference --gpus 2 --steps 20 --warmup 5 | cut -c1-160
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
