@@ -144,17 +144,28 @@ __device__ __forceinline__ Piece decode_piece(const GatherArgs &a, int64_t w, in
     return p;
 }
 
+// Owned strata of a sharded sample (see owned_range in update_kernels.cuh).  ONE thread per CTA reads the three tag words
+// and hands the range to the others through shared memory: with every warp of the grid reading them (3 552 warps x 3
+// loads of one 32-byte sector) the requests queue up at a single L2 slice and the whole gather starts ~1.7 us late
+// (measured: bound gather 11.05 -> see profiles/r02_notes.md).  Must be called by all threads of the CTA.
 __device__ __forceinline__ void gather_range(const GatherArgs &a, int64_t &first, int64_t &last) {
     first = 0;
     last = a.batch;
-    if (!a.range) return;
-    const u64 epoch = __ldcg(a.range), tl = __ldcg(a.range + 2), th = __ldcg(a.range + 3);
-    if ((tl >> 32) != (epoch & 0xffffffffu) || (th >> 32) != (epoch & 0xffffffffu)) {
-        first = last = 0;
-        return;
+    if (!a.range) return;  // uniform over the grid
+    __shared__ int64_t s_range[2];
+    if (threadIdx.x == 0) {
+        const u64 epoch = __ldcg(a.range), tl = __ldcg(a.range + 2), th = __ldcg(a.range + 3);
+        int64_t f = 0, l = 0;  // tags of another epoch: this shard owned no stratum of that sample
+        if ((tl >> 32) == (epoch & 0xffffffffu) && (th >> 32) == (epoch & 0xffffffffu)) {
+            f = (int64_t)(0xffffffffu - (unsigned)(tl & 0xffffffffu));
+            l = (int64_t)(th & 0xffffffffu);
+        }
+        s_range[0] = f;
+        s_range[1] = l;
     }
-    first = (int64_t)(0xffffffffu - (unsigned)(tl & 0xffffffffu));
-    last = (int64_t)(th & 0xffffffffu);
+    __syncthreads();
+    first = s_range[0];
+    last = s_range[1];
 }
 
 __device__ __forceinline__ void gather_scalars(const GatherArgs &a, int64_t first, int64_t last) {
