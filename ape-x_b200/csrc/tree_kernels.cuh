@@ -385,8 +385,31 @@ __device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int6
     }
 }
 
+// What every query of a launch shares — the block under the root, the two roots, the prefix total — is fetched by ONE
+// warp per CTA and handed to the others through shared memory: with every warp of the grid fetching it, 512 warps queue
+// up at the same ~50 L2 sectors before their first descent step.
+struct SampleShared {
+    double blk[4][32];  // DescentBlock of the root, by register and lane
+    double root_sum, root_min, total;
+};
+__device__ __forceinline__ DescentBlock block_from_shared(const SampleShared &sh, const int lane) {
+    DescentBlock b;
+    b.r0 = sh.blk[0][lane];
+    b.r1 = sh.blk[1][lane];
+    b.r2 = sh.blk[2][lane];
+    b.r3 = sh.blk[3][lane];
+    return b;
+}
+__device__ __forceinline__ void block_to_shared(SampleShared &sh, const DescentBlock &b, const int lane) {
+    sh.blk[0][lane] = b.r0;
+    sh.blk[1][lane] = b.r1;
+    sh.blk[2][lane] = b.r2;
+    sh.blk[3][lane] = b.r3;
+}
+
 // Unsharded: one warp per query.
 __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
+    __shared__ SampleShared sh;
     const bool tl_on = a.tl && blockIdx.x == 0 && threadIdx.x == 0;
     if (tl_on) tl_stamp(a.tl, 0, 1);
     pdl_launch_dependents();
@@ -394,19 +417,30 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
     if (tl_on) tl_stamp(a.tl, 1, 2);
     const int lane = threadIdx.x & 31;
     const int64_t q = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const double uq = (q < a.batch && lane == 0) ? a.u[q] : 0.0;  // requested beside the shared part
+    if (threadIdx.x < 32) {
+        const DescentBlock left = root_block(a, lane);  // in flight together with the loads of the prefix total
+        const double rs = a.sum[1], rm = a.mnn ? a.mnn[1] : 0.0;
+        const double total = a.direct_mass ? 0.0 : warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
+        block_to_shared(sh, left, lane);
+        if (lane == 0) {
+            sh.root_sum = rs;
+            sh.root_min = rm;
+            sh.total = total;
+        }
+    }
+    __syncthreads();
     if (q >= a.batch) return;  // whole warps take the same side
-    const DescentBlock left = root_block(a, lane);  // in flight together with the loads of the prefix total
-    const double root_sum = a.sum[1];
-    double mass;
+    const DescentBlock left = block_from_shared(sh, lane);
+    const double root_sum = sh.root_sum;
+    double mass = shfl_f64(uq, 0);
     if (a.direct_mass) {
-        mass = a.u[q];
         if (lane == 0 && !(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
     } else {
-        const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
-        const double seg = __ddiv_rn(total, (double)a.batch);                // memory.py:245
-        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg)); // memory.py:247
+        const double seg = __ddiv_rn(sh.total, (double)a.batch);            // memory.py:245
+        mass = __dadd_rn(__dmul_rn(mass, seg), __dmul_rn((double)q, seg));  // memory.py:247
     }
-    descend_and_emit(a, q, lane, mass, left, root_sum, a.mnn ? a.mnn[1] : 0.0, 0);
+    descend_and_emit(a, q, lane, mass, left, root_sum, sh.root_min, 0);
     if (tl_on) tl_stamp(a.tl, 2, 3);
 }
 
@@ -603,6 +637,7 @@ constexpr int SAMPLE_THREADS = 128;  // one CTA per 4 owned strata: the descents
 
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
     __shared__ double s_top[32];
+    __shared__ SampleShared sh;                // the block under this shard's root: fetched by warp 0 for the whole CTA
     __shared__ double s_recs[16 * SHARD_REC];  // the records of this sample, decoded out of the mailbox by warp 0
     __shared__ double s_scal[3];
     __shared__ int64_t s_range[2];
@@ -639,9 +674,10 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         if (tl_on) tl_stamp(a.tl, 1, 10);  // records in, view built
         if (early) pdl_wait();
         if (tl_on) tl_stamp(a.tl, 2, 2);   // the kernel in front has retired
-        left = root_block(a, lane);
+        left = root_block(a, lane);  // in flight while the owned strata are searched
         int64_t lo, hi;
         owned_strata(a, v, lane, lo, hi);
+        block_to_shared(sh, left, lane);
         s_top[lane] = v.top;
         if (lane == 0) {
             s_scal[0] = v.root_sum;
@@ -656,10 +692,10 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
         }
     } else {
         if (early) pdl_wait();
-        left = root_block(a, lane);  // the same for every query: requested before the range is known
     }
     if (tl_on) tl_stamp(a.tl, 3, 11);  // owned strata known
     __syncthreads();
+    if (warp != 0) left = block_from_shared(sh, lane);  // the same for every query of the launch
     if (threadIdx.x == 32) {
         // warp 0 of this CTA has consumed the epoch: the last CTA to say so advances it (nothing in this launch
         // reads it again; the kernels behind this one see the new value)
