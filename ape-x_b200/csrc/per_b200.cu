@@ -76,6 +76,7 @@ struct per_buffer_s {
     int upd_cluster_max;       // per_tune("update_cluster_max", items): larger plain updates take the multi-launch form
     int upd_max_ctas;          // per_tune("update_ctas", n): cap on the cluster size of the one-launch update (0: none)
     int sorted_update;         // per_tune("sorted_update", 0/1): updates of the sample just drawn take the sorted fast path
+    int dense_lmax;            // per_tune("dense_update_lmax", log2 leaves): bound updates of trees up to this depth take the dense form (0: never)
     int update_trace;          // per_tune("update_trace", 1): phase timestamps of the update kernel at scal[11..16]
     const int64_t *last_sample_idx;  // sharded replay: output buffer and size of the last per_sample_sharded; gather /
     int64_t last_sample_batch;       //   update calls that pass the same buffer visit only the strata this shard owns
@@ -127,85 +128,103 @@ int grid_for(int64_t n, int threads, int sm_count) {
     return (int)g;
 }
 
-// The dense one-launch form (k_upd_dense_sorted) pays when the batch is the ascending sample just drawn, too large for
-// the per-CTA climb, and dirties enough of the tree that streaming all of it is cheaper than chasing paths.
+// The dense form (k_upd_dense_sorted) serves updates of the ascending sample just drawn when the batch dirties enough of
+// the tree (measured, tools/tree_sweep.py and profiles/r02_notes.md): more than 1 024 items on trees up to 2^20 leaves, a
+// 256th / 64th of the leaves at 2^21 / 2^22.  Smaller batches stay on the per-CTA climb: in isolation the dense form
+// is faster for them too on trees up to 2^18 leaves, but its one CTA per 1 024 leaves occupies the whole GPU, and inside a
+// sample / gather / update step that costs the neighbouring kernels more than it saves (2^20 leaves, 512 items: step
+// 28.3 -> 29.8 us).  per_tune("dense_update_lmax", L) sends every bound update of trees up to 2^L leaves there.
 bool dense_update_ok(const UpdArgs &a) {
-    return a.dense_counter && a.sorted_idx && a.sorted_fast && !a.publish_to && a.t.sum && a.t.mnn && a.n > 1024 &&
-           a.t.L > DENSE_LG_MAX && a.t.L <= 2 * DENSE_LG_MIN && a.t.cap <= 256 * a.n;  // measured: past 2^20 leaves the tree pair
-                                                                                       // leaves L2 and the multi-launch form wins
+    if (!(a.dense_counter && a.sorted_idx && a.sorted_fast && a.t.sum && a.t.mnn && a.t.L >= DENSE_L_MIN && a.t.L <= DENSE_L_MAX)) return false;
+    if (a.t.L <= a.dense_lmax) return true;
+    const int64_t n = (a.range && a.n_shards > 1) ? a.n / a.n_shards : a.n;  // a shard applies its own strata only
+    if (n <= 1024) return false;
+    return a.t.L <= 20 || (a.t.L == 21 && a.t.cap <= 256 * n) || (a.t.L == 22 && a.t.cap <= 64 * n);
 }
 
-// Batched leaf update + re-reduction (K1).  `td` non-null fuses K5 in front (one-CTA form only).
-int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s, bool pdl = false) {
+static int launch_update_cluster(const UpdArgs &a, const TdArgs *td, int skip_update, cudaStream_t s, bool pdl) {
     TdArgs none;
     memset(&none, 0, sizeof none);
-    if (!td && dense_update_ok(a)) {
-        // a large batch that is the sample just drawn: rebuild everything in one streaming launch
-        static bool attr_set = false;
-        if (!attr_set) {
-            PER_CUDA(cudaFuncSetAttribute(k_upd_dense_sorted<DENSE_LG_MIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, DenseShape<DENSE_LG_MIN>::SMEM_BYTES));
-            PER_CUDA(cudaFuncSetAttribute(k_upd_dense_sorted<DENSE_LG_MAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, DenseShape<DENSE_LG_MAX>::SMEM_BYTES));
-            attr_set = true;
+    // one launch: a cluster of CTAs (at most 16 where the device offers the non-portable size, else 8)
+    static int max_ctas = 0;
+    if (!max_ctas) {
+        PER_CUDA(cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, UPD_SMEM_BYTES));
+        max_ctas = 8;
+        if (cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
+            cudaLaunchConfig_t probe;
+            memset(&probe, 0, sizeof probe);
+            probe.gridDim = dim3(UPD_MAX_CTAS);
+            probe.blockDim = dim3(UPD_THREADS);
+            probe.dynamicSmemBytes = UPD_SMEM_BYTES;
+            cudaLaunchAttribute pa[1];
+            pa[0].id = cudaLaunchAttributeClusterDimension;
+            pa[0].val.clusterDim.x = UPD_MAX_CTAS;
+            pa[0].val.clusterDim.y = 1;
+            pa[0].val.clusterDim.z = 1;
+            probe.attrs = pa;
+            probe.numAttrs = 1;
+            int nclusters = 0;
+            if (cudaOccupancyMaxActiveClusters(&nclusters, k_update_cluster, &probe) == cudaSuccess && nclusters >= 1) max_ctas = UPD_MAX_CTAS;
         }
-        if (a.t.L <= 2 * DENSE_LG_MIN)
-            PER_CUDA(launch_pdl(k_upd_dense_sorted<DENSE_LG_MIN>, dim3((unsigned)(a.t.cap >> DENSE_LG_MIN)), dim3(DenseShape<DENSE_LG_MIN>::THREADS),
-                                DenseShape<DENSE_LG_MIN>::SMEM_BYTES, s, pdl, a, a.dense_counter));
-        else
-            PER_CUDA(launch_pdl(k_upd_dense_sorted<DENSE_LG_MAX>, dim3((unsigned)(a.t.cap >> DENSE_LG_MAX)), dim3(DenseShape<DENSE_LG_MAX>::THREADS),
-                                DenseShape<DENSE_LG_MAX>::SMEM_BYTES, s, pdl, a, a.dense_counter));
+        cudaGetLastError();
+    }
+    // 8 CTAs by default: A/B on one box, 16 CTAs cost +0.3 us per step at 512 items (the phases are latency chains, not
+    // sector throughput; the larger cluster's barriers cost more than the halved per-SM work saves).  16 where it keeps a
+    // sorted batch of 1 025 .. 2 048 items on the per-CTA climb (<= 128 items per CTA), or when asked for (per_tune).
+    int limit = 8;
+    if (a.max_ctas > 0) limit = a.max_ctas < max_ctas ? a.max_ctas : max_ctas;
+    else if (a.sorted_idx && a.sorted_fast && a.n > 8 * SORT_SLICE_MAX && a.n <= 16 * SORT_SLICE_MAX) limit = max_ctas;
+    int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));  // 64 items per CTA and round
+    if (ncta < 1) ncta = 1;
+    if (ncta > limit) ncta = limit;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(ncta);
+    cfg.blockDim = dim3(UPD_THREADS);
+    cfg.dynamicSmemBytes = UPD_SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ncta;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // the kernel starts with pdl_wait()
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 2 : 1;
+    PER_CUDA(cudaLaunchKernelEx(&cfg, k_update_cluster, a, td ? *td : none, td ? 1 : 0, skip_update));
+    return PER_OK;
+}
+
+// Batched leaf update + re-reduction (K1).  `td` non-null puts K5 in front: fused into the one-launch cluster form, or as
+// a TD launch of that kernel followed by the dense form.
+int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cudaStream_t s, bool pdl = false) {
+    if (!skip_update && dense_update_ok(a) && (!td || td->batch <= UPD_CLUSTER_MAX_ITEMS)) {
+        static int slots = 0;  // resident CTAs of the device
+        if (!slots) {
+            int per_sm = 0;
+            PER_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_upd_dense_sorted, DENSE_THREADS, 0));
+            slots = (per_sm > 0 ? per_sm : 1) * sm_count;
+        }
+        UpdArgs d = a;
+        if (td) {
+            // the TD launch writes td->out_prio; the dense launch behind it searches its item runs meanwhile
+            UpdArgs t = a;
+            t.late_release = 1;
+            t.n = td->batch;
+            const int rc = launch_update_cluster(t, td, 1, s, pdl);
+            if (rc) return rc;
+            d.src = td->out_prio;
+            d.src_kind = LEAF_PRIO_F32;
+            d.early_search = 1;
+        }
+        const int64_t chunks = a.t.cap >> DENSE_CHUNK_LOG2;
+        PER_CUDA(launch_pdl(k_upd_dense_sorted, dim3((unsigned)(chunks < slots ? chunks : slots)), dim3(DENSE_THREADS), 0, s, pdl || td, d,
+                            a.dense_counter));
         return PER_OK;
     }
-    if (a.n <= (td || a.range || a.cluster_max <= 0 ? UPD_CLUSTER_MAX_ITEMS : a.cluster_max)) {
-        // one launch: a cluster of CTAs (at most 16 where the device offers the non-portable size, else 8)
-        static int max_ctas = 0;
-        if (!max_ctas) {
-            PER_CUDA(cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, UPD_SMEM_BYTES));
-            max_ctas = 8;
-            if (cudaFuncSetAttribute(k_update_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) {
-                cudaLaunchConfig_t probe;
-                memset(&probe, 0, sizeof probe);
-                probe.gridDim = dim3(UPD_MAX_CTAS);
-                probe.blockDim = dim3(UPD_THREADS);
-                probe.dynamicSmemBytes = UPD_SMEM_BYTES;
-                cudaLaunchAttribute pa[1];
-                pa[0].id = cudaLaunchAttributeClusterDimension;
-                pa[0].val.clusterDim.x = UPD_MAX_CTAS;
-                pa[0].val.clusterDim.y = 1;
-                pa[0].val.clusterDim.z = 1;
-                probe.attrs = pa;
-                probe.numAttrs = 1;
-                int nclusters = 0;
-                if (cudaOccupancyMaxActiveClusters(&nclusters, k_update_cluster, &probe) == cudaSuccess && nclusters >= 1) max_ctas = UPD_MAX_CTAS;
-            }
-            cudaGetLastError();
-        }
-        // 8 CTAs by default: A/B on one box, 16 CTAs cost +0.3 us per step at 512 items (the phases are latency chains, not
-        // sector throughput; the larger cluster's barriers cost more than the halved per-SM work saves).  16 where it keeps a
-        // sorted batch of 1 025 .. 2 048 items on the per-CTA climb (<= 128 items per CTA), or when asked for (per_tune).
-        int limit = 8;
-        if (a.max_ctas > 0) limit = a.max_ctas < max_ctas ? a.max_ctas : max_ctas;
-        else if (a.sorted_idx && a.sorted_fast && a.n > 8 * SORT_SLICE_MAX && a.n <= 16 * SORT_SLICE_MAX) limit = max_ctas;
-        int ncta = (int)((a.n + UPD_THREADS / LIFT_LANES - 1) / (UPD_THREADS / LIFT_LANES));  // 64 items per CTA and round
-        if (ncta < 1) ncta = 1;
-        if (ncta > limit) ncta = limit;
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof cfg);
-        cfg.gridDim = dim3(ncta);
-        cfg.blockDim = dim3(UPD_THREADS);
-        cfg.dynamicSmemBytes = UPD_SMEM_BYTES;
-        cfg.stream = s;
-        cudaLaunchAttribute attr[2];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = ncta;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // the kernel starts with pdl_wait()
-        attr[1].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = pdl ? 2 : 1;
-        PER_CUDA(cudaLaunchKernelEx(&cfg, k_update_cluster, a, td ? *td : none, td ? 1 : 0, skip_update));
-        return PER_OK;
-    }
+    if (a.n <= (td || a.range || a.cluster_max <= 0 ? UPD_CLUSTER_MAX_ITEMS : a.cluster_max))
+        return launch_update_cluster(a, td, skip_update, s, pdl);
     if (td) return fail(PER_ERR_ARG, "internal: fused TD needs the one-launch update form");
     const int g = grid_for(a.n, 256, sm_count);
     if (a.stamps) k_upd_stamp<<<g, 256, 0, s>>>(a);
@@ -385,6 +404,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     b->device = device;
     b->pdl = 3;
     b->sorted_update = 1;
+    b->dense_lmax = 0;
     b->ring_size = ring_size;
     b->alpha = alpha;
     b->obs_bytes = obs_bytes;
@@ -1021,6 +1041,11 @@ int per_tune(per_buffer *b, const char *key, int64_t value) {
         b->upd_max_ctas = (int)value;
         return PER_OK;
     }
+    if (!strcmp(key, "dense_update_lmax")) {
+        if (value < 0 || value > DENSE_L_MAX) return fail(PER_ERR_ARG, "per_tune: dense_update_lmax must be 0..%d", DENSE_L_MAX);
+        b->dense_lmax = (int)value;
+        return PER_OK;
+    }
     if (!strcmp(key, "sorted_update")) {
         b->sorted_update = value != 0;
         return PER_OK;
@@ -1069,6 +1094,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.rec_need = shard_need(b->global_len, b->idx_base, b->t.cap);
     a.rec_len = b->len;
     a.range = (b->sharded && b->last_sample_idx && d_idx == b->last_sample_idx && n == b->last_sample_batch) ? b->scal + 3 : nullptr;
+    a.n_shards = b->n_shards;
     if (b->early_publish && b->mailbox && n <= UPD_CLUSTER_MAX_ITEMS) {
         if (b->rec_published) return fail(PER_ERR_ARG, "early publish: the record of the next sample is already in the peers' mailboxes; sample before updating again");
         a.publish_to = b->d_peer_mailbox;
@@ -1085,6 +1111,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.cluster_max = b->upd_cluster_max;
     a.max_ctas = b->upd_max_ctas;
     a.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
+    a.dense_lmax = b->dense_lmax;
     if (a.sorted_idx) b->last_sample_idx = nullptr;  // the binding to that sample ends with its first update (see per_sample_sharded)
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);
 }
@@ -1204,19 +1231,7 @@ int per_td_priority_update(per_buffer *b, const float *d_q, const float *d_q_nex
     t.out_loss = d_out_loss;
     t.red = b->td_red();
     t.status = b->status();
-    bool dense = false;
-    if (d_idx && batch > 1024 && batch <= UPD_CLUSTER_MAX_ITEMS) {  // would update_common pick the dense form for this batch?
-        UpdArgs probe;
-        memset(&probe, 0, sizeof probe);
-        probe.t = b->t;
-        probe.n = batch;
-        probe.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
-        probe.sorted_idx = b->last_sample_idx && d_idx == b->last_sample_idx && batch == b->last_sample_batch;
-        probe.sorted_fast = b->sorted_update;
-        probe.publish_to = (b->early_publish && b->mailbox) ? b->d_peer_mailbox : nullptr;
-        dense = dense_update_ok(probe);
-    }
-    if (batch <= UPD_CLUSTER_MAX_ITEMS && !dense) {
+    if (batch <= UPD_CLUSTER_MAX_ITEMS) {
         if (d_idx) return update_common(b, d_idx, t.out_prio, LEAF_PRIO_F32, 0.0, batch, &t, s);
         UpdArgs a;
         memset(&a, 0, sizeof a);

@@ -367,6 +367,7 @@ __device__ __forceinline__ void descend_and_emit(const SampleArgs &a, const int6
         depth += s;
     }
     const int64_t k = node - a.cap;
+    if (a.tl && blockIdx.x == 0 && threadIdx.x == 0) tl_stamp(a.tl, 4, 21);  // descent done (first query of CTA 0)
     if (lane == 0) a.out_idx[q] = idx_base + k;
     if (want_w) {
         // memory.py:289-295.
@@ -430,6 +431,7 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
         }
     }
     __syncthreads();
+    if (tl_on) tl_stamp(a.tl, 3, 20);  // shared part in
     if (q >= a.batch) return;  // whole warps take the same side
     const DescentBlock left = block_from_shared(sh, lane);
     const double root_sum = sh.root_sum;

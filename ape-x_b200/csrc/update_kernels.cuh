@@ -85,6 +85,9 @@ struct UpdArgs {
     const u64 *range;         // sharded replay: {epoch, -, lo tag, hi tag} left by the last per_sample_sharded; when set, only
                               // the strata [lo, hi) that this shard owns are visited (null: all n items)
     unsigned *dense_counter;  // per-buffer word for k_upd_dense_sorted's "last CTA" election (null: that form is not offered)
+    int dense_lmax;           // deepest tree (log2 leaves) whose bound updates always take the dense form (0: form off)
+    int late_release;         // k_update_cluster as the TD launch in front of k_upd_dense_sorted: dependents are released behind the wait
+    int early_search;         // k_upd_dense_sorted behind such a launch: the item runs are searched before the wait
 };
 
 // Owned strata of the last sharded sample: tags are (epoch << 32) | value, written with atomicMax
@@ -390,9 +393,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
     // retired by then.  Otherwise the dependents are released at once.
     const bool tl_on = a.tl && rank == 0 && tid == 0;
     if (tl_on) tl_stamp(a.tl, 0, 7);
-    if (!a.publish_to) pdl_launch_dependents();  // (early publish: only behind the wait, see above)
+    const bool release_late = a.publish_to || a.late_release;
+    if (!release_late) pdl_launch_dependents();  // (early publish, TD in front of the dense form: only behind the wait)
     pdl_wait();  // indices / Q tables / the tree itself come from the kernels in front of this one
-    if (a.publish_to) pdl_launch_dependents();
+    if (release_late) pdl_launch_dependents();
     if (tl_on) tl_stamp(a.tl, 1, 8);
     UPD_TRACE(0);
     int first, last;  // items this launch visits: all of them, or the strata this shard owns
@@ -933,19 +937,24 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
 
 // ---------------------------------------------------------------------------------------
 // Dense form for LARGE sorted batches (the update of the sample just drawn, n > 1 024 items, trees of at most ~256 n
-// leaves): when a batch dirties a sizeable share of the leaves, rebuilding every node costs less than chasing the dirty
-// paths — a pair of 2^20-leaf trees is 16 MB of leaves in and 16 MB of nodes out, a few microseconds of L2 / HBM
-// streaming, against ~30 us for 4 096 scattered 20-level climbs.  ONE launch: CTA c owns leaves [2048 c, 2048 c + 2048):
-//   1. the items that fall there are a contiguous run of the ascending index array, found by a 32-ary search;
-//   2. the CTA's leaves are loaded into shared memory and the items applied to them in index order (equal indices are
-//      adjacent: the last of a run wins, memory.py:314-318); changed leaves are also written out;
-//   3. the 11 generations above them are rebuilt in shared memory and written out (every node = left (op) right);
-//   4. the last CTA to finish (a self-resetting counter) rebuilds the generations above the CTA roots.
+// leaves): when a batch dirties a sizeable share of the leaves, rebuilding every node above them costs less than chasing
+// the dirty paths — a pair of 2^20-leaf trees is 16 MB of leaves in and 16 MB of nodes out, a few microseconds of L2 /
+// HBM streaming, against ~30 us for 4 096 scattered 20-level climbs.  ONE launch; CTA c owns the chunks of 1 024 leaves
+// c, c + grid, ...:
+//   1. the items that fall into a chunk are a contiguous run of the ascending index array: its two ends are found by two
+//      warps side by side (32-ary searches); a chunk without items is left alone (its nodes are already right);
+//   2. the items write their leaves (equal indices are adjacent: the last of a run wins, memory.py:314-318);
+//   3. dense_lift(): every thread takes 8 consecutive leaves of each tree in two 32-byte loads, folds three generations in
+//      registers, five more by warp shuffles, the last two through 64 bytes of shared memory; nodes go out as 32-, 16- and
+//      8-byte stores.  No shared-memory staging of the chunk: ~16 resident CTAs per SM, so 2^21 leaves are one wave (the
+//      first version staged the chunk in 32 KB: 6 CTAs per SM, 1.15 waves at 2^20 leaves and 70 instructions per leaf —
+//      23-27 us, profiles/r02_notes.md);
+//   4. the last CTA to finish (a self-resetting counter) lifts the generations above the chunk roots the same way.
 // Same node values as every other form: the node array is a function of the leaves alone.
 // ---------------------------------------------------------------------------------------
-constexpr int DENSE_LG_MAX = 11;                       // leaves per CTA: 2^10 (trees up to 2^20 leaves: every CTA resident at once)
-constexpr int DENSE_LG_MIN = 10;                       //   or 2^11 (up to 2^22 leaves)
-constexpr int DENSE_TOP_MAX_LOG2 = DENSE_LG_MAX;       // CTA roots the last CTA can take (same buffers)
+constexpr int DENSE_CHUNK_LOG2 = 10;  // leaves per chunk = 8 per thread
+constexpr int DENSE_THREADS = 128;
+constexpr int DENSE_L_MIN = 12, DENSE_L_MAX = 22;  // tree depths the form is offered for (run_update narrows it further)
 
 // first position j in [lo, hi) with key(j) >= want (hi if none), keys ascending; all lanes of the warp return it
 __device__ __forceinline__ int64_t dense_lower_bound(const UpdArgs &a, int64_t lo, int64_t hi, int64_t want, int lane) {
@@ -967,128 +976,224 @@ __device__ __forceinline__ int64_t dense_lower_bound(const UpdArgs &a, int64_t l
     return lo;
 }
 
-template <int LG>
-struct DenseShape {
-    static constexpr int LEAVES = 1 << LG;
-    static constexpr int THREADS = LEAVES / 8;                              // 128 or 256
-    static constexpr int SMEM_BYTES = 2 * 2 * LEAVES * (int)sizeof(double);  // 32 or 64 KB of dynamic shared memory
-};
+// 32-byte accesses that are coherent at L2 (the nodes read were written by other threads of this launch)
+__device__ __forceinline__ void ld_cg_f64x4(const double *p, double &a, double &b, double &c, double &d) {
+    asm volatile("ld.global.cg.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_f64x4(double *p, double a, double b, double c, double d) {
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
 
-template <int LG>
-__global__ void __launch_bounds__(DenseShape<LG>::THREADS) k_upd_dense_sorted(UpdArgs a, unsigned *counter) {
-    constexpr int DENSE_LEAVES_LOG2 = LG, DENSE_LEAVES = DenseShape<LG>::LEAVES, DENSE_THREADS = DenseShape<LG>::THREADS;
-    extern __shared__ __align__(16) double s_dense[];
-    double *s_sum = s_dense;                      // relative heap of this CTA's subtree: node (1 << j) + i
-    double *s_min = s_dense + 2 * DENSE_LEAVES;
+// Rebuilds, in both trees, the g generations (1 <= g <= 10) above the 2^g consecutive nodes below node `sub_root`
+// (children of generation g: nodes (sub_root << g) + i).  Called by all DENSE_THREADS threads of the CTA; the nodes read
+// must be visible to the CTA (written before a __syncthreads() by this CTA, or fenced by their writers).  s_w: 8 doubles.
+// Rebuilds, in both trees, the g generations (1 <= g <= 10) above the 2^g consecutive nodes below node `sub_root`
+// (children of generation g: nodes (sub_root << g) + i).  Called by all DENSE_THREADS threads of the CTA; the nodes read
+// must be visible to the CTA (written before a __syncthreads() by this CTA, or fenced by their writers).  s_w: 8 doubles.
+// dirty8: which of this thread's 8 nodes changed (0xff where that is not known).  A thread whose 8 nodes are clean
+// fetches the node three generations above them instead (it is right already) and a node goes out only if something
+// below it changed: a chunk with a handful of new leaves costs 2 KB of reads and the dirty paths, not 32 KB each way.
+__device__ __forceinline__ void dense_lift(const TreeRef &t, const int64_t sub_root, const int g, double *s_w, const unsigned dirty8 = 0xffu) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (g < 3) {  // at most four nodes: one thread, level by level (it re-reads what it has just written)
+        if (tid == 0) {
+            for (int lvl = g - 1; lvl >= 0; --lvl)
+                for (int i = 0; i < (1 << lvl); ++i) {
+                    const int64_t node = (sub_root << lvl) + i;
+                    const double2 cs = ldcg_f64x2(t.sum + 2 * node), cm = ldcg_f64x2(t.mnn + 2 * node);
+                    t.sum[node] = __dadd_rn(cs.x, cs.y);
+                    t.mnn[node] = fmin(cm.x, cm.y);
+                }
+        }
+        return;
+    }
+    const bool on = tid < (1 << (g - 3));  // threads with 8 nodes each
+    double vs = 0.0, vm = 0.0;
+    bool dirty = on && dirty8 != 0;
+    if (on && !dirty) {
+        const int64_t n0 = (sub_root << g) + 8 * tid;
+        vs = ldcg_f64(t.sum + (n0 >> 3));
+        vm = ldcg_f64(t.mnn + (n0 >> 3));
+    }
+    if (dirty) {
+        const int64_t n0 = (sub_root << g) + 8 * tid;
+        double x0, x1, x2, x3, x4, x5, x6, x7, y0, y1, y2, y3, y4, y5, y6, y7;
+        ld_cg_f64x4(t.sum + n0, x0, x1, x2, x3);
+        ld_cg_f64x4(t.sum + n0 + 4, x4, x5, x6, x7);
+        ld_cg_f64x4(t.mnn + n0, y0, y1, y2, y3);
+        ld_cg_f64x4(t.mnn + n0 + 4, y4, y5, y6, y7);
+        const double a0 = __dadd_rn(x0, x1), a1 = __dadd_rn(x2, x3), a2 = __dadd_rn(x4, x5), a3 = __dadd_rn(x6, x7);
+        const double b0 = fmin(y0, y1), b1 = fmin(y2, y3), b2 = fmin(y4, y5), b3 = fmin(y6, y7);
+        st_f64x4(t.sum + (n0 >> 1), a0, a1, a2, a3);
+        st_f64x4(t.mnn + (n0 >> 1), b0, b1, b2, b3);
+        const double c0 = __dadd_rn(a0, a1), c1 = __dadd_rn(a2, a3), d0 = fmin(b0, b1), d1 = fmin(b2, b3);
+        *reinterpret_cast<double2 *>(t.sum + (n0 >> 2)) = make_double2(c0, c1);
+        *reinterpret_cast<double2 *>(t.mnn + (n0 >> 2)) = make_double2(d0, d1);
+        vs = __dadd_rn(c0, c1);
+        vm = fmin(d0, d1);
+        t.sum[n0 >> 3] = vs;
+        t.mnn[n0 >> 3] = vm;
+    }
+    const int64_t n3 = (sub_root << (g - 3)) + tid;  // this thread's node three generations up
+    const int shuf = g - 3 < 5 ? g - 3 : 5;
+#pragma unroll
+    for (int s = 1; s <= 5; ++s) {
+        if (s <= shuf) {  // the same for the whole CTA
+            const double ps = shfl_f64(vs, (lane + (1 << (s - 1))) & 31), pm = shfl_f64(vm, (lane + (1 << (s - 1))) & 31);
+            const bool pd = __shfl_sync(0xffffffffu, (int)dirty, (lane + (1 << (s - 1))) & 31) != 0;
+            if ((lane & ((1 << s) - 1)) == 0) {  // left operand here, right operand 2^(s-1) lanes up
+                vs = __dadd_rn(vs, ps);
+                vm = fmin(vm, pm);
+                dirty = dirty || pd;
+                if (on && dirty) {
+                    t.sum[n3 >> s] = vs;
+                    t.mnn[n3 >> s] = vm;
+                }
+            }
+        }
+    }
+    if (g - 3 > 5) {  // two or four warps hold one subtree root each (callers lift only what has a dirty node: all stored)
+        if (lane == 0 && on) {
+            s_w[tid >> 5] = vs;
+            s_w[4 + (tid >> 5)] = vm;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            if (g == 10) {
+                const double l0 = __dadd_rn(s_w[0], s_w[1]), l1 = __dadd_rn(s_w[2], s_w[3]);
+                const double m0 = fmin(s_w[4], s_w[5]), m1 = fmin(s_w[6], s_w[7]);
+                *reinterpret_cast<double2 *>(t.sum + 2 * sub_root) = make_double2(l0, l1);
+                *reinterpret_cast<double2 *>(t.mnn + 2 * sub_root) = make_double2(m0, m1);
+                t.sum[sub_root] = __dadd_rn(l0, l1);
+                t.mnn[sub_root] = fmin(m0, m1);
+            } else {
+                t.sum[sub_root] = __dadd_rn(s_w[0], s_w[1]);
+                t.mnn[sub_root] = fmin(s_w[4], s_w[5]);
+            }
+        }
+        __syncthreads();  // s_w is free again
+    }
+}
+
+__global__ void __launch_bounds__(DENSE_THREADS) k_upd_dense_sorted(UpdArgs a, unsigned *counter) {
+    constexpr int CHUNK = 1 << DENSE_CHUNK_LOG2;
     __shared__ int64_t s_run[2];
     __shared__ int s_last;
     __shared__ double s_max[DENSE_THREADS / 32];
-    pdl_launch_dependents();
-    pdl_wait();
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int64_t leaf0 = (int64_t)blockIdx.x * DENSE_LEAVES;
+    __shared__ double s_w[8];
+    __shared__ unsigned s_dirty[CHUNK / 32];  // leaves of the chunk that got a new value
+    // Behind the TD launch of the same update (early_search) the item runs are searched BEFORE the wait: that launch
+    // releases its dependents only behind its own wait, so the sample that wrote the indices and the owned range has
+    // retired; the priorities it is still computing are read behind the wait.  With early publish the sampling kernel
+    // behind this one starts its exchange before its wait and relies on every kernel up to the previous sample having
+    // retired: dependents are then released behind the wait (as k_update_cluster does).
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    bool waited = !a.early_search;
+    if (waited) {
+        if (!a.publish_to) pdl_launch_dependents();
+        pdl_wait();
+        if (a.publish_to) pdl_launch_dependents();
+    }
+#define DENSE_TRACE(slot, any_cta)                                        \
+    do {                                                                  \
+        if (a.trace && tid == 0 && ((any_cta) || blockIdx.x == 0)) {      \
+            u64 t__;                                                      \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));       \
+            a.trace[slot] = t__;                                          \
+        }                                                                 \
+    } while (0)
+    if (!a.early_search) DENSE_TRACE(0, false);
     int first, last;
     owned_range(a.range, a.n, first, last);
-    if (tid < 32) {
-        const int64_t lo = dense_lower_bound(a, first, last, leaf0, lane);
-        const int64_t hi = dense_lower_bound(a, lo, last, leaf0 + DENSE_LEAVES, lane);
-        if (lane == 0) {
-            s_run[0] = lo;
-            s_run[1] = hi;
-        }
-    }
-    for (int i = tid; i < DENSE_LEAVES; i += DENSE_THREADS) {  // the leaves as they are
-        s_sum[DENSE_LEAVES + i] = ldcg_f64(a.t.sum + a.t.cap + leaf0 + i);
-        s_min[DENSE_LEAVES + i] = ldcg_f64(a.t.mnn + a.t.cap + leaf0 + i);
-    }
-    __syncthreads();
-    const int64_t lo = s_run[0], hi = s_run[1];
+    const int64_t chunks = a.t.cap >> DENSE_CHUNK_LOG2;
     double my_max = 0.0;
-    for (int64_t j = lo + tid; j < hi; j += DENSE_THREADS) {  // the items of this CTA; the last of an equal run wins
-        int64_t k;
-        double leaf, raw;
-        if (!upd_item(a, j, k, leaf, raw)) continue;
-        my_max = fmax(my_max, raw);
-        const int64_t nxt = j + 1 < hi ? upd_index(a, j + 1) : INT64_MAX;
-        if (nxt < k) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending: not the sample's buffer any more
-        if (nxt == k) continue;
-        const int64_t i = k - leaf0;
-        if (i < 0 || i >= DENSE_LEAVES) {  // cannot happen for an ascending array
-            atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
-            continue;
+    for (int64_t chunk = blockIdx.x; chunk < chunks; chunk += gridDim.x) {
+        const int64_t leaf0 = chunk << DENSE_CHUNK_LOG2;
+        if (warp == 0) {
+            const int64_t lo = dense_lower_bound(a, first, last, leaf0, lane);
+            if (lane == 0) s_run[0] = lo;
+        } else if (warp == 1) {
+            const int64_t hi = dense_lower_bound(a, first, last, leaf0 + CHUNK, lane);
+            if (lane == 0) s_run[1] = hi;
+        } else if (warp == 2) {
+            s_dirty[lane] = 0;
         }
-        s_sum[DENSE_LEAVES + i] = leaf;
-        s_min[DENSE_LEAVES + i] = leaf;
-        a.t.sum[a.t.cap + k] = leaf;
-        a.t.mnn[a.t.cap + k] = leaf;
+        DENSE_TRACE(14, false);  // runs found
+        if (!waited) {
+            pdl_wait();
+            pdl_launch_dependents();
+            waited = true;
+        }
+        DENSE_TRACE(1, false);  // priorities ready
+        __syncthreads();
+        const int64_t lo = s_run[0], hi = s_run[1];
+        for (int64_t j = lo + tid; j < hi; j += DENSE_THREADS) {  // the items of this chunk; the last of an equal run wins
+            int64_t k;
+            double leaf, raw;
+            if (!upd_item(a, j, k, leaf, raw)) continue;
+            my_max = fmax(my_max, raw);
+            const int64_t nxt = j + 1 < hi ? upd_index(a, j + 1) : INT64_MAX;
+            if (nxt < k) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending: not the sample's buffer any more
+            if (nxt == k) continue;
+            if (k < leaf0 || k >= leaf0 + CHUNK) {  // cannot happen for an ascending array
+                atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
+                continue;
+            }
+            a.t.sum[a.t.cap + k] = leaf;
+            a.t.mnn[a.t.cap + k] = leaf;
+            atomicOr(&s_dirty[(k - leaf0) >> 5], 1u << ((k - leaf0) & 31));
+        }
+        __syncthreads();  // the leaves just written are visible to the CTA's loads; s_run may be rewritten
+        DENSE_TRACE(10, false);  // leaves written
+        if (hi > lo) {           // (a chunk without items is right as it is)
+            const unsigned dirty8 = (s_dirty[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
+            dense_lift(a.t, (a.t.cap >> DENSE_CHUNK_LOG2) + chunk, DENSE_CHUNK_LOG2, s_w, dirty8);  // ends with a CTA barrier
+        }
+        DENSE_TRACE(11, false);  // chunk lifted
+    }
+    if (!waited) {  // a CTA without a chunk
+        pdl_wait();
+        pdl_launch_dependents();
     }
     if (a.max_prio) {
         if (a.src_kind == LEAF_GIVEN) my_max = (tid == 0 && blockIdx.x == 0) ? a.batch_max : 0.0;
         for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, lane ^ o));
-        if (lane == 0) s_max[tid >> 5] = my_max;
+        if (lane == 0) s_max[warp] = my_max;
     }
-    __syncthreads();
-    if (a.max_prio && tid == 0) {
-        double m = 0.0;
-        for (int w = 0; w < DENSE_THREADS / 32; ++w) m = fmax(m, s_max[w]);
-        if (m > 0.0) atomic_max_pos_f64(a.max_prio, m);
-    }
-    // generations above the leaves, level by level (thread i of a level reads one 16-byte pair: conflict-free)
-#pragma unroll 1
-    for (int m = DENSE_LEAVES >> 1; m >= 1; m >>= 1) {
-        for (int i = tid; i < m; i += DENSE_THREADS) {
-            const double2 cs = *reinterpret_cast<const double2 *>(s_sum + 2 * (m + i));
-            const double2 cm = *reinterpret_cast<const double2 *>(s_min + 2 * (m + i));
-            s_sum[m + i] = __dadd_rn(cs.x, cs.y);
-            s_min[m + i] = fmin(cm.x, cm.y);
-        }
-        __syncthreads();
-    }
-    // write the subtree's internal nodes: relative slot p = (1 << j) + i  <->  node ((sub_root << j) + i)
-    const int64_t sub_root = (a.t.cap >> DENSE_LEAVES_LOG2) + blockIdx.x;
-    for (int p = 1 + tid; p < DENSE_LEAVES; p += DENSE_THREADS) {
-        const int j = 31 - __clz(p);
-        const int64_t node = (sub_root << j) + (p - (1 << j));
-        a.t.sum[node] = s_sum[p];
-        a.t.mnn[node] = s_min[p];
-    }
-    // the last CTA to get here rebuilds what is above the CTA roots
+    // the last CTA to get here rebuilds what is above the chunk roots
     __threadfence();
     __syncthreads();
+    DENSE_TRACE(3, false);  // fenced
     if (tid == 0) {
+        if (a.max_prio) {
+            double m = 0.0;
+            for (int w = 0; w < DENSE_THREADS / 32; ++w) m = fmax(m, s_max[w]);
+            if (m > 0.0) atomic_max_pos_f64(a.max_prio, m);
+        }
         const unsigned done = atomicAdd(counter, 1u);
         s_last = done == gridDim.x - 1;
         if (s_last) *counter = 0;  // ready for the next launch
     }
     __syncthreads();
     if (!s_last) return;
+    DENSE_TRACE(12, true);  // last CTA elected
     __threadfence();
-    const int top_log2 = a.t.L - DENSE_LEAVES_LOG2;  // log2 of the number of CTA roots (<= DENSE_TOP_MAX_LOG2)
-    const int nroots = 1 << top_log2;
-    for (int i = tid; i < nroots; i += DENSE_THREADS) {
-        s_sum[nroots + i] = ldcg_f64(a.t.sum + nroots + i);
-        s_min[nroots + i] = ldcg_f64(a.t.mnn + nroots + i);
+    int left = a.t.L - DENSE_CHUNK_LOG2;  // generations still to lift: the 2^left chunk roots are right
+    while (left > 0) {
+        const int g = left < 10 ? left : 10;
+        for (int64_t grp = 0; grp < (int64_t(1) << (left - g)); ++grp) dense_lift(a.t, (int64_t(1) << (left - g)) + grp, g, s_w);
+        left -= g;
+        __syncthreads();  // the next round reads what this one wrote
     }
-    __syncthreads();
-#pragma unroll 1
-    for (int m = nroots >> 1; m >= 1; m >>= 1) {
-        for (int i = tid; i < m; i += DENSE_THREADS) {
-            const double2 cs = *reinterpret_cast<const double2 *>(s_sum + 2 * (m + i));
-            const double2 cm = *reinterpret_cast<const double2 *>(s_min + 2 * (m + i));
-            s_sum[m + i] = __dadd_rn(cs.x, cs.y);
-            s_min[m + i] = fmin(cm.x, cm.y);
-        }
-        __syncthreads();
+    DENSE_TRACE(5, true);  // top lifted
+    if (a.rec_out || a.publish_to) {  // sharded replay: the record of the refreshed tree, for this rank and (early publish) its peers
+        if (tid < 32)     // (reads nodes this CTA wrote before the barrier above, or fenced by the CTAs that have counted)
+            emit_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out, a.publish_to, a.n_shards, a.shard_rank,
+                        a.publish_to ? __ldcg(a.d_epoch) + 1 : 0);
     }
-    for (int p = 1 + tid; p < nroots; p += DENSE_THREADS) {
-        a.t.sum[p] = s_sum[p];
-        a.t.mnn[p] = s_min[p];
-    }
-    if (a.rec_out) {  // sharded replay: the record of the refreshed tree (roots from shared memory need the writes above)
-        __threadfence();
-        __syncthreads();
-        if (tid < 32) write_shard_record(a.t.sum, a.t.mnn, a.t.cap, a.rec_need, a.rec_len, a.rec_out);
-    }
+    DENSE_TRACE(13, true);
+#undef DENSE_TRACE
+    if (a.tl && tid == 0) tl_stamp(a.tl, 3, 9);  // (the last CTA, not CTA 0: this is the end of the update)
 }
 
 // ---------------------------------------------------------------------------------------

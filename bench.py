@@ -481,9 +481,16 @@ def main():
             None, P(o_loss), sp)
     u_ptrs = [pn.C.c_void_p(u_all[i].data_ptr()) for i in range(n_u)]
     a_rec, a_all = P(shard_rec), P(all_rec)
-    # kernels per step: k_sample, k_gather_ldg, k_update_cluster (TD fused in front); sharded adds
-    # k_shard_record (+ NCCL's all-gather kernel, not ours) and B > 2048 uses the multi-launch update
-    launches_per_step = 3 if (world == 1 or use_mailbox) else 4
+    # kernels per step: k_sample / k_sample_sharded, k_gather_bal, k_update_cluster (TD fused in front; global batches above
+    # 1 024 on trees the dense form serves: k_update_cluster as the TD launch + k_upd_dense_sorted); without the mailbox the
+    # sharded step adds k_shard_record (+ NCCL's all-gather kernel, not ours)
+    dense_lmax = int(os.environ.get("PER_DENSE_LMAX", "0"))
+    if "PER_DENSE_LMAX" in os.environ:
+        pn.check(pn.lib.per_tune(h, b"dense_update_lmax", dense_lmax))
+    tree_log2 = (ring - 1).bit_length()  # this rank's tree
+    two_launch_update = os.environ.get("PER_SORTED_UPDATE", "1") != "0" and 12 <= tree_log2 and (
+        tree_log2 <= dense_lmax or (BATCH > 1024 and (tree_log2 <= 20 or (tree_log2 == 21 and (1 << 21) <= 256 * BATCH))))  # dense_update_ok()
+    launches_per_step = (3 if (world == 1 or use_mailbox) else 4) + (1 if two_launch_update else 0)
 
     if world > 1 and not args.no_parity_check:
         # the sharded path against the single-tree oracle on the very GPUs about to be timed (tests/multi_gpu_parity.py;
@@ -785,7 +792,7 @@ def main():
         ent = sorted(((int(arr[i]) & ((1 << 56) - 1), (int(arr[i]) >> 56) & 0xff) for i in range(cnt.value)))
         names = {7: "update entered", 8: "update past wait", 12: "TD done", 9: "update CTA0 done", 1: "sample entered",
                  10: "records in", 2: "sample past wait", 11: "strata known", 3: "sample CTA0 done", 4: "gather entered",
-                 5: "gather past wait", 6: "gather CTA0 done", 13: "gather grid done"}
+                 5: "gather past wait", 6: "gather CTA0 done", 13: "gather grid done", 20: "sample shared part in", 21: "descent done"}
         steps_tl, cur = [], None
         for t, tag in ent:  # a step of the graph = [update, sample, gather]; anchor = update past its wait
             if tag == 8:
@@ -804,7 +811,7 @@ def main():
                           "the timed region: past the programmatic-launch wait -> done"}
         if args.timeline:
             msg = "rank %d timeline (us after 'update past wait', median of %d steps; period %.2f): " % (rank, len(body), anatomy["period"] or 0.0)
-            for tag in (12, 9, 1, 10, 2, 11, 3, 4, 5, 6, 13, 7):
+            for tag in (12, 9, 1, 10, 2, 20, 11, 21, 3, 4, 5, 6, 13, 7):
                 vals = [c[tag] for c in body if tag in c]
                 if vals:
                     msg += "%s %.2f | " % (names[tag], med(vals))

@@ -1,3 +1,5 @@
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_sharded.py tests/test_gpu_multi.py tests/test_gpu_dropin.py -x -q 2>&1 | tail -2
-for i in 1 2; do timeout 600 python bench.py --steps 1000 --warmup 5 --timeline --no-cpu-baseline --no-extras 2>&1 >/dev/null | grep -E "rank 0 timeline" | sed 's/.*period/N=1 period/' | cut -c1-300; done
-timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 300 --warmup 5 --no-extras --no-parity-check --timeline 2>&1 >gpurun_out/probe.json | grep -E "rank 0 timeline" | sed 's/.*period/N=2 period/' | cut -c1-420
+#!/bin/bash
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
+python tools/tree_sweep.py --caps 16 20 21 22 --batches 512 4096 16384 65536 2>&1 | tail -17
+python tools/update_phases.py --batch 2048 4096 2>&1 | tail -2
+python bench.py --steps 500 --warmup 5 --timeline --no-cpu-baseline --no-extras 2>&1 >/dev/null | grep -E "rank 0 timeline" | cut -c1-800

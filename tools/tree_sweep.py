@@ -115,7 +115,8 @@ for lc in args.caps:
         t_u = graph_us(sample_update, reps, inner) - t_s
         bytes_s = B * (8 * lc + 8 + 8 + 4)
         bytes_u = 2 * (8 * B + 24 * sum(min(B, 1 << l) for l in range(lc)))
-        dense = B > 1024 and 11 < lc <= 20 and cap <= 256 * B and not os.environ.get('NO_DENSE')
+        dense = (B > 1024 and 12 <= lc and (lc <= 20 or (lc == 21 and cap <= 256 * B) or (lc == 22 and cap <= 64 * B))
+                 and not os.environ.get('NO_DENSE'))  # dense_update_ok() in csrc/per_b200.cu
         if os.environ.get('NO_DENSE'):
             pn.check(lib.per_tune(h, b'sorted_update', 0))
         path = "cluster, sorted climb" if B <= 1024 else ("dense one-launch" if dense else ("cluster rounds" if B <= 4096 else "multi-launch"))

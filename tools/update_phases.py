@@ -20,6 +20,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--cap", type=int, default=1 << 20)
 ap.add_argument("--batch", type=int, nargs="+", default=[512, 1024, 4096])
 ap.add_argument("--iters", type=int, default=200)
+ap.add_argument("--dense-lmax", type=int, default=None)
 args = ap.parse_args()
 dev = torch.device("cuda")
 buf = memory.CustomPrioritizedReplayBuffer(args.cap, 0.6)
@@ -35,6 +36,12 @@ pn.check(lib.per_tune(h, b"update_trace", 1))
 NAMES = ["wait passed", "TD done", "arbitration", "leaves/barrier", "rounds done", "top rebuilt", "TD staged", "CTA max", "TD cl.sync",
          "batch max", "leaves+sib in", "climb done", "top loaded", "top written", "-", "-"]
 ORDER = [0, 6, 7, 8, 9, 1, 10, 2, 11, 3, 4, 12, 5, 13]
+if args.dense_lmax is not None:
+    pn.check(lib.per_tune(h, b"dense_update_lmax", args.dense_lmax))
+if args.dense_lmax is None or args.dense_lmax >= (args.cap - 1).bit_length():  # TD launch + k_upd_dense_sorted
+    NAMES = ["wait passed", "priorities ready (dense)", "-", "fenced (CTA 0)", "-", "top lifted", "TD staged", "CTA max", "TD cl.sync", "batch max",
+             "leaves written (CTA 0)", "chunk lifted (CTA 0)", "last CTA elected", "end", "runs found (CTA 0)", "-"]
+    ORDER = [0, 6, 7, 8, 9, 14, 1, 10, 11, 3, 12, 5, 13]
 for B in args.batch:
     u = [torch.rand(B, dtype=torch.float64, device=dev, generator=gen) for _ in range(8)]
     idx = torch.empty(B, dtype=torch.int64, device=dev)
