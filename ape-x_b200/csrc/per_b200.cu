@@ -212,6 +212,7 @@ int run_update(UpdArgs &a, const TdArgs *td, int skip_update, int sm_count, cuda
             UpdArgs t = a;
             t.late_release = 1;
             t.n = td->batch;
+            t.sorted_idx = 0;  // (the cluster size then follows the generic rule: the loss is summed in the same grouping as the fused form's)
             const int rc = launch_update_cluster(t, td, 1, s, pdl);
             if (rc) return rc;
             d.src = td->out_prio;

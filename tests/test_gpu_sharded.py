@@ -110,9 +110,11 @@ def test_sharded_equals_single_tree(mods, size, world, n_add, batch):
             assert s.status() == 0
 
 
-def test_sharded_fused_td_update(mods):
+@pytest.mark.parametrize("size,world,batch", [(1 << 14, 4, 512), (1 << 15, 2, 4096), (1 << 16, 2, 3000)])
+def test_sharded_fused_td_update(mods, size, world, batch):
+    """The fused TD update of the strata a shard has just drawn: k_update_cluster alone, or (more than 1 024 own strata)
+    as the TD launch in front of k_upd_dense_sorted, which then visits the owned range only."""
     memory, sharded, pn = mods
-    size, world, batch = 1 << 14, 4, 512
     data = make_data(size, (2, 8), 5)
     single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
     store = {}
@@ -135,9 +137,49 @@ def test_sharded_fused_td_update(mods):
         d = s.sample_device(batch, 0.4, u, gather=False)
         loss, prio = s.td_priority_update(q, qn, qt, want["act"], want["rew"], want["done"], want["weights"], 3, 0.99, d["idx"])
         assert torch.equal(prio, prio0) and float(loss) == float(loss0)
-    sv = single._it_sum._value
+    sv, mv = single._it_sum._value, single._it_min._value
     for r, s in enumerate(shards):
+        assert s.status() == 0
         assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
+        assert np.array_equal(bits(s.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, r, world))[1:])
+
+
+@pytest.mark.parametrize("size,world,batch", [(6000, 2, 512), (1 << 15, 2, 4096), (1 << 13, 2, 3000)])
+def test_early_publish_from_bound_updates(mods, size, world, batch):
+    """Early publish with every update applied to the sample's own index buffer (the learner loop): the record of the
+    next sample comes from the tail of k_update_cluster (the sorted climb) or, above 1 024 own strata, of
+    k_upd_dense_sorted."""
+    memory, sharded, pn = mods
+    data = make_data(size, (2, 8), 23 + world)
+    single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    single.add_batch_device(*data[:5], priorities=data[5])
+    shards = [sharded.ShardedReplay(size, 0.6, r, world, obs_shape=(2, 8), exchange=None) for r in range(world)]
+    for s in shards:
+        s.add_batch_device(*data)
+    sharded.ShardedReplay.enable_local_exchange(shards)
+    for s in shards:
+        s.enable_early_publish()
+        s.publish_record()
+    rng = np.random.default_rng(9)
+    for step in range(4):
+        u = rng.random(batch)
+        want = single.sample_device(batch, 0.4, uniforms=u, gather=False)
+        drawn = [s.sample_device(batch, 0.4, u, gather=False) for s in shards]
+        merged = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        for d in drawn:
+            mine = d["idx"] >= 0
+            assert not bool((merged[mine] >= 0).any())
+            merged[mine] = d["idx"][mine]
+        assert torch.equal(merged, want["idx"]), step
+        newp = torch.rand(batch, device="cuda") + 1e-3
+        single.update_priorities_device(want["idx"], newp)
+        for s, d in zip(shards, drawn):
+            s.update_priorities_device(d["idx"], newp)  # bound: the owned range of the sample's buffer
+            assert s.status() == 0
+        sv, mv = single._it_sum._value, single._it_min._value
+        for r, s in enumerate(shards):
+            assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
+            assert np.array_equal(bits(s.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, r, world))[1:])
 
 
 @pytest.mark.parametrize("world,early", [(2, False), (8, False), (2, True), (8, True)])

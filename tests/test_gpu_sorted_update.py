@@ -92,10 +92,11 @@ def test_sorted_path_equals_generic_path(mods, size, batch, kind):
     assert np.array_equal(bits(fast.tree_values(pn.TREE_SUM))[1:], bits(want)[1:])
 
 
-def test_sorted_path_fused_td(mods):
-    """The fused TD prologue in front of the sorted path (the bench's call)."""
+@pytest.mark.parametrize("size,batch", [(1 << 15, 512), (1 << 15, 2048), (1 << 20, 4096), (1 << 12, 1500)])
+def test_sorted_path_fused_td(mods, size, batch):
+    """The fused TD prologue in front of the sorted path (the bench's call); above 1 024 items the TD launch of
+    k_update_cluster followed by k_upd_dense_sorted."""
     memory, pn = mods
-    size, batch = 1 << 15, 512
     gen = torch.Generator(device="cuda").manual_seed(3)
     obs = torch.zeros((size, 8), dtype=torch.uint8, device="cuda")
     z = torch.zeros(size, device="cuda")
