@@ -448,47 +448,75 @@ __global__ void __launch_bounds__(128) k_sample(SampleArgs a) {
 
 // Unsharded, large batches (thousands of queries): one THREAD per query.  A warp per query spends ~750 warp
 // instructions on a query (shuffle-resolved walk, pow on two lanes); with enough queries to fill the machine the
-// dependent 8-byte loads of a per-thread walk (L of them, the top levels hitting in L1) hide behind each other and
-// the instruction count per query drops 30-fold.  Same arithmetic, same order: same bits.  p_total is computed
-// once per CTA.
-constexpr int SAMPLE_WIDE_THREADS = 256;
+// dependent loads of a per-thread walk hide behind each other and the instruction count per query drops 30-fold.
+// THREE generations per round trip: below node n the left children the walk can meet are 2n, {4n, 4n+2} and
+// {8n, 8n+2, 8n+4, 8n+6} — one 8-byte and three 32-byte loads whose addresses depend on n alone, four sectors instead of
+// three, a third of the dependent round trips.  L mod 3 single generations come first (the top of the tree: L1 hits), so the
+// last round ends at the leaves and its 32-byte loads have brought the sampled leaf itself (left or right child): the
+// weight's numerator needs no load of its own.  Same comparisons and subtractions in the same order: same bits.
+// p_total and the minimum's logarithm are computed once per CTA.
+constexpr int SAMPLE_WIDE_THREADS = 128;  // measured at 2^20 leaves, 4 096 / 16 384 / 65 536 queries: 32, 64, 128, 256 threads -> 128 best (5.75 / 6.19 / 6.65 us)
+__device__ __forceinline__ void ld_f64x4(const double *p, double &a, double &b, double &c, double &d) {
+    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+__device__ __forceinline__ bool walk_step(const double lv, double &mass) {  // memory.py:122-129; true: right child
+    if (lv > mass) return false;
+    mass = __dsub_rn(mass, lv);
+    return true;
+}
 __global__ void __launch_bounds__(SAMPLE_WIDE_THREADS) k_sample_wide(SampleArgs a) {
-    __shared__ double s_seg;
+    __shared__ double s_seg, s_lg_min;
     pdl_launch_dependents();
     pdl_wait();
-    if (threadIdx.x < 32 && !a.direct_mass) {
-        const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
-        if (threadIdx.x == 0) s_seg = __ddiv_rn(total, (double)a.batch);     // memory.py:245
+    const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const bool want_w = a.mnn && (a.out_w64 || a.out_w32);
+    const double uq = q < a.batch ? a.u[q] : 0.0;  // requested beside the shared part
+    const double root_sum = a.sum[1];
+    if (threadIdx.x < 32) {
+        if (!a.direct_mass) {
+            const double total = warp_prefix_total(a.sum, a.cap, a.n_rows - 1);  // memory.py:244
+            if (threadIdx.x == 0) s_seg = __ddiv_rn(total, (double)a.batch);     // memory.py:245
+        }
+        if (threadIdx.x == 0 && want_w) s_lg_min = log2(__dmul_rn(__ddiv_rn(a.mnn[1], root_sum), (double)a.n_rows));
     }
     __syncthreads();
-    const int64_t q = blockIdx.x * (int64_t)SAMPLE_WIDE_THREADS + threadIdx.x;
     if (q >= a.batch) return;
-    const double root_sum = a.sum[1];
     double mass;
     if (a.direct_mass) {
-        mass = a.u[q];
+        mass = uq;
         if (!(mass >= 0.0 && mass <= __dadd_rn(root_sum, 1e-5))) atomicOr(a.status, (u64)PER_STATUS_BAD_PREFIXSUM);
     } else {
         const double seg = s_seg;
-        mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));  // memory.py:247
+        mass = __dadd_rn(__dmul_rn(uq, seg), __dmul_rn((double)q, seg));  // memory.py:247
     }
     int64_t node = 1;
-#pragma unroll 1
-    for (int d = 0; d < a.L; ++d) {  // memory.py:122-129
+    double leaf_v = root_sum;  // (a tree of one leaf)
+    int d = 0;
+    for (const int singles = a.L % 3; d < singles; ++d) {
         const double lv = a.sum[2 * node];
-        if (lv > mass) {
-            node = 2 * node;
-        } else {
-            mass = __dsub_rn(mass, lv);
-            node = 2 * node + 1;
-        }
+        const bool right = walk_step(lv, mass);
+        if (d + 1 == a.L) leaf_v = right ? a.sum[2 * node + 1] : lv;  // (trees of 2 or 4 leaves)
+        node = 2 * node + right;
+    }
+#pragma unroll 1
+    for (; d < a.L; d += 3) {
+        double g0, g1, g2, g3, h0, h1, h2, h3, h4, h5, h6, h7;
+        const double c = a.sum[2 * node];
+        ld_f64x4(a.sum + 4 * node, g0, g1, g2, g3);
+        ld_f64x4(a.sum + 8 * node, h0, h1, h2, h3);
+        ld_f64x4(a.sum + 8 * node + 4, h4, h5, h6, h7);
+        const bool b1 = walk_step(c, mass);
+        const bool b2 = walk_step(b1 ? g2 : g0, mass);
+        const double hl = b1 ? (b2 ? h6 : h4) : (b2 ? h2 : h0);  // left child of the node two steps down
+        const bool b3 = walk_step(hl, mass);
+        if (b3) leaf_v = b1 ? (b2 ? h7 : h5) : (b2 ? h3 : h1);   // (used after the last round only)
+        else leaf_v = hl;
+        node = 8 * node + 4 * b1 + 2 * b2 + b3;
     }
     const int64_t k = node - a.cap;
     a.out_idx[q] = k;
-    if (a.mnn && (a.out_w64 || a.out_w32)) {  // memory.py:289-295
-        const double n = (double)a.n_rows;
-        const double lg_min = log2(__dmul_rn(__ddiv_rn(a.mnn[1], root_sum), n));
-        const double w = exp2(-a.beta * (log2(__dmul_rn(__ddiv_rn(a.sum[node], root_sum), n)) - lg_min));
+    if (want_w) {  // memory.py:289-295
+        const double w = exp2(-a.beta * (log2(__dmul_rn(__ddiv_rn(leaf_v, root_sum), (double)a.n_rows)) - s_lg_min));
         if (a.out_w64) a.out_w64[q] = w;
         if (a.out_w32) a.out_w32[q] = (float)w;
     }
