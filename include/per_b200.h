@@ -392,6 +392,8 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * sorted batches of 1 025 .. 2 048 items; 16 needs the device's non-portable cluster size);
  * "sorted_update" (default 1: an update of exactly the index buffer the last sample wrote takes
  * the sorted fast path of update_kernels.cuh; 0 = always the level-synchronous rounds);
+ * "dense_update_lmax" (default 0: such an update takes the dense streaming form only above 1 024 items; L = 12..22 sends
+ * every such update of a tree of up to 2^L leaves there, whatever its size);
  * "early_publish" (default 0; needs per_shard_attach_exchange): every priority update ends by
  * storing the refreshed shard record, tagged with the next exchange epoch, into all ranks'
  * mailboxes, so the record is on its way over NVLink while the update kernel retires and the next
@@ -407,7 +409,10 @@ int per_tune(per_buffer *b, const char *key, int64_t value);
  * run): [0] past the launch wait, [1] TD done, [2] arbitration done, [3] leaves written / cluster barrier passed,
  * [4] sparse rounds done, [5] top rebuilt, and finer ones: [6] TD inputs staged, [7] CTA maximum known,
  * [8] cluster barrier of the TD phase passed, [9] batch maximum known, [10] sorted path: leaves and siblings in,
- * [11] sorted path: climb done, [12] dense top loaded, [13] dense top written out.  Synchronises. */
+ * [11] sorted path: climb done, [12] dense top loaded, [13] dense top written out.  When the update runs as the TD
+ * launch + k_upd_dense_sorted, the second kernel stamps [14] item runs found, [1] priorities ready, [10] leaves written,
+ * [11] chunk lifted, [3] fenced (all CTA 0), then the CTA that finishes last: [12] elected, [5] top lifted, [13] end.
+ * Synchronises. */
 int per_update_trace(per_buffer *b, int64_t *h_out16, void *stream);
 /* Diagnostics: after per_tune(b, "timeline", entries) thread 0 of CTA 0 of every sample / gather /
  * update launch stores, into the six entries that launch owns (plain stores, nothing waits for
