@@ -61,9 +61,11 @@ struct per_buffer_s {
     // block for the small uploads; grown on demand, reused from call to call
     struct HostPath {
         int64_t cap;  // rows
-        double *d_u, *d_w64;
+        double *d_u, *d_w64;     // d_w64 .. d_done are the parts of d_small
         int64_t *d_idx, *d_act;
         float *d_rew, *d_done;
+        uint8_t *d_small;        // [cap] float64 weights | [cap] int64 indices | [cap] int64 actions | [cap] float rewards | [cap] float dones
+        uint8_t *h_small;        // pinned mirror of d_small: the per-row scalars of a sample come down in ONE copy
         uint8_t *d_obs, *d_next, *d_extra;
         uint8_t *d_upd;   // [cap] int64 indices | [cap] float64 leaves
         uint8_t *h_pin;   // pinned: [cap] float64 uniforms | [cap] int64 indices | [cap] float64 leaves
@@ -482,9 +484,10 @@ int per_create_shard(per_buffer **out, int device, int64_t global_size, int rank
 
 static void free_host_path(per_buffer *b) {
     per_buffer::HostPath &h = b->hp;
-    cudaFree(h.d_u); cudaFree(h.d_w64); cudaFree(h.d_idx); cudaFree(h.d_act); cudaFree(h.d_rew); cudaFree(h.d_done);
+    cudaFree(h.d_u); cudaFree(h.d_small);
     cudaFree(h.d_obs); cudaFree(h.d_next); cudaFree(h.d_extra); cudaFree(h.d_upd);
     if (h.h_pin) cudaFreeHost(h.h_pin);
+    if (h.h_small) cudaFreeHost(h.h_small);
     if (h.have_event) cudaEventDestroy(h.up_done);
     memset(&h, 0, sizeof h);
 }
@@ -502,16 +505,13 @@ static int ensure_host_path(per_buffer *b, int64_t rows, cudaStream_t s) {
         if (e == cudaSuccess && bytes) e = cudaMalloc(p, bytes);
     };
     grab((void **)&h.d_u, sizeof(double) * cap);
-    grab((void **)&h.d_w64, sizeof(double) * cap);
-    grab((void **)&h.d_idx, sizeof(int64_t) * cap);
-    grab((void **)&h.d_act, sizeof(int64_t) * cap);
-    grab((void **)&h.d_rew, sizeof(float) * cap);
-    grab((void **)&h.d_done, sizeof(float) * cap);
+    grab((void **)&h.d_small, 32 * (size_t)cap);
     grab((void **)&h.d_obs, (size_t)b->obs_bytes * cap);
     grab((void **)&h.d_next, (size_t)b->obs_bytes * cap);
     grab((void **)&h.d_extra, (size_t)b->extra_bytes * cap);
     grab((void **)&h.d_upd, 16 * (size_t)cap);
     if (e == cudaSuccess) e = cudaHostAlloc(&h.h_pin, 24 * (size_t)cap, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc(&h.h_small, 32 * (size_t)cap, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h.up_done, cudaEventDisableTiming);
     if (e != cudaSuccess) {  // all or nothing: a later, smaller request starts from a clean slate
         cudaGetLastError();
@@ -519,6 +519,11 @@ static int ensure_host_path(per_buffer *b, int64_t rows, cudaStream_t s) {
         return fail(e == cudaErrorMemoryAllocation ? PER_ERR_NOMEM : PER_ERR_CUDA, "host-buffer staging for %lld rows: %s",
                     (long long)cap, cudaGetErrorString(e));
     }
+    h.d_w64 = reinterpret_cast<double *>(h.d_small);
+    h.d_idx = reinterpret_cast<int64_t *>(h.d_small + 8 * (size_t)cap);
+    h.d_act = reinterpret_cast<int64_t *>(h.d_small + 16 * (size_t)cap);
+    h.d_rew = reinterpret_cast<float *>(h.d_small + 24 * (size_t)cap);
+    h.d_done = reinterpret_cast<float *>(h.d_small + 28 * (size_t)cap);
     h.have_event = true;
     h.cap = cap;
     return PER_OK;
@@ -1160,12 +1165,15 @@ int per_sample_host(per_buffer *b, const double *h_u, int64_t batch, double beta
     if (h_obs) PER_CUDA(cudaMemcpyAsync(h_obs, h.d_obs, (size_t)b->obs_bytes * batch, cudaMemcpyDeviceToHost, s));
     if (h_next) PER_CUDA(cudaMemcpyAsync(h_next, h.d_next, (size_t)b->obs_bytes * batch, cudaMemcpyDeviceToHost, s));
     if (h_extra && b->extra_bytes) PER_CUDA(cudaMemcpyAsync(h_extra, h.d_extra, (size_t)b->extra_bytes * batch, cudaMemcpyDeviceToHost, s));
-    if (h_act) PER_CUDA(cudaMemcpyAsync(h_act, h.d_act, sizeof(int64_t) * batch, cudaMemcpyDeviceToHost, s));
-    if (h_rew) PER_CUDA(cudaMemcpyAsync(h_rew, h.d_rew, sizeof(float) * batch, cudaMemcpyDeviceToHost, s));
-    if (h_done) PER_CUDA(cudaMemcpyAsync(h_done, h.d_done, sizeof(float) * batch, cudaMemcpyDeviceToHost, s));
-    if (h_w64) PER_CUDA(cudaMemcpyAsync(h_w64, h.d_w64, sizeof(double) * batch, cudaMemcpyDeviceToHost, s));
-    if (h_idx) PER_CUDA(cudaMemcpyAsync(h_idx, h.d_idx, sizeof(int64_t) * batch, cudaMemcpyDeviceToHost, s));
+    // the per-row scalars (32 bytes per row) in one copy into the pinned mirror, handed out from there
+    PER_CUDA(cudaMemcpyAsync(h.h_small, h.d_small, 32 * (size_t)h.cap, cudaMemcpyDeviceToHost, s));
     PER_CUDA(cudaStreamSynchronize(s));
+    const size_t cap = (size_t)h.cap;
+    if (h_w64) memcpy(h_w64, h.h_small, sizeof(double) * batch);
+    if (h_idx) memcpy(h_idx, h.h_small + 8 * cap, sizeof(int64_t) * batch);
+    if (h_act) memcpy(h_act, h.h_small + 16 * cap, sizeof(int64_t) * batch);
+    if (h_rew) memcpy(h_rew, h.h_small + 24 * cap, sizeof(float) * batch);
+    if (h_done) memcpy(h_done, h.h_small + 28 * cap, sizeof(float) * batch);
     return PER_OK;
 }
 
@@ -1191,8 +1199,8 @@ int per_update_host(per_buffer *b, const int64_t *h_idx, const double *h_prio, i
     for (int64_t i = 0; i < n; ++i) p_leaf[i] = pow(h_prio[i], b->alpha);  // libm: the bits CPython produces at memory.py:317
     int64_t *d_idx = reinterpret_cast<int64_t *>(h.d_upd);
     double *d_leaf = reinterpret_cast<double *>(h.d_upd + 8 * (size_t)h.cap);
-    PER_CUDA(cudaMemcpyAsync(d_idx, p_idx, sizeof(int64_t) * n, cudaMemcpyHostToDevice, s));
-    PER_CUDA(cudaMemcpyAsync(d_leaf, p_leaf, sizeof(double) * n, cudaMemcpyHostToDevice, s));
+    // indices and leaves are neighbours in the pinned block and in d_upd: one copy ([n, cap) of the index part is stale, unused)
+    PER_CUDA(cudaMemcpyAsync(d_idx, p_idx, 8 * (size_t)h.cap + sizeof(double) * n, cudaMemcpyHostToDevice, s));
     PER_CUDA(cudaEventRecord(h.up_done, s));
     if (h_batch_max) *h_batch_max = bmax;
     return per_update_leaves(b, d_idx, d_leaf, bmax, n, stream);

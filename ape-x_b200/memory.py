@@ -73,17 +73,6 @@ class _HostStage(object):
         ent[1].record()
         return d.reshape(a.shape)
 
-    def out_slot(self, name, shape, dtype):
-        """One of RING pinned host tensors for a result the native library writes by itself (per_sample_host)."""
-        key = ("out:" + name, tuple(shape), str(dtype))
-        ent = self.down_bufs.get(key)
-        if ent is None:
-            ent = [[torch.empty(tuple(shape), dtype=dtype, pin_memory=True) for _ in range(self.RING)], 0]
-            self.down_bufs[key] = ent
-        slot = ent[0][ent[1] % self.RING]
-        ent[1] += 1
-        return slot
-
     def down(self, named_tensors):
         """{name: cuda tensor} -> {name: numpy array}; one synchronisation for the lot."""
         outs = {}
@@ -517,7 +506,8 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         super(PrioritizedReplayBuffer, self)._stage(row, prio)
 
     def _draw_uniforms(self, batch_size):
-        return np.array([random.random() for _ in range(batch_size)], dtype=np.float64)  # memory.py:247
+        rnd = random.random
+        return np.array([rnd() for _ in range(batch_size)], dtype=np.float64)  # memory.py:247
 
     def sample_device(self, batch_size, beta, uniforms=None, gather=True, obs_dtype=None, obs_scale=1.0, channels_last=False):
         """Extension: sample() with every output left on the GPU.  Returns a dict with
@@ -566,20 +556,36 @@ class PrioritizedReplayBuffer(ReplayBuffer):
         self._flush()
         B = int(batch_size)
         u = self._draw_uniforms(B)
-        slot = self._host.out_slot
-        odt = getattr(torch, self._obs_dtype.name)
-        h = {"obs": slot("obs", (B,) + tuple(self._obs_shape), odt), "next_obs": slot("next_obs", (B,) + tuple(self._obs_shape), odt),
-             "act": slot("act", (B,), torch.int64), "rew": slot("rew", (B,), torch.float32),
-             "done": slot("done", (B,), torch.float32), "weights64": slot("w64", (B,), torch.float64),
-             "idx": slot("idx", (B,), torch.int64)}
-        if self._extra_shape is not None:
-            h["a_mu"] = slot("a_mu", (B,) + tuple(self._extra_shape), getattr(torch, self._extra_dtype.name))
-        P = lambda t: _n.C.c_void_p(t.data_ptr())
-        _n.check(_n.lib.per_sample_host(self._h, u.ctypes.data, B, float(beta), P(h["obs"]), P(h["next_obs"]), P(h["act"]),
-                                        P(h["rew"]), P(h["done"]), P(h["a_mu"]) if "a_mu" in h else None, P(h["weights64"]),
-                                        P(h["idx"]), _n.stream_ptr()))
-        out = {k: (np.array(v.numpy()) if COPY_SAMPLES else v.numpy()) for k, v in h.items()}
+        arrs, ptrs = self._sample_slot(B)
+        _n.check(_n.lib.per_sample_host(self._h, u.ctypes.data, B, float(beta), *ptrs, _n.stream_ptr()))
+        out = {k: np.array(v) for k, v in arrs.items()} if COPY_SAMPLES else arrs
         return tuple([out[k] for k in self._sample_fields] + [out["weights64"], out["idx"].tolist()])
+
+    def _sample_slot(self, B):
+        """Host arrays for one sample of B rows and their addresses in per_sample_host's argument order: a ring of
+        _HostStage.RING sets per batch size, built once (the frame arrays pinned: the library copies straight into them;
+        the per-row scalars plain: it hands them out of its own pinned block)."""
+        plans = self.__dict__.setdefault("_sample_plans", {})
+        plan = plans.get(B)
+        if plan is None:
+            sets = []
+            for _ in range(_HostStage.RING):
+                odt = getattr(torch, self._obs_dtype.name)
+                keep = [torch.empty((B,) + tuple(self._obs_shape), dtype=odt, pin_memory=True) for _ in range(2)]
+                arrs = {"obs": keep[0].numpy(), "next_obs": keep[1].numpy(), "act": np.empty(B, np.int64),
+                        "rew": np.empty(B, np.float32), "done": np.empty(B, np.float32),
+                        "weights64": np.empty(B, np.float64), "idx": np.empty(B, np.int64)}
+                if self._extra_shape is not None:
+                    keep.append(torch.empty((B,) + tuple(self._extra_shape), dtype=getattr(torch, self._extra_dtype.name), pin_memory=True))
+                    arrs["a_mu"] = keep[-1].numpy()
+                P = lambda a: _n.C.c_void_p(a.ctypes.data)
+                ptrs = (P(arrs["obs"]), P(arrs["next_obs"]), P(arrs["act"]), P(arrs["rew"]), P(arrs["done"]),
+                        P(arrs["a_mu"]) if "a_mu" in arrs else None, P(arrs["weights64"]), P(arrs["idx"]))
+                sets.append((arrs, ptrs, keep))
+            plan = plans[B] = [sets, 0]
+        arrs, ptrs, _ = plan[0][plan[1] % _HostStage.RING]
+        plan[1] += 1
+        return arrs, ptrs
 
     def update_priorities(self, idxes, priorities):
         """memory.py:300-320.  The reference walks the pairs in order and asserts as it goes;
