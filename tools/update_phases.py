@@ -38,10 +38,21 @@ NAMES = ["wait passed", "TD done", "arbitration", "leaves/barrier", "rounds done
 ORDER = [0, 6, 7, 8, 9, 1, 10, 2, 11, 3, 4, 12, 5, 13]
 if args.dense_lmax is not None:
     pn.check(lib.per_tune(h, b"dense_update_lmax", args.dense_lmax))
-if args.dense_lmax is None or args.dense_lmax >= (args.cap - 1).bit_length():  # TD launch + k_upd_dense_sorted
-    NAMES = ["wait passed", "priorities ready (dense)", "-", "fenced (CTA 0)", "-", "top lifted", "TD staged", "CTA max", "TD cl.sync", "batch max",
-             "leaves written (CTA 0)", "chunk lifted (CTA 0)", "last CTA elected", "end", "runs found (CTA 0)", "-"]
-    ORDER = [0, 6, 7, 8, 9, 14, 1, 10, 11, 3, 12, 5, 13]
+LOG2 = (args.cap - 1).bit_length()
+# the update as TD launch + k_upd_dense_sorted (per_update_trace in include/per_b200.h)
+NAMES_DENSE = ["wait passed", "priorities ready (dense)", "-", "fenced (CTA 0)", "-", "top lifted", "TD staged", "CTA max", "TD cl.sync", "batch max",
+               "leaves written (CTA 0)", "chunk lifted (CTA 0)", "last CTA elected", "end", "runs found (CTA 0)", "-"]
+ORDER_DENSE = [0, 6, 7, 8, 9, 14, 1, 10, 11, 3, 12, 5, 13]
+
+
+def dense_form(B):  # dense_update_ok() in csrc/per_b200.cu
+    if not 12 <= LOG2 <= 22:
+        return False
+    if args.dense_lmax is not None and LOG2 <= args.dense_lmax:
+        return True
+    return B > 1024 and (LOG2 <= 20 or (LOG2 == 21 and args.cap <= 256 * B) or (LOG2 == 22 and args.cap <= 64 * B))
+
+
 for B in args.batch:
     u = [torch.rand(B, dtype=torch.float64, device=dev, generator=gen) for _ in range(8)]
     idx = torch.empty(B, dtype=torch.int64, device=dev)
@@ -59,4 +70,6 @@ for B in args.batch:
         pn.check(lib.per_update_trace(h, st, sp))
         rows.append([st[i] - st[0] for i in range(16)])
     med = np.median(np.array(rows[20:]), axis=0) / 1e3
-    print("batch %d: " % B + " | ".join("%s %.2f" % (NAMES[i], med[i]) for i in ORDER if med[i] > 0 or i == 0))
+    names, order = (NAMES_DENSE, ORDER_DENSE) if dense_form(B) else (NAMES, ORDER)
+    print("batch %d%s: " % (B, " (TD launch + dense form)" if dense_form(B) else "") +
+          " | ".join("%s %.2f" % (names[i], med[i]) for i in order if med[i] > 0 or i == 0))
