@@ -37,6 +37,7 @@ struct per_buffer_s {
     u64 *stamps;
     // device scalars: word 0 status (u64), word 1 _max_priority (f64), word 2 two floats for K5,
     // word 3 sharded-sample epoch, word 4 retired-warp counter, words 5-6 owned-strata range tags
+    // ... words 48 and up: the chunk counters of k_upd_dense_sorted (DENSE_MAX_GROUPS + 1 unsigned)
     u64 *scal;
     uint8_t *obs, *next, *extra;
     int64_t *act;
@@ -101,6 +102,7 @@ __global__ void k_fill_f64(double *p, int64_t n, double x) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = x;
 }
 
+constexpr int SCAL_WORDS = 48 + (DENSE_MAX_GROUPS + 1 + 1) / 2;  // per_buffer::scal, in u64 words
 constexpr int64_t SAMPLE_WIDE_MIN = 2048;  // per_sample_indices: batches from here on use k_sample_wide
 
 bool is_pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
@@ -130,18 +132,23 @@ int grid_for(int64_t n, int threads, int sm_count) {
     return (int)g;
 }
 
-// The dense form (k_upd_dense_sorted) serves updates of the ascending sample just drawn when the batch dirties enough of
-// the tree (measured, tools/tree_sweep.py and profiles/r02_notes.md): more than 1 024 items on trees up to 2^20 leaves, a
-// 256th / 64th of the leaves at 2^21 / 2^22.  Smaller batches stay on the per-CTA climb: in isolation the dense form
-// is faster for them too on trees up to 2^18 leaves, but its one CTA per 1 024 leaves occupies the whole GPU, and inside a
-// sample / gather / update step that costs the neighbouring kernels more than it saves (2^20 leaves, 512 items: step
-// 28.3 -> 29.8 us).  per_tune("dense_update_lmax", L) sends every bound update of trees up to 2^L leaves there.
+// The dense form (k_upd_dense_sorted) serves updates of the ascending sample just drawn that are too large for the
+// per-CTA climb of k_update_cluster (measured, tools/tree_sweep.py and profiles/r02_notes.md): more than 1 024 items on
+// trees up to 2^20 leaves, more than 2 048 on deeper ones, as long as no CTA gets more than ~7 dirty chunks.  Smaller
+// batches stay on the climb: in isolation the dense form is faster for them too on trees up to 2^18 leaves, but its one
+// CTA per 1 024 leaves occupies the whole GPU, and inside a sample / gather / update step that costs the neighbouring
+// kernels more than it saves (2^20 leaves, 512 items: step 28.3 -> 29.8 us).  per_tune("dense_update_lmax", L) sends
+// every bound update of trees up to 2^L leaves there.
 bool dense_update_ok(const UpdArgs &a) {
     if (!(a.dense_counter && a.sorted_idx && a.sorted_fast && a.t.sum && a.t.mnn && a.t.L >= DENSE_L_MIN && a.t.L <= DENSE_L_MAX)) return false;
     if (a.t.L <= a.dense_lmax) return true;
     const int64_t n = (a.range && a.n_shards > 1) ? a.n / a.n_shards : a.n;  // a shard applies its own strata only
-    if (n <= 1024) return false;
-    return a.t.L <= 20 || (a.t.L == 21 && a.t.cap <= 256 * n) || (a.t.L == 22 && a.t.cap <= 64 * n);
+    if (n <= (a.t.L <= 20 ? 1024 : 2048)) return false;  // (up to 2 048 items a 16-CTA cluster keeps the per-CTA climb)
+    // a CTA lifts its dirty chunks one after the other (~4 us each): past ~7 of them the multi-launch form's grid-wide
+    // passes win (measured at 2^24 / 2^26 leaves: 8 192 items 37 / 38 us against 40 / 55, 16 384 items 56 / 60 against
+    // 43 / 60; 1 184 = the resident CTAs of a B200 at 64 registers)
+    const int64_t chunks = a.t.cap >> DENSE_CHUNK_LOG2;
+    return (n < chunks ? n : chunks) <= 7 * 1184;
 }
 
 static int launch_update_cluster(const UpdArgs &a, const TdArgs *td, int skip_update, cudaStream_t s, bool pdl) {
@@ -435,7 +442,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
         }                                                                                          \
     } while (0)
     TRY_ALLOC(b->stamps, sizeof(u64) * cap);
-    TRY_ALLOC(b->scal, sizeof(u64) * 48);
+    TRY_ALLOC(b->scal, sizeof(u64) * SCAL_WORDS);
     TRY_ALLOC(b->obs, b->obs_stride * ring_size);
     TRY_ALLOC(b->next, b->obs_stride * ring_size);
     TRY_ALLOC(b->extra, b->extra_stride * ring_size);
@@ -446,7 +453,7 @@ static int create_impl(per_buffer **out, int device, int64_t ring_size, int64_t 
     TRY_ALLOC(b->td_scratch, sizeof(float) * 2 * b->td_scratch_cap);
 #undef TRY_ALLOC
     PER_CUDA(cudaMemsetAsync(b->stamps, 0, sizeof(u64) * cap, 0));
-    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * 48, 0));
+    PER_CUDA(cudaMemsetAsync(b->scal, 0, sizeof(u64) * SCAL_WORDS, 0));
     const double one = 1.0;  // _max_priority = 1.0 (memory.py:233)
     PER_CUDA(cudaMemcpyAsync(b->max_prio(), &one, sizeof one, cudaMemcpyHostToDevice, 0));
     PER_CUDA(cudaFuncSetAttribute(k_gather_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, GATHER_SMEM_MAX));
@@ -1116,7 +1123,7 @@ static int update_common(per_buffer *b, const int64_t *d_idx, const void *src, i
     a.sorted_fast = b->sorted_update;
     a.cluster_max = b->upd_cluster_max;
     a.max_ctas = b->upd_max_ctas;
-    a.dense_counter = reinterpret_cast<unsigned *>(b->scal + 28);
+    a.dense_counter = reinterpret_cast<unsigned *>(b->scal + 48);
     a.dense_lmax = b->dense_lmax;
     if (a.sorted_idx) b->last_sample_idx = nullptr;  // the binding to that sample ends with its first update (see per_sample_sharded)
     return run_update(a, td, 0, b->sm_count, s, (b->pdl & 4) != 0);

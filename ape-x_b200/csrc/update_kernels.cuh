@@ -936,25 +936,31 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) k_update_cluster(UpdArgs a, Td
 }
 
 // ---------------------------------------------------------------------------------------
-// Dense form for LARGE sorted batches (the update of the sample just drawn, n > 1 024 items, trees of at most ~256 n
-// leaves): when a batch dirties a sizeable share of the leaves, rebuilding every node above them costs less than chasing
-// the dirty paths — a pair of 2^20-leaf trees is 16 MB of leaves in and 16 MB of nodes out, a few microseconds of L2 /
-// HBM streaming, against ~30 us for 4 096 scattered 20-level climbs.  ONE launch; CTA c owns the chunks of 1 024 leaves
-// c, c + grid, ...:
-//   1. the items that fall into a chunk are a contiguous run of the ascending index array: its two ends are found by two
-//      warps side by side (32-ary searches); a chunk without items is left alone (its nodes are already right);
-//   2. the items write their leaves (equal indices are adjacent: the last of a run wins, memory.py:314-318);
+// Dense form for LARGE sorted batches (the update of the sample just drawn): when a batch dirties a sizeable share of the
+// tree, rebuilding whole 1 024-leaf chunks costs less than chasing every dirty path through barriers — a pair of
+// 2^20-leaf trees is 16 MB of leaves in and 16 MB of nodes out, a few microseconds of L2 streaming.  ONE launch; the
+// tree is cut into chunks of 1 024 leaves and CTA b owns the contiguous range of chunks [b C / G, (b + 1) C / G):
+//   1. the items that fall into that range are a contiguous run of the ascending index array: its two ends are found by
+//      two warps side by side (32-ary searches);
+//   2. the run is walked in pieces of 128 items: the items of the piece that belong to the chunk of its first item write
+//      their leaves (equal indices are adjacent: the last of a run wins, memory.py:314-318) and mark them in a 1 024-bit
+//      map; when the chunk's last item has gone by, the chunk is lifted.  Chunks without items are never touched;
 //   3. dense_lift(): every thread takes 8 consecutive leaves of each tree in two 32-byte loads, folds three generations in
 //      registers, five more by warp shuffles, the last two through 64 bytes of shared memory; nodes go out as 32-, 16- and
-//      8-byte stores.  No shared-memory staging of the chunk: ~16 resident CTAs per SM, so 2^21 leaves are one wave (the
-//      first version staged the chunk in 32 KB: 6 CTAs per SM, 1.15 waves at 2^20 leaves and 70 instructions per leaf —
-//      23-27 us, profiles/r02_notes.md);
-//   4. the last CTA to finish (a self-resetting counter) lifts the generations above the chunk roots the same way.
+//      8-byte stores.  A thread whose 8 leaves are clean fetches the node three generations up instead, and a node is
+//      stored only if something below it changed.  No shared-memory staging of the chunk: 10 resident CTAs per SM (the
+//      first version staged the chunk in 32 KB: 6 CTAs per SM, 1.15 waves at 2^20 leaves, 70 instructions per leaf —
+//      23-27 us where this one takes 12-13, profiles/r02_dense_update_ncu.csv);
+//   4. chunks are counted per GROUP of 1 024 chunks (self-resetting counters); the CTA that completes a group lifts the
+//      ten generations above its chunk roots, and the CTA that completes the last group lifts what is left above the
+//      group roots (trees above 2^20 leaves) and writes the shard record.
 // Same node values as every other form: the node array is a function of the leaves alone.
 // ---------------------------------------------------------------------------------------
 constexpr int DENSE_CHUNK_LOG2 = 10;  // leaves per chunk = 8 per thread
 constexpr int DENSE_THREADS = 128;
-constexpr int DENSE_L_MIN = 12, DENSE_L_MAX = 22;  // tree depths the form is offered for (run_update narrows it further)
+constexpr int DENSE_GROUP_LOG2 = 10;  // chunks per group: one dense_lift above their roots
+constexpr int DENSE_L_MIN = 12, DENSE_L_MAX = 26;  // tree depths the form is offered for (run_update narrows it further)
+constexpr int DENSE_MAX_GROUPS = 1 << (DENSE_L_MAX - DENSE_CHUNK_LOG2 - DENSE_GROUP_LOG2);  // 64 group counters + 1 for the groups
 
 // first position j in [lo, hi) with key(j) >= want (hi if none), keys ascending; all lanes of the warp return it
 __device__ __forceinline__ int64_t dense_lower_bound(const UpdArgs &a, int64_t lo, int64_t hi, int64_t want, int lane) {
@@ -1075,14 +1081,15 @@ __device__ __forceinline__ void dense_lift(const TreeRef &t, const int64_t sub_r
     }
 }
 
-__global__ void __launch_bounds__(DENSE_THREADS) k_upd_dense_sorted(UpdArgs a, unsigned *counter) {
+__global__ void __launch_bounds__(DENSE_THREADS, 8) k_upd_dense_sorted(UpdArgs a, unsigned *counter) {
     constexpr int CHUNK = 1 << DENSE_CHUNK_LOG2;
     __shared__ int64_t s_run[2];
-    __shared__ int s_last;
+    __shared__ int64_t s_chunk;
+    __shared__ int s_lift[2];  // group to lift (-1: none), and whether this CTA completed the last group
     __shared__ double s_max[DENSE_THREADS / 32];
     __shared__ double s_w[8];
     __shared__ unsigned s_dirty[CHUNK / 32];  // leaves of the chunk that got a new value
-    // Behind the TD launch of the same update (early_search) the item runs are searched BEFORE the wait: that launch
+    // Behind the TD launch of the same update (early_search) the item run is searched BEFORE the wait: that launch
     // releases its dependents only behind its own wait, so the sample that wrote the indices and the owned range has
     // retired; the priorities it is still computing are read behind the wait.  With early publish the sampling kernel
     // behind this one starts its exchange before its wait and relies on every kernel up to the previous sample having
@@ -1106,84 +1113,127 @@ __global__ void __launch_bounds__(DENSE_THREADS) k_upd_dense_sorted(UpdArgs a, u
     int first, last;
     owned_range(a.range, a.n, first, last);
     const int64_t chunks = a.t.cap >> DENSE_CHUNK_LOG2;
-    double my_max = 0.0;
-    for (int64_t chunk = blockIdx.x; chunk < chunks; chunk += gridDim.x) {
-        const int64_t leaf0 = chunk << DENSE_CHUNK_LOG2;
-        if (warp == 0) {
-            const int64_t lo = dense_lower_bound(a, first, last, leaf0, lane);
-            if (lane == 0) s_run[0] = lo;
-        } else if (warp == 1) {
-            const int64_t hi = dense_lower_bound(a, first, last, leaf0 + CHUNK, lane);
-            if (lane == 0) s_run[1] = hi;
-        } else if (warp == 2) {
-            s_dirty[lane] = 0;
-        }
-        DENSE_TRACE(14, false);  // runs found
-        if (!waited) {
-            pdl_wait();
-            pdl_launch_dependents();
-            waited = true;
-        }
-        DENSE_TRACE(1, false);  // priorities ready
-        __syncthreads();
-        const int64_t lo = s_run[0], hi = s_run[1];
-        for (int64_t j = lo + tid; j < hi; j += DENSE_THREADS) {  // the items of this chunk; the last of an equal run wins
-            int64_t k;
-            double leaf, raw;
-            if (!upd_item(a, j, k, leaf, raw)) continue;
-            my_max = fmax(my_max, raw);
-            const int64_t nxt = j + 1 < hi ? upd_index(a, j + 1) : INT64_MAX;
-            if (nxt < k) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending: not the sample's buffer any more
-            if (nxt == k) continue;
-            if (k < leaf0 || k >= leaf0 + CHUNK) {  // cannot happen for an ascending array
-                atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
-                continue;
-            }
-            a.t.sum[a.t.cap + k] = leaf;
-            a.t.mnn[a.t.cap + k] = leaf;
-            atomicOr(&s_dirty[(k - leaf0) >> 5], 1u << ((k - leaf0) & 31));
-        }
-        __syncthreads();  // the leaves just written are visible to the CTA's loads; s_run may be rewritten
-        DENSE_TRACE(10, false);  // leaves written
-        if (hi > lo) {           // (a chunk without items is right as it is)
-            const unsigned dirty8 = (s_dirty[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
-            dense_lift(a.t, (a.t.cap >> DENSE_CHUNK_LOG2) + chunk, DENSE_CHUNK_LOG2, s_w, dirty8);  // ends with a CTA barrier
-        }
-        DENSE_TRACE(11, false);  // chunk lifted
+    const int64_t c0 = chunks * blockIdx.x / gridDim.x, c1 = chunks * (blockIdx.x + 1) / gridDim.x;  // this CTA's chunks
+    if (warp == 0) {
+        const int64_t lo = dense_lower_bound(a, first, last, c0 << DENSE_CHUNK_LOG2, lane);
+        if (lane == 0) s_run[0] = lo;
+    } else if (warp == 1) {
+        const int64_t hi = dense_lower_bound(a, first, last, c1 << DENSE_CHUNK_LOG2, lane);
+        if (lane == 0) s_run[1] = hi;
+    } else if (warp == 2) {
+        s_dirty[lane] = 0;
     }
-    if (!waited) {  // a CTA without a chunk
+    DENSE_TRACE(14, false);  // run found
+    if (!waited) {
         pdl_wait();
         pdl_launch_dependents();
     }
+    DENSE_TRACE(1, false);  // priorities ready
+    __syncthreads();
+    const int64_t lo = s_run[0], hi = s_run[1];
+    double my_max = 0.0;
+    int64_t j = lo;
+    int64_t open_chunk = -1;  // chunk with leaves written and not lifted yet (the same in every thread)
+    while (j < hi) {  // pieces of up to DENSE_THREADS items, all of one chunk
+        const bool have = j + tid < hi;
+        const int64_t key = have ? upd_index(a, j + tid) : -1;  // (valid or not: what the run was searched by)
+        if (tid == 0) s_chunk = key >> DENSE_CHUNK_LOG2;
+        __syncthreads();
+        const int64_t c = s_chunk;
+        if (c != open_chunk && open_chunk >= 0) {  // the chunk in front is complete: lift it (ends with a CTA barrier)
+            const unsigned dirty8 = (s_dirty[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
+            dense_lift(a.t, (a.t.cap >> DENSE_CHUNK_LOG2) + open_chunk, DENSE_CHUNK_LOG2, s_w, dirty8);
+            if (tid < CHUNK / 32) s_dirty[tid] = 0;
+            __syncthreads();
+        }
+        open_chunk = c;
+        const bool mine = have && (key >> DENSE_CHUNK_LOG2) == c;
+        if (c < c0 || c >= c1) {  // cannot happen for an ascending array
+            if (tid == 0) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);
+            open_chunk = -1;
+            break;
+        }
+        int64_t k = -1;
+        double leaf = 0.0, raw = 0.0;
+        if (mine && upd_item(a, j + tid, k, leaf, raw)) {  // (pow only for the items of this chunk)
+            my_max = fmax(my_max, raw);
+            const int64_t nxt = j + tid + 1 < hi ? upd_index(a, j + tid + 1) : INT64_MAX;
+            if (nxt < k) atomicOr(a.status, (u64)PER_STATUS_BAD_INDEX);  // not ascending: not the sample's buffer any more
+            if (nxt != k) {
+                a.t.sum[a.t.cap + k] = leaf;
+                a.t.mnn[a.t.cap + k] = leaf;
+                atomicOr(&s_dirty[(k & (CHUNK - 1)) >> 5], 1u << (k & 31));
+            }
+        }
+        j += __syncthreads_count(mine);  // (also: the leaves just written are visible to the CTA's loads)
+    }
+    DENSE_TRACE(10, false);  // leaves written
+    if (open_chunk >= 0) {
+        const unsigned dirty8 = (s_dirty[tid >> 2] >> ((tid & 3) * 8)) & 0xffu;
+        dense_lift(a.t, (a.t.cap >> DENSE_CHUNK_LOG2) + open_chunk, DENSE_CHUNK_LOG2, s_w, dirty8);
+    }
+    DENSE_TRACE(11, false);  // chunks lifted
     if (a.max_prio) {
         if (a.src_kind == LEAF_GIVEN) my_max = (tid == 0 && blockIdx.x == 0) ? a.batch_max : 0.0;
         for (int o = 16; o; o >>= 1) my_max = fmax(my_max, shfl_f64(my_max, lane ^ o));
         if (lane == 0) s_max[warp] = my_max;
     }
-    // the last CTA to get here rebuilds what is above the chunk roots
+    // Count this CTA's chunks into their groups.  A CTA that completes a group lifts the generations above the group's
+    // chunk roots; the one that completes the last group lifts what is above the group roots.
     __threadfence();
     __syncthreads();
     DENSE_TRACE(3, false);  // fenced
-    if (tid == 0) {
-        if (a.max_prio) {
-            double m = 0.0;
-            for (int w = 0; w < DENSE_THREADS / 32; ++w) m = fmax(m, s_max[w]);
-            if (m > 0.0) atomic_max_pos_f64(a.max_prio, m);
-        }
-        const unsigned done = atomicAdd(counter, 1u);
-        s_last = done == gridDim.x - 1;
-        if (s_last) *counter = 0;  // ready for the next launch
+    if (tid == 0 && a.max_prio) {
+        double m = 0.0;
+        for (int w = 0; w < DENSE_THREADS / 32; ++w) m = fmax(m, s_max[w]);
+        if (m > 0.0) atomic_max_pos_f64(a.max_prio, m);
     }
-    __syncthreads();
-    if (!s_last) return;
-    DENSE_TRACE(12, true);  // last CTA elected
-    __threadfence();
-    int left = a.t.L - DENSE_CHUNK_LOG2;  // generations still to lift: the 2^left chunk roots are right
-    while (left > 0) {
-        const int g = left < 10 ? left : 10;
-        for (int64_t grp = 0; grp < (int64_t(1) << (left - g)); ++grp) dense_lift(a.t, (int64_t(1) << (left - g)) + grp, g, s_w);
-        left -= g;
-        __syncthreads();  // the next round reads what this one wrote
+    const int top_gens = a.t.L - DENSE_CHUNK_LOG2;                                  // generations above the chunk roots
+    const int group_gens = top_gens < DENSE_GROUP_LOG2 ? top_gens : DENSE_GROUP_LOG2;  // ... of which a group lift takes these
+    const int64_t n_groups = chunks >> group_gens;
+    bool closes_all = false;
+    for (int64_t g = c0 >> group_gens; g <= (c1 - 1) >> group_gens && c1 > c0; ++g) {
+        if (tid == 0) {
+            const int64_t g_lo = g << group_gens, g_hi = (g + 1) << group_gens;
+            const unsigned mine = (unsigned)((c1 < g_hi ? c1 : g_hi) - (c0 > g_lo ? c0 : g_lo));
+            const unsigned before = atomicAdd(counter + g, mine);
+            s_lift[0] = before + mine == (1u << group_gens);
+            s_lift[1] = 0;
+            if (s_lift[0]) {
+                counter[g] = 0;  // ready for the next launch
+                __threadfence();
+            }
+        }
+        __syncthreads();
+        if (s_lift[0]) {  // (the same for the whole CTA)
+            DENSE_TRACE(12, true);  // a group completed
+            dense_lift(a.t, (int64_t(1) << (top_gens - group_gens)) + g, group_gens, s_w);
+            __syncthreads();
+            if (n_groups > 1) {
+                __threadfence();
+                __syncthreads();
+            }
+            if (n_groups == 1) {  // (trees up to 2^20 leaves: nothing above the group)
+                closes_all = true;
+                break;
+            }
+            if (tid == 0) {
+                const unsigned before = atomicAdd(counter + DENSE_MAX_GROUPS, 1u);
+                s_lift[1] = before + 1 == (unsigned)n_groups;
+                if (s_lift[1]) {
+                    counter[DENSE_MAX_GROUPS] = 0;
+                    __threadfence();
+                }
+            }
+            __syncthreads();
+            closes_all = closes_all || s_lift[1];
+        }
+        __syncthreads();  // s_lift is rewritten by the next round
+    }
+    if (!closes_all) return;
+    if (top_gens > group_gens) {
+        dense_lift(a.t, 1, top_gens - group_gens, s_w);  // at most 6 generations above the group roots
+        __syncthreads();
     }
     DENSE_TRACE(5, true);  // top lifted
     if (a.rec_out || a.publish_to) {  // sharded replay: the record of the refreshed tree, for this rank and (early publish) its peers
@@ -1193,7 +1243,7 @@ __global__ void __launch_bounds__(DENSE_THREADS) k_upd_dense_sorted(UpdArgs a, u
     }
     DENSE_TRACE(13, true);
 #undef DENSE_TRACE
-    if (a.tl && tid == 0) tl_stamp(a.tl, 3, 9);  // (the last CTA, not CTA 0: this is the end of the update)
+    if (a.tl && tid == 0) tl_stamp(a.tl, 3, 9);  // (the CTA that finishes, not CTA 0: this is the end of the update)
 }
 
 // ---------------------------------------------------------------------------------------

@@ -488,8 +488,8 @@ def main():
     if "PER_DENSE_LMAX" in os.environ:
         pn.check(pn.lib.per_tune(h, b"dense_update_lmax", dense_lmax))
     tree_log2 = (ring - 1).bit_length()  # this rank's tree
-    two_launch_update = os.environ.get("PER_SORTED_UPDATE", "1") != "0" and 12 <= tree_log2 and (
-        tree_log2 <= dense_lmax or (BATCH > 1024 and (tree_log2 <= 20 or (tree_log2 == 21 and (1 << 21) <= 256 * BATCH))))  # dense_update_ok()
+    two_launch_update = os.environ.get("PER_SORTED_UPDATE", "1") != "0" and 12 <= tree_log2 <= 26 and (
+        tree_log2 <= dense_lmax or (BATCH > (1024 if tree_log2 <= 20 else 2048) and min(BATCH, (1 << tree_log2) >> 10) <= 7 * 1184))  # dense_update_ok()
     launches_per_step = (3 if (world == 1 or use_mailbox) else 4) + (1 if two_launch_update else 0)
 
     if world > 1 and not args.no_parity_check:

@@ -392,8 +392,8 @@ int per_shard_exchange_stats(per_buffer *b, int64_t *h_out3, void *stream);
  * sorted batches of 1 025 .. 2 048 items; 16 needs the device's non-portable cluster size);
  * "sorted_update" (default 1: an update of exactly the index buffer the last sample wrote takes
  * the sorted fast path of update_kernels.cuh; 0 = always the level-synchronous rounds);
- * "dense_update_lmax" (default 0: such an update takes the dense streaming form only above 1 024 items; L = 12..22 sends
- * every such update of a tree of up to 2^L leaves there, whatever its size);
+ * "dense_update_lmax" (default 0: such an update takes the dense streaming form only when it is too large for the
+ * per-CTA climb; L = 12..26 sends every such update of a tree of up to 2^L leaves there, whatever its size);
  * "early_publish" (default 0; needs per_shard_attach_exchange): every priority update ends by
  * storing the refreshed shard record, tagged with the next exchange epoch, into all ranks'
  * mailboxes, so the record is on its way over NVLink while the update kernel retires and the next

@@ -212,7 +212,7 @@ def fill_device(buf, n, obs_shape, rng_seed, chunk=8192, with_prio=True):
     return (np.concatenate(prios) if prios else None), np.concatenate(tags)
 
 
-@pytest.mark.parametrize("size,batch", [(1 << 17, 512), (1 << 20, 512), (1 << 20, 2048), (1 << 22, 1500), (1 << 20, 4096), (1 << 20, 8191), (1 << 20, 8192), (300000, 20000), (1 << 20, 65536), (1 << 22, 65536), (1 << 16, 4096), (1 << 13, 2048), (1 << 12, 1500), (1 << 17, 2048), (1 << 14, 2500)])
+@pytest.mark.parametrize("size,batch", [(1 << 17, 512), (1 << 20, 512), (1 << 20, 2048), (1 << 22, 1500), (1 << 20, 4096), (1 << 20, 8191), (1 << 20, 8192), (300000, 20000), (1 << 20, 65536), (1 << 22, 65536), (1 << 16, 4096), (1 << 13, 2048), (1 << 12, 1500), (1 << 17, 2048), (1 << 14, 2500), (1 << 21, 3000), (1 << 23, 5000)])
 def test_sample_update_full_size_properties(memory, size, batch):
     """BASELINE config 2 tree sizes, tree-only rows (16-byte observations so the test stays
     light).  Device pow: leaves within 2 ulp of libm's; every internal node must then be the

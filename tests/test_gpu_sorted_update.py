@@ -54,7 +54,7 @@ def priorities(kind, n, gen):
 
 @pytest.mark.parametrize("size,batch", [(1 << 16, 512), (1 << 16, 64), (1 << 16, 1000), (5000, 512), (3000, 777), (1 << 11, 256),
                                         (700, 128), (40, 16), (1 << 20, 512), (1 << 14, 1), (1 << 20, 2048), (1 << 16, 1300), (1 << 22, 1025),
-                                        (1 << 12, 1100), (1 << 13, 3000), (1 << 18, 5000), (1 << 21, 9000), (1 << 22, 17000)])
+                                        (1 << 12, 1100), (1 << 13, 3000), (1 << 18, 5000), (1 << 21, 9000), (1 << 22, 17000), (1 << 22, 2500), (3000000, 4096)])
 @pytest.mark.parametrize("kind", ["uniform", "few_hot", "one_block", "two_ends", "steps"])
 def test_sorted_path_equals_generic_path(mods, size, batch, kind):
     memory, pn = mods

@@ -23,6 +23,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--caps", type=int, nargs="+", default=[16, 20, 24, 26])
 ap.add_argument("--batches", type=int, nargs="+", default=[256, 512, 1024, 4096, 16384, 65536])
 ap.add_argument("--cpu", action="store_true")
+ap.add_argument("--dense-lmax", type=int, default=None, help="per_tune dense_update_lmax (experiments)")
 args = ap.parse_args()
 dev = torch.device("cuda")
 lib, P = pn.lib, pn.ptr
@@ -92,6 +93,8 @@ for lc in args.caps:
                              priorities=torch.rand(m, dtype=torch.float64, device=dev, generator=gen) + 1e-3)
     del o, z
     h, sp = buf._h, pn.stream_ptr()
+    if args.dense_lmax is not None:
+        pn.check(lib.per_tune(h, b"dense_update_lmax", args.dense_lmax))
     if os.environ.get("UPD_CLUSTER_MAX"):
         pn.check(lib.per_tune(h, b"update_cluster_max", int(os.environ["UPD_CLUSTER_MAX"])))
     for B in args.batches:
@@ -115,11 +118,13 @@ for lc in args.caps:
         t_u = graph_us(sample_update, reps, inner) - t_s
         bytes_s = B * (8 * lc + 8 + 8 + 4)
         bytes_u = 2 * (8 * B + 24 * sum(min(B, 1 << l) for l in range(lc)))
-        dense = (B > 1024 and 12 <= lc and (lc <= 20 or (lc == 21 and cap <= 256 * B) or (lc == 22 and cap <= 64 * B))
+        dense = (12 <= lc <= 26 and B > (1024 if lc <= 20 else 2048) and min(B, cap >> 10) <= 7 * 1184
                  and not os.environ.get('NO_DENSE'))  # dense_update_ok() in csrc/per_b200.cu
+        if args.dense_lmax is not None and 12 <= lc <= args.dense_lmax:
+            dense = True
         if os.environ.get('NO_DENSE'):
             pn.check(lib.per_tune(h, b'sorted_update', 0))
-        path = "cluster, sorted climb" if B <= 1024 else ("dense one-launch" if dense else ("cluster rounds" if B <= 4096 else "multi-launch"))
+        path = "dense one-launch" if dense else ("cluster, sorted climb" if B <= 2048 else ("cluster rounds" if B <= 4096 else "multi-launch"))
         cpu = ""
         if args.cpu and lc <= 22:
             cs, cu = cpu_point(lc, B)

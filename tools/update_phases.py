@@ -46,11 +46,11 @@ ORDER_DENSE = [0, 6, 7, 8, 9, 14, 1, 10, 11, 3, 12, 5, 13]
 
 
 def dense_form(B):  # dense_update_ok() in csrc/per_b200.cu
-    if not 12 <= LOG2 <= 22:
+    if not 12 <= LOG2 <= 26:
         return False
     if args.dense_lmax is not None and LOG2 <= args.dense_lmax:
         return True
-    return B > 1024 and (LOG2 <= 20 or (LOG2 == 21 and args.cap <= 256 * B) or (LOG2 == 22 and args.cap <= 64 * B))
+    return B > (1024 if LOG2 <= 20 else 2048) and min(B, args.cap >> 10) <= 7 * 1184
 
 
 for B in args.batch:
