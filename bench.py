@@ -723,36 +723,6 @@ def main():
     finally:
         pn.check(lib.per_tune(h, b"pdl", int(os.environ.get("PER_PDL", pdl_default))))
     clocks = sampler.stop()
-    if os.environ.get("PER_GATHER_PROBE") and use_mailbox:
-        # experiment: the gather in BOUND mode (the sample's own index buffer, owned-range tags) without the update in front:
-        # graph of M x (sample, gather) minus graph of M x (sample), no programmatic chaining
-        pn.check(lib.per_tune(h, b"pdl", 0))
-        with torch.cuda.stream(side):
-            sp_side = pn.stream_ptr(side)
-
-            def s_only():
-                for i in range(M_SETS):
-                    pn.check(lib.per_sample_sharded(h, None, u_ptrs[(5 * i + 1) % n_u], GB, BETA, glen, a_idx, None, a_w32, sp_side))
-
-            def s_and_g():
-                for i in range(M_SETS):
-                    pn.check(lib.per_sample_sharded(h, None, u_ptrs[(5 * i + 1) % n_u], GB, BETA, glen, a_idx, None, a_w32, sp_side))
-                    pn.check(lib.per_gather(*(a_gather[:-1] + (sp_side,))))
-            s_only(); s_and_g()
-            g_a, g_b = capture(s_only), capture(s_and_g)
-        stream.wait_stream(side)
-        res = []
-        for g_ in (g_a, g_b):
-            g_.replay(); barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            for _ in range(5):
-                g_.replay()
-            e1.record(stream)
-            barrier()
-            res.append(e0.elapsed_time(e1) * 1e3 / (5 * M_SETS))
-        sys.stderr.write("rank %d gather probe: sample %.2f us, sample+gather %.2f us -> bound gather %.2f us\n" % (rank, res[0], res[1], res[1] - res[0]))
-        pn.check(lib.per_tune(h, b"pdl", int(os.environ.get("PER_PDL", pdl_default))))
     # back to the loop's own buffers: one sample + gather into idx / o_*
     draw_batch()
 
