@@ -826,8 +826,14 @@ int per_sample_sharded(per_buffer *b, const double *d_records, const double *d_u
     // more loops over them
     int64_t warps = batch / b->n_shards + batch / (4 * b->n_shards) + 4;
     if (warps > batch) warps = batch;
+    if (batch / b->n_shards >= SAMPLE_WIDE_MIN) {  // thousands of own strata: one thread each (the slack of the warp form, in threads)
+        const int64_t ctas = (warps + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
+        PER_CUDA(launch_pdl(k_sample_sharded<true>, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
+        PER_CUDA(cudaGetLastError());
+        return PER_OK;
+    }
     const int64_t ctas = (warps * 32 + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
-    PER_CUDA(launch_pdl(k_sample_sharded, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
+    PER_CUDA(launch_pdl(k_sample_sharded<false>, dim3((unsigned)ctas), dim3(SAMPLE_THREADS), 0, (cudaStream_t)stream, (b->pdl & 1) != 0, a));
     PER_CUDA(cudaGetLastError());
     return PER_OK;
 }

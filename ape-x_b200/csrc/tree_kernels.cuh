@@ -464,6 +464,36 @@ __device__ __forceinline__ bool walk_step(const double lv, double &mass) {  // m
     mass = __dsub_rn(mass, lv);
     return true;
 }
+// The descent of one query by one thread (memory.py:122-129), three generations per round trip; returns the leaf's slot
+// and leaves its value in leaf_v.
+__device__ __forceinline__ int64_t thread_descent(const double *sum, const int64_t cap, const int L, double mass, double &leaf_v) {
+    int64_t node = 1;
+    leaf_v = sum[1];  // (a tree of one leaf)
+    int d = 0;
+    for (const int singles = L % 3; d < singles; ++d) {
+        const double lv = sum[2 * node];
+        const bool right = walk_step(lv, mass);
+        if (d + 1 == L) leaf_v = right ? sum[2 * node + 1] : lv;  // (trees of 2 or 4 leaves)
+        node = 2 * node + right;
+    }
+#pragma unroll 1
+    for (; d < L; d += 3) {
+        double g0, g1, g2, g3, h0, h1, h2, h3, h4, h5, h6, h7;
+        const double c = sum[2 * node];
+        ld_f64x4(sum + 4 * node, g0, g1, g2, g3);
+        ld_f64x4(sum + 8 * node, h0, h1, h2, h3);
+        ld_f64x4(sum + 8 * node + 4, h4, h5, h6, h7);
+        const bool b1 = walk_step(c, mass);
+        const bool b2 = walk_step(b1 ? g2 : g0, mass);
+        const double hl = b1 ? (b2 ? h6 : h4) : (b2 ? h2 : h0);  // left child of the node two steps down
+        const bool b3 = walk_step(hl, mass);
+        if (b3) leaf_v = b1 ? (b2 ? h7 : h5) : (b2 ? h3 : h1);   // (used after the last round only)
+        else leaf_v = hl;
+        node = 8 * node + 4 * b1 + 2 * b2 + b3;
+    }
+    return node - cap;
+}
+
 __global__ void __launch_bounds__(SAMPLE_WIDE_THREADS) k_sample_wide(SampleArgs a) {
     __shared__ double s_seg, s_lg_min;
     pdl_launch_dependents();
@@ -489,31 +519,8 @@ __global__ void __launch_bounds__(SAMPLE_WIDE_THREADS) k_sample_wide(SampleArgs 
         const double seg = s_seg;
         mass = __dadd_rn(__dmul_rn(uq, seg), __dmul_rn((double)q, seg));  // memory.py:247
     }
-    int64_t node = 1;
-    double leaf_v = root_sum;  // (a tree of one leaf)
-    int d = 0;
-    for (const int singles = a.L % 3; d < singles; ++d) {
-        const double lv = a.sum[2 * node];
-        const bool right = walk_step(lv, mass);
-        if (d + 1 == a.L) leaf_v = right ? a.sum[2 * node + 1] : lv;  // (trees of 2 or 4 leaves)
-        node = 2 * node + right;
-    }
-#pragma unroll 1
-    for (; d < a.L; d += 3) {
-        double g0, g1, g2, g3, h0, h1, h2, h3, h4, h5, h6, h7;
-        const double c = a.sum[2 * node];
-        ld_f64x4(a.sum + 4 * node, g0, g1, g2, g3);
-        ld_f64x4(a.sum + 8 * node, h0, h1, h2, h3);
-        ld_f64x4(a.sum + 8 * node + 4, h4, h5, h6, h7);
-        const bool b1 = walk_step(c, mass);
-        const bool b2 = walk_step(b1 ? g2 : g0, mass);
-        const double hl = b1 ? (b2 ? h6 : h4) : (b2 ? h2 : h0);  // left child of the node two steps down
-        const bool b3 = walk_step(hl, mass);
-        if (b3) leaf_v = b1 ? (b2 ? h7 : h5) : (b2 ? h3 : h1);   // (used after the last round only)
-        else leaf_v = hl;
-        node = 8 * node + 4 * b1 + 2 * b2 + b3;
-    }
-    const int64_t k = node - a.cap;
+    double leaf_v;
+    const int64_t k = thread_descent(a.sum, a.cap, a.L, mass, leaf_v);
     a.out_idx[q] = k;
     if (want_w) {  // memory.py:289-295
         const double w = exp2(-a.beta * (log2(__dmul_rn(__ddiv_rn(leaf_v, root_sum), (double)a.n_rows)) - s_lg_min));
@@ -665,6 +672,8 @@ __global__ void k_shard_deliver(const int64_t *idx, const float *w32, int64_t n,
 
 constexpr int SAMPLE_THREADS = 128;  // one CTA per 4 owned strata: the descents spread over ~160 SMs (512-thread CTAs: +1 us per step, A/B in profiles/r02_notes.md)
 
+// WIDE: one THREAD per owned stratum instead of one warp (shards that own thousands of strata, like k_sample_wide).
+template <bool WIDE>
 __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a) {
     __shared__ double s_top[32];
     __shared__ SampleShared sh;                // the block under this shard's root: fetched by warp 0 for the whole CTA
@@ -745,8 +754,34 @@ __global__ void __launch_bounds__(SAMPLE_THREADS) k_sample_sharded(SampleArgs a)
             if (a.out_w32) a.out_w32[q] = 0.0f;
         }
     }
-    // own strata, one warp per query
     const int64_t idx_base = (int64_t)a.rank * a.cap;
+    if (WIDE) {  // own strata, one thread per query: the top walk out of shared memory, then thread_descent()
+        const bool want_w = a.mnn && (a.out_w64 || a.out_w32);
+        const double lg_min = want_w ? log2(__dmul_rn(__ddiv_rn(root_min, root_sum), (double)a.n_rows)) : 0.0;
+        for (int64_t q = lo + blockIdx.x * (int64_t)SAMPLE_THREADS + threadIdx.x; q < hi; q += (int64_t)gridDim.x * SAMPLE_THREADS) {
+            double mass = __dadd_rn(__dmul_rn(a.u[q], seg), __dmul_rn((double)q, seg));  // memory.py:247
+            for (int node = 1; node < a.n_shards;) {  // == shard_owner(): ends at this shard by construction of [lo, hi)
+                const double lv = s_top[2 * node];
+                if (lv > mass) {
+                    node = 2 * node;
+                } else {
+                    mass = __dsub_rn(mass, lv);
+                    node = 2 * node + 1;
+                }
+            }
+            double leaf_v;
+            const int64_t k = thread_descent(a.sum, a.cap, a.L, mass, leaf_v);
+            a.out_idx[q] = idx_base + k;
+            if (want_w) {  // memory.py:289-295, as in descend_and_emit()
+                const double w = exp2(-a.beta * (log2(__dmul_rn(__ddiv_rn(leaf_v, root_sum), (double)a.n_rows)) - lg_min));
+                if (a.out_w64) a.out_w64[q] = w;
+                if (a.out_w32) a.out_w32[q] = (float)w;
+            }
+        }
+        if (tl_on) tl_stamp(a.tl, 4, 3);
+        return;
+    }
+    // own strata, one warp per query
     const int64_t warps = (int64_t)gridDim.x * (SAMPLE_THREADS / 32);
     for (int64_t q = lo + blockIdx.x * (SAMPLE_THREADS / 32) + warp; q < hi; q += warps) {
         double mass;

@@ -43,6 +43,7 @@ def make_data(n, obs_shape, seed):
     (4096, 2, 4096, 256), (5000, 4, 5000, 512), (5000, 8, 3001, 512), (100000, 8, 100000, 4096),
     (5000, 8, 7300, 512),      # wraps the global ring: early slots overwritten
     (1 << 16, 16, 60000, 512),
+    (1 << 16, 2, 1 << 16, 8192), (70000, 4, 70000, 20000),  # thousands of own strata: one thread per stratum (k_sample_sharded<true>)
 ])
 def test_sharded_equals_single_tree(mods, size, world, n_add, batch):
     memory, sharded, pn = mods
