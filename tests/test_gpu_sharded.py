@@ -183,6 +183,45 @@ def test_early_publish_from_bound_updates(mods, size, world, batch):
             assert np.array_equal(bits(s.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, r, world))[1:])
 
 
+@pytest.mark.parametrize("size,world,batch", [(6000, 2, 512), (1 << 15, 2, 4096)])
+def test_early_publish_from_fused_td_updates(mods, size, world, batch):
+    """The learner loop on shards with early publish: sample, fused TD update of the sample's own buffer.  Above 1 024 own
+    strata the update is k_update_cluster as the TD launch + k_upd_dense_sorted, whose tail publishes the next record."""
+    memory, sharded, pn = mods
+    data = make_data(size, (2, 8), 31 + world)
+    single = memory.CustomPrioritizedReplayBuffer(size, 0.6)
+    single.add_batch_device(*data[:5], priorities=data[5])
+    shards = [sharded.ShardedReplay(size, 0.6, r, world, obs_shape=(2, 8), exchange=None) for r in range(world)]
+    for s in shards:
+        s.add_batch_device(*data)
+    sharded.ShardedReplay.enable_local_exchange(shards)
+    for s in shards:
+        s.enable_early_publish()
+        s.publish_record()
+    rng = np.random.default_rng(13)
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    for step in range(3):
+        u = rng.random(batch)
+        want = single.sample_device(batch, 0.4, uniforms=u)
+        drawn = [s.sample_device(batch, 0.4, u, gather=False) for s in shards]
+        merged = torch.full((batch,), -1, dtype=torch.int64, device="cuda")
+        for d in drawn:
+            mine = d["idx"] >= 0
+            merged[mine] = d["idx"][mine]
+        assert torch.equal(merged, want["idx"]), step
+        q, qn, qt = (torch.randn(batch, 18, device="cuda", generator=gen) for _ in range(3))
+        loss0, prio0, _ = single.td_priority_update(q, qn, qt, want["act"], want["rew"], want["done"], want["weights"], 3, 0.99,
+                                                    idx=want["idx"])
+        for s, d in zip(shards, drawn):
+            loss, prio = s.td_priority_update(q, qn, qt, want["act"], want["rew"], want["done"], want["weights"], 3, 0.99, d["idx"])
+            assert torch.equal(prio, prio0) and float(loss) == float(loss0)
+            assert s.status() == 0
+        sv, mv = single._it_sum._value, single._it_min._value
+        for r, s in enumerate(shards):
+            assert np.array_equal(bits(s.tree_values(pn.TREE_SUM))[1:], bits(so.slice_of(sv, r, world))[1:])
+            assert np.array_equal(bits(s.tree_values(pn.TREE_MIN))[1:], bits(so.slice_of(mv, r, world))[1:])
+
+
 @pytest.mark.parametrize("world,early", [(2, False), (8, False), (2, True), (8, True)])
 def test_peer_mailbox_exchange_matches_collective(mods, world, early):
     """The record exchange through mailboxes (per_shard_attach_exchange) must give the same
