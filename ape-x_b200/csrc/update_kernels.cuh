@@ -1085,7 +1085,7 @@ __global__ void __launch_bounds__(DENSE_THREADS, 8) k_upd_dense_sorted(UpdArgs a
     constexpr int CHUNK = 1 << DENSE_CHUNK_LOG2;
     __shared__ int64_t s_run[2];
     __shared__ int64_t s_chunk;
-    __shared__ int s_lift[2];  // group to lift (-1: none), and whether this CTA completed the last group
+    __shared__ int s_lift[2];  // whether this CTA's count completed the group at hand / the last group of all
     __shared__ double s_max[DENSE_THREADS / 32];
     __shared__ double s_w[8];
     __shared__ unsigned s_dirty[CHUNK / 32];  // leaves of the chunk that got a new value
